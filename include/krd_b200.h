@@ -1,0 +1,130 @@
+/* krd_b200.h — C ABI of the B200-native Kantorovich-Rubinstein (KR / earth mover's) distance path.
+ *
+ * This is the drop-in boundary for ONE call of the reference:
+ *
+ *     auto krd_matrix = earth_movers_distance( mass_trees, options.exponent );
+ *         gappa   src/commands/analyze/krd.cpp:140
+ *         genesis libs/genesis/lib/genesis/tree/mass_tree/emd.hpp:124  (declaration)
+ *                 libs/genesis/lib/genesis/tree/mass_tree/emd.cpp:183-235 (all pairs)
+ *                 libs/genesis/lib/genesis/tree/mass_tree/emd.cpp:60-181  (one pair)
+ *
+ * plus the optional steps around it: mass_tree_binify_masses
+ * (tree/mass_tree/functions.cpp:222-265, selected with krd_config.bins) and the
+ * "--normalize" division (src/commands/analyze/krd.cpp:144-150, the `divisor` argument).
+ *
+ * Plain C, POD only, no exceptions cross this boundary.  Every function returns a krd_status;
+ * krd_last_error() gives the message (same wording as the reference's exceptions where one exists).
+ *
+ * Flat data model
+ *   tree    n_edges edges, nodes 0..n_edges.  Edge e joins parent_node[e] (root side; genesis
+ *           "primary_node") and child_node[e] (leaf side; "secondary_node").
+ *   masses  CSR over samples (= one genesis MassTree each): sample_off[n_samples+1]; entry m has
+ *           edge[m], pos[m] = distance from the edge's parent node ("proximal_length",
+ *           tree/mass_tree/tree.hpp:186-199) and mass[m].  Any order is accepted; the iteration
+ *           order of a MassTree (edge ascending, pos ascending) is the fast path.
+ *   result  n_samples x n_samples row-major doubles, symmetric, zero diagonal
+ *           (utils/containers/matrix.hpp:85-94,214).
+ */
+#ifndef KRD_B200_H
+#define KRD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum krd_status {
+    KRD_OK = 0,
+    KRD_ERR_INVALID_EXPONENT = 1, /* emd.cpp:186-190  p <= 0 */
+    KRD_ERR_INCOMPATIBLE_TREES = 2, /* emd.cpp:78,109,123,172 */
+    KRD_ERR_TOO_FEW_SAMPLES = 3,  /* krd.cpp:131-133 (raised by the host command, not here) */
+    KRD_ERR_INVALID_ARGUMENT = 4,
+    KRD_ERR_CUDA = 5,
+    KRD_ERR_STATE = 6,            /* call order violated (e.g. masses before tree) */
+    KRD_ERR_NO_DEVICE = 7         /* no CUDA device: this library has NO CPU fallback */
+} krd_status;
+
+typedef struct krd_handle krd_handle;
+
+typedef struct krd_config {
+    int device;        /* CUDA device ordinal */
+    int bins;          /* 0 = exact positions (what `gappa analyze krd` does);
+                          B>0 = mass_tree_binify_masses(tree, B) first (functions.cpp:222) */
+    int split;         /* 0 = auto; >0 forces the segment-axis split factor of the pair kernel */
+    int reserved[5];   /* must be 0 */
+} krd_config;
+
+typedef struct krd_stats {
+    int64_t n_samples, n_edges, n_masses;
+    int64_t n_segments;     /* S: union segments (exact) or n_edges*(bins+1) (binned) */
+    int64_t ld_samples;     /* padded sample stride of the dense matrix F[S][ld] */
+    int64_t f_bytes;        /* bytes of F resident in HBM */
+    int64_t n_tiles;        /* 128x128 upper-triangular tiles (incl. diagonal) */
+    int32_t split;          /* segment-axis split used by the last pair launch */
+    int32_t pair_ctas;      /* CTAs of the last pair launch */
+    int32_t levels;         /* tree levels = launches of the F builder */
+    int32_t launches;       /* kernels launched by the last krd_compute* call */
+    float   ms_build;       /* device time of the F builder in the last compute (CUDA events) */
+    float   ms_pairs;       /* device time of pair kernel + epilogue in the last compute */
+} krd_stats;
+
+krd_status  krd_create(const krd_config* cfg, krd_handle** out);
+void        krd_destroy(krd_handle* h);
+const char* krd_last_error(const krd_handle* h); /* h may be NULL: error of a failed krd_create */
+
+/* Run all later work of this handle on the given cudaStream_t (NULL = legacy default stream). */
+krd_status krd_set_stream(krd_handle* h, void* cuda_stream);
+
+/* Topology + branch lengths shared by all samples (after
+ * mass_trees_make_average_branch_lengths, functions.cpp:271-335).  HOST pointers. */
+krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_node,
+                        const int32_t* child_node, const double* branch_length, int32_t root_node);
+
+/* The N mass trees.  HOST pointers (pinned memory makes the copy faster; see krd_host_alloc).
+ * Copies to HBM, assigns every mass to its segment slot and builds the segment table.
+ * Asynchronous w.r.t. the host when the buffers are pinned. */
+krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off,
+                          const int32_t* edge, const double* pos, const double* mass);
+
+/* Same, but the four arrays are already DEVICE pointers on cfg.device (no copy is made of
+ * edge/pos/mass: they must stay valid until the next krd_set_masses*).  sample_off is host. */
+krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off,
+                                 const int32_t* d_edge, const double* d_pos, const double* d_mass);
+
+/* earth_movers_distance(trees, p) [/ divisor].  Builds F (level-synchronous subtree scan), runs
+ * the all-pairs kernel, writes the n x n matrix.  `out` is a HOST pointer; returns after the
+ * matrix is complete in host memory. divisor = 1.0 for no normalisation. */
+krd_status krd_compute(krd_handle* h, double p, double divisor, double* out);
+
+/* Same with a DEVICE output pointer (n*n doubles); asynchronous on the handle's stream. */
+krd_status krd_compute_device(krd_handle* h, double p, double divisor, double* d_out);
+
+/* Multi-GPU sharding (one process per GPU, F replicated): rank r of `world` computes its share
+ * of the upper-triangular tiles into a packed DEVICE buffer of krd_shard_doubles() doubles
+ * (equal on every rank, so it can feed an NCCL all-gather directly). */
+int64_t    krd_shard_doubles(const krd_handle* h, int32_t world);
+krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t rank, int32_t world,
+                             double* d_packed);
+/* Scatter the all-gathered packed tiles (world * krd_shard_doubles doubles, DEVICE) into the
+ * full symmetric n x n DEVICE matrix. */
+krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out);
+
+/* Introspection for parity tests: copy the dense cumulative-mass matrix F (n_segments x
+ * ld_samples doubles) and the segment lengths (n_segments doubles) to HOST buffers. */
+krd_status krd_get_stats(const krd_handle* h, krd_stats* out);
+krd_status krd_debug_copy_F(krd_handle* h, double* out_F, double* out_len);
+
+/* Pinned host memory helpers for callers that want full-speed copies. */
+void* krd_host_alloc(int64_t bytes);
+void  krd_host_free(void* p);
+
+/* Roofline denominator: measured FP64 FMA throughput (TFLOP/s, FMA = 2 flop) of `device`, from a
+ * register-resident DFMA loop run for about `ms` milliseconds.  mode 0 = DFMA, 1 = DADD+DFMA mix
+ * (the p = 1 instruction mix), 2 = DMMA m8n8k4 tensor-core path. */
+double krd_measure_fp64_peak(int device, int mode, double ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KRD_B200_H */

@@ -1,0 +1,276 @@
+// C ABI of libkrd_b200.so — see include/krd_b200.h.  No exception leaves this file.
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "krd_common.cuh"
+
+namespace krd {
+
+static thread_local std::string g_create_error;
+
+krd_status fail(krd_handle* h, krd_status st, const std::string& msg)
+{
+    if (h) h->err = msg; else g_create_error = msg;
+    return st;
+}
+
+krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what)
+{
+    std::string m = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+    cudaGetLastError();  // clear sticky-less errors
+    return fail(h, KRD_ERR_CUDA, m);
+}
+
+static void free_masses(krd_handle* h)
+{
+    for (void*& q : h->d_owned) { if (q) cudaFree(q); q = nullptr; }
+    cudaFree(h->d_off); h->d_off = nullptr;
+    h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr;
+    h->have_masses = false; h->F_valid = false;
+}
+
+static krd_status set_masses_common(krd_handle* h, int32_t n_samples, const int64_t* sample_off)
+{
+    if (!h->have_tree) return fail(h, KRD_ERR_STATE, "krd_set_tree must be called before krd_set_masses");
+    if (n_samples < 0 || !sample_off) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad sample arguments");
+    if (sample_off[0] != 0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "sample_off[0] must be 0");
+    for (int i = 0; i < n_samples; ++i)
+        if (sample_off[i + 1] < sample_off[i]) return fail(h, KRD_ERR_INVALID_ARGUMENT, "sample_off must be non-decreasing");
+    return KRD_OK;
+}
+
+}  // namespace krd
+
+using namespace krd;
+
+extern "C" {
+
+krd_status krd_create(const krd_config* cfg, krd_handle** out)
+{
+    if (!out) return KRD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, KRD_ERR_NO_DEVICE, "no CUDA device available (this library has no CPU fallback)");
+    }
+    krd_config c{};
+    if (cfg) c = *cfg;
+    if (c.device < 0 || c.device >= n_dev) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    if (c.bins < 0) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "bins must be >= 0");
+    cudaDeviceProp prop;
+    if ((e = cudaSetDevice(c.device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, c.device)) != cudaSuccess)
+        return cuda_fail(nullptr, e, "cudaSetDevice");
+    if (prop.major != 10) return fail(nullptr, KRD_ERR_NO_DEVICE, "device is not sm_100 (this library is built for B200 only)");
+    krd_handle* h = new (std::nothrow) krd_handle();
+    if (!h) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "out of host memory");
+    h->cfg = c; h->device = c.device; h->num_sms = prop.multiProcessorCount;
+    for (auto& ev : h->ev) cudaEventCreate(&ev);
+    *out = h;
+    return KRD_OK;
+}
+
+void krd_destroy(krd_handle* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    free_masses(h);
+    cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
+    cudaFree(h->d_ws); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
+    for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    delete h;
+}
+
+const char* krd_last_error(const krd_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+krd_status krd_set_stream(krd_handle* h, void* cuda_stream)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    h->stream = static_cast<cudaStream_t>(cuda_stream);
+    return KRD_OK;
+}
+
+krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_node, const int32_t* child_node,
+                        const double* branch_length, int32_t root_node)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (n_edges < 0 || (n_edges > 0 && (!parent_node || !child_node || !branch_length)))
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad tree arguments");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    h->E = n_edges; h->root = root_node;
+    h->parent.assign(parent_node, parent_node + n_edges);
+    h->child.assign(child_node, child_node + n_edges);
+    h->bl.assign(branch_length, branch_length + n_edges);
+    h->have_tree = false; h->F_valid = false; h->have_masses = false;
+    krd_status st = build_tree(h);
+    if (st == KRD_OK) h->have_tree = true;
+    return st;
+}
+
+krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
+                          const double* pos, const double* mass)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    krd_status st = set_masses_common(h, n_samples, sample_off);
+    if (st != KRD_OK) return st;
+    const int64_t M = sample_off[n_samples];
+    if (M > 0 && (!edge || !pos || !mass)) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    free_masses(h);
+    h->N = n_samples; h->M = M;
+    const size_t Mx = (size_t)std::max<int64_t>(M, 1);
+    KRD_CUDA(h, cudaMalloc(&h->d_off, (size_t)(n_samples + 1) * 8));
+    KRD_CUDA(h, cudaMalloc(&h->d_owned[0], Mx * 4));
+    KRD_CUDA(h, cudaMalloc(&h->d_owned[1], Mx * 8));
+    KRD_CUDA(h, cudaMalloc(&h->d_owned[2], Mx * 8));
+    h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; h->d_mass = (double*)h->d_owned[2];
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_edge, edge, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_pos, pos, (size_t)M * 8, cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_mass, mass, (size_t)M * 8, cudaMemcpyHostToDevice, h->stream));
+    st = prepare_masses(h);
+    if (st != KRD_OK) return st;
+    h->have_masses = true;
+    h->stats.n_samples = n_samples; h->stats.n_edges = h->E; h->stats.n_masses = M;
+    return KRD_OK;
+}
+
+krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
+                                 const double* d_pos, const double* d_mass)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    krd_status st = set_masses_common(h, n_samples, sample_off);
+    if (st != KRD_OK) return st;
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    free_masses(h);
+    h->N = n_samples; h->M = sample_off[n_samples];
+    KRD_CUDA(h, cudaMalloc(&h->d_off, (size_t)(n_samples + 1) * 8));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    h->d_edge = const_cast<int32_t*>(d_edge); h->d_pos = const_cast<double*>(d_pos); h->d_mass = const_cast<double*>(d_mass);
+    st = prepare_masses(h);
+    if (st != KRD_OK) return st;
+    h->have_masses = true;
+    h->stats.n_samples = n_samples; h->stats.n_edges = h->E; h->stats.n_masses = h->M;
+    return KRD_OK;
+}
+
+static krd_status check_compute(krd_handle* h, double p, double divisor)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!(p > 0.0))  // also rejects NaN; genesis emd.cpp:186-190
+        return fail(h, KRD_ERR_INVALID_EXPONENT, "Invalid exponent value p for earth mover's distance calculation. Has to be > 0.0.");
+    if (!h->have_tree || !h->have_masses) return fail(h, KRD_ERR_STATE, "krd_set_tree and krd_set_masses must be called first");
+    if (divisor == 0.0 || divisor != divisor) return fail(h, KRD_ERR_INVALID_ARGUMENT, "divisor must be a non-zero number");
+    return KRD_OK;
+}
+
+static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed)
+{
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    h->stats.launches = 0;
+    cudaEventRecord(h->ev[0], h->stream);
+    if (!h->F_valid) {
+        krd_status st = build_F(h);
+        if (st != KRD_OK) return st;
+        h->stats.launches += h->stats.levels;
+    }
+    cudaEventRecord(h->ev[1], h->stream);
+    krd_status st = run_pairs(h, p, divisor, rank, world, d_out, d_packed);
+    if (st != KRD_OK) return st;
+    cudaEventRecord(h->ev[2], h->stream);
+    return KRD_OK;
+}
+
+krd_status krd_compute_device(krd_handle* h, double p, double divisor, double* d_out)
+{
+    krd_status st = check_compute(h, p, divisor);
+    if (st != KRD_OK) return st;
+    if (!d_out && h->N > 0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    if (h->N == 0) return KRD_OK;
+    return compute_impl(h, p, divisor, 0, 1, d_out, nullptr);
+}
+
+krd_status krd_compute(krd_handle* h, double p, double divisor, double* out)
+{
+    krd_status st = check_compute(h, p, divisor);
+    if (st != KRD_OK) return st;
+    if (h->N == 0) return KRD_OK;
+    if (!out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    const size_t bytes = (size_t)h->N * h->N * 8;
+    if (bytes > h->out_tmp_capacity) {
+        cudaFree(h->d_out_tmp); h->d_out_tmp = nullptr; h->out_tmp_capacity = 0;
+        KRD_CUDA(h, cudaMalloc(&h->d_out_tmp, bytes));
+        h->out_tmp_capacity = bytes;
+    }
+    st = compute_impl(h, p, divisor, 0, 1, h->d_out_tmp, nullptr);
+    if (st != KRD_OK) return st;
+    KRD_CUDA(h, cudaMemcpyAsync(out, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    return KRD_OK;
+}
+
+int64_t krd_shard_doubles(const krd_handle* h, int32_t world)
+{
+    if (!h || world < 1 || !h->have_masses) return -1;
+    const int64_t T = h->ld / TILE;
+    return tiles_per_rank(T * (T + 1) / 2, world) * TILE * TILE;
+}
+
+krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t rank, int32_t world, double* d_packed)
+{
+    krd_status st = check_compute(h, p, divisor);
+    if (st != KRD_OK) return st;
+    if (world < 1 || rank < 0 || rank >= world) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad rank/world");
+    if (!d_packed) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    return compute_impl(h, p, divisor, rank, world, nullptr, d_packed);
+}
+
+krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
+    if (world < 1 || !d_gathered || !d_out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad arguments");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    return unpack_shards(h, world, d_gathered, d_out);
+}
+
+krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
+{
+    if (!hc || !out) return KRD_ERR_INVALID_ARGUMENT;
+    krd_handle* h = const_cast<krd_handle*>(hc);
+    cudaSetDevice(h->device);
+    if (h->ev[2] && cudaEventQuery(h->ev[2]) == cudaSuccess && h->stats.launches > 0) {
+        cudaEventElapsedTime(&h->stats.ms_build, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&h->stats.ms_pairs, h->ev[1], h->ev[2]);
+    }
+    cudaGetLastError();
+    *out = h->stats;
+    return KRD_OK;
+}
+
+krd_status krd_debug_copy_F(krd_handle* h, double* out_F, double* out_len)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    if (!h->F_valid) { krd_status st = build_F(h); if (st != KRD_OK) return st; }
+    if (out_F) KRD_CUDA(h, cudaMemcpyAsync(out_F, h->d_F, (size_t)h->S * h->ld * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (out_len) KRD_CUDA(h, cudaMemcpyAsync(out_len, h->d_len, (size_t)h->S * 8, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    return KRD_OK;
+}
+
+void* krd_host_alloc(int64_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMallocHost(&p, (size_t)std::max<int64_t>(bytes, 1)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void krd_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+}  // extern "C"

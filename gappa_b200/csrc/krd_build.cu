@@ -1,0 +1,451 @@
+// K0 (mass -> segment slot, segment table) and K1 (dense cumulative subtree-mass matrix F).
+//
+// What the reference does once PER PAIR — a postorder walk that carries subtree mass through
+// node_masses[] and sweeps every edge distal -> proximal (genesis tree/mass_tree/emd.cpp:89-167) —
+// is done here once PER SAMPLE, level by level, and stored densely:
+//     F[s][i] = mass of sample i strictly below segment s
+//             = M_i(child_node(e)) + sum of sample i's masses on e at positions above segment s.
+// The pair kernel (krd_pairs.cu) then only needs  sum_s len[s] * |F[s][i] - F[s][j]|^p.
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <cmath>
+
+#include "krd_common.cuh"
+
+namespace krd {
+
+// ------------------------------------------------------------------------------------------------
+//  Tree preprocessing (host): validate, levels, child-edge lists
+// ------------------------------------------------------------------------------------------------
+
+krd_status build_tree(krd_handle* h)
+{
+    const int E = h->E, n_nodes = E + 1;
+    if (h->root < 0 || h->root >= n_nodes) return fail(h, KRD_ERR_INVALID_ARGUMENT, "root_node out of range");
+    std::vector<int> up(n_nodes, -1);        // edge above each node
+    std::vector<int> kcnt(n_nodes + 1, 0);
+    for (int e = 0; e < E; ++e) {
+        int p = h->parent[e], c = h->child[e];
+        if (p < 0 || p >= n_nodes || c < 0 || c >= n_nodes || p == c)
+            return fail(h, KRD_ERR_INVALID_ARGUMENT, "edge endpoints out of range");
+        if (up[c] != -1 || c == h->root)
+            return fail(h, KRD_ERR_INCOMPATIBLE_TREES, "Incompatible MassTrees.");
+        up[c] = e;
+        kcnt[p + 1]++;
+    }
+    for (int n = 0; n < n_nodes; ++n) kcnt[n + 1] += kcnt[n];
+    std::vector<int> kids(E > 0 ? E : 1), fill(kcnt.begin(), kcnt.end() - 1);
+    for (int e = 0; e < E; ++e) kids[fill[h->parent[e]]++] = e;   // listing order = child order
+
+    // BFS from the root gives a top-down node order; reversed it is bottom-up.
+    std::vector<int> order; order.reserve(n_nodes);
+    order.push_back(h->root);
+    for (size_t q = 0; q < order.size(); ++q) {
+        int n = order[q];
+        for (int k = kcnt[n]; k < kcnt[n + 1]; ++k) order.push_back(h->child[kids[k]]);
+    }
+    if ((int)order.size() != n_nodes)  // unreachable nodes <=> cycle / forest
+        return fail(h, KRD_ERR_INCOMPATIBLE_TREES, "Incompatible MassTrees.");
+    std::vector<int> height(n_nodes, 0);
+    int max_h = 0;
+    for (int q = n_nodes - 1; q > 0; --q) {
+        int n = order[q], pn = h->parent[up[n]];
+        height[pn] = std::max(height[pn], height[n] + 1);
+    }
+    for (int e = 0; e < E; ++e) max_h = std::max(max_h, height[h->child[e]]);
+    const int L = (E > 0) ? max_h + 1 : 0;
+    h->lvl_off.assign(L + 1, 0);
+    for (int e = 0; e < E; ++e) h->lvl_off[height[h->child[e]] + 1]++;
+    for (int l = 0; l < L; ++l) h->lvl_off[l + 1] += h->lvl_off[l];
+    std::vector<int> lvl_edges(E > 0 ? E : 1), lf(h->lvl_off.begin(), h->lvl_off.end() - (L > 0 ? 1 : 0));
+    for (int e = 0; e < E; ++e) lvl_edges[lf[height[h->child[e]]]++] = e;
+
+    std::vector<int> kid_off(E + 1, 0), kid_edge(E > 0 ? E : 1);
+    for (int e = 0; e < E; ++e) {
+        int c = h->child[e];
+        kid_off[e + 1] = kid_off[e] + (kcnt[c + 1] - kcnt[c]);
+        std::copy(kids.begin() + kcnt[c], kids.begin() + kcnt[c + 1], kid_edge.begin() + kid_off[e]);
+    }
+
+    cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    h->d_lvl_edges = h->d_kid_off = h->d_kid_edge = nullptr; h->d_bl = nullptr;
+    size_t ne = (size_t)std::max(E, 1);
+    KRD_CUDA(h, cudaMalloc(&h->d_lvl_edges, ne * sizeof(int)));
+    KRD_CUDA(h, cudaMalloc(&h->d_kid_off, (ne + 1) * sizeof(int)));
+    KRD_CUDA(h, cudaMalloc(&h->d_kid_edge, ne * sizeof(int)));
+    KRD_CUDA(h, cudaMalloc(&h->d_bl, ne * sizeof(double)));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_lvl_edges, lvl_edges.data(), (size_t)E * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_kid_off, kid_off.data(), (size_t)(E + 1) * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_kid_edge, kid_edge.data(), (size_t)E * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_bl, h->bl.data(), (size_t)E * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));  // host vectors above go out of scope
+    h->stats.levels = L;
+    return KRD_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+//  K0: canonical order, slots, segment table
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ int sample_of(const int64_t* __restrict__ off, int n, int64_t m)
+{
+    int lo = 0, hi = n;  // largest i with off[i] <= m
+    while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (off[mid] <= m) lo = mid; else hi = mid; }
+    return lo;
+}
+
+__global__ void k_sample_ids(const int64_t* __restrict__ off, int n, int64_t M, uint32_t* __restrict__ sid)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < M) sid[m] = (uint32_t)sample_of(off, n, m);
+}
+
+// flags[0] |= 1 if some sample is not sorted by (edge asc, pos asc); |= 2 if an edge id is invalid
+__global__ void k_check_canonical(const uint32_t* __restrict__ sid, const int32_t* __restrict__ edge,
+                                  const double* __restrict__ pos, int64_t M, int E, int* __restrict__ flags)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    int e = edge[m];
+    if (e < 0 || e >= E) { atomicOr(flags, 2); return; }
+    if (m > 0 && sid[m - 1] == sid[m]) {
+        int ep = edge[m - 1];
+        if (ep > e || (ep == e && !(pos[m - 1] <= pos[m]))) atomicOr(flags, 1);
+    }
+}
+
+__global__ void k_iota(uint32_t* a, int64_t M)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < M) a[m] = (uint32_t)m;
+}
+
+template <typename T, typename U>
+__global__ void k_gather(const T* __restrict__ src, const uint32_t* __restrict__ idx, int64_t M, U* __restrict__ dst)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < M) dst[m] = (U)src[idx[m]];
+}
+
+// mass_tree_binify_masses' bin index (genesis tree/mass_tree/functions.cpp:231-237), same
+// operation order: pn = min(max(0, pos / bl * nb), nextafter(nb, 0)); q = floor(pn).
+// std::max(0.0, v) returns 0.0 unless 0.0 < v (so NaN -> 0.0); std::min(pn, hi) returns pn unless hi < pn.
+__global__ void k_slots_binned(const int32_t* __restrict__ edge, const double* __restrict__ pos,
+                               const double* __restrict__ bl, int64_t M, double nb, double nb_below,
+                               int32_t* __restrict__ slot)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    double v = __dmul_rn(__ddiv_rn(pos[m], bl[edge[m]]), nb);
+    double pn = (0.0 < v) ? v : 0.0;
+    pn = (nb_below < pn) ? nb_below : pn;
+    slot[m] = (int32_t)floor(pn);
+}
+
+// Segment table of the binned mode: edge e owns segments e*(B+1)+t, t = 0..B, bounded by the bin
+// centres c_q = q*bl/nb + bl/nb/2 (functions.cpp:240): [0,c_0], (c_0,c_1], ..., (c_{B-1}, bl].
+__global__ void k_len_binned(const double* __restrict__ bl, int E, int B, double* __restrict__ len,
+                             int32_t* __restrict__ seg_off)
+{
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > (int64_t)E * (B + 1)) return;
+    if (g <= E) seg_off[g] = (int32_t)(g * (B + 1));
+    if (g == (int64_t)E * (B + 1)) return;
+    int e = (int)(g / (B + 1)), t = (int)(g % (B + 1));
+    double b = bl[e], nb = (double)B;
+    double hi = (t == B) ? b : __dadd_rn(__ddiv_rn(__dmul_rn((double)t, b), nb), __ddiv_rn(__ddiv_rn(b, nb), 2.0));
+    double lo = (t == 0) ? 0.0 : __dadd_rn(__ddiv_rn(__dmul_rn((double)(t - 1), b), nb), __ddiv_rn(__ddiv_rn(b, nb), 2.0));
+    len[g] = hi - lo;
+}
+
+// ---- exact mode -------------------------------------------------------------------------------
+
+__global__ void k_heads(const uint32_t* __restrict__ sedge, const uint32_t* __restrict__ perm,
+                        const double* __restrict__ pos, int64_t M, uint32_t* __restrict__ head)
+{
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    uint32_t hd = 1;
+    if (k > 0 && sedge[k] == sedge[k - 1] && pos[perm[k]] == pos[perm[k - 1]]) hd = 0;
+    head[k] = hd;
+}
+
+__global__ void k_unique_scatter(const uint32_t* __restrict__ sedge, const uint32_t* __restrict__ perm,
+                                 const double* __restrict__ pos, const uint32_t* __restrict__ head,
+                                 const uint32_t* __restrict__ rank, int64_t M,
+                                 uint32_t* __restrict__ uidx, double* __restrict__ upos,
+                                 uint32_t* __restrict__ uedge, uint32_t* __restrict__ cnt)
+{
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    uint32_t u = rank[k] - 1, m = perm[k];
+    uidx[m] = u;
+    if (head[k]) { upos[u] = pos[m]; uedge[u] = sedge[k]; atomicAdd(&cnt[sedge[k]], 1u); }
+}
+
+__global__ void k_exact_slots(const int32_t* __restrict__ edge, const uint32_t* __restrict__ uidx,
+                              const uint32_t* __restrict__ ubase, int64_t M, int32_t* __restrict__ slot)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < M) slot[m] = (int32_t)(uidx[m] - ubase[edge[m]]);
+}
+
+// Segment t of edge e (k_e distinct positions b_1<..<b_k): t<k: (b_t, b_{t+1}] (b_0 = 0); t=k: (b_k, bl].
+// Lengths are the same differences genesis forms while walking (emd.cpp:154-166).
+__global__ void k_exact_len_unique(const double* __restrict__ upos, const uint32_t* __restrict__ uedge,
+                                   const uint32_t* __restrict__ ubase, int64_t U, double* __restrict__ len)
+{
+    int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= U) return;
+    uint32_t e = uedge[u], r = (uint32_t)u - ubase[e];
+    double lo = (r > 0) ? upos[u - 1] : 0.0;
+    len[(int64_t)ubase[e] + e + r] = upos[u] - lo;
+}
+
+__global__ void k_exact_len_last(const double* __restrict__ upos, const uint32_t* __restrict__ ubase,
+                                 const double* __restrict__ bl, int E, double* __restrict__ len,
+                                 int32_t* __restrict__ seg_off)
+{
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e > E) return;
+    seg_off[e] = (int32_t)(ubase[e] + e);
+    if (e == E) return;
+    uint32_t k = ubase[e + 1] - ubase[e];
+    len[(int64_t)ubase[e] + e + k] = (k > 0) ? bl[e] - upos[ubase[e] + k - 1] : bl[e];
+}
+
+__global__ void k_sqrt(const double* __restrict__ a, int64_t n, double* __restrict__ b)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) b[i] = sqrt(a[i]);
+}
+
+static inline unsigned nblk(int64_t n, int bs = 256) { return (unsigned)((n + bs - 1) / bs); }
+
+struct DevBuf {  // scoped device scratch
+    void* p = nullptr;
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+    ~DevBuf() { if (p) cudaFree(p); }
+    template <typename T> T* as() { return static_cast<T*>(p); }
+};
+
+static int bits_for(uint32_t max_value) { int b = 1; while (b < 32 && (max_value >> b)) ++b; return b; }
+
+// stable sort of `perm` by 32-bit keys gathered through perm: perm_out[k] ordered by key[perm[..]]
+template <typename SrcT>
+static krd_status stable_pass_u32(krd_handle* h, const SrcT* d_src, uint32_t max_key, int64_t M,
+                                  uint32_t* perm_in, uint32_t* perm_out, uint32_t* keys_sorted_out)
+{
+    DevBuf kin, tmp;
+    KRD_CUDA(h, kin.alloc((size_t)M * 4));
+    k_gather<SrcT, uint32_t><<<nblk(M), 256, 0, h->stream>>>(d_src, perm_in, M, kin.as<uint32_t>());
+    size_t bytes = 0;
+    KRD_CUDA(h, cub::DeviceRadixSort::SortPairs(nullptr, bytes, kin.as<uint32_t>(), keys_sorted_out, perm_in, perm_out, M, 0, bits_for(max_key), h->stream));
+    KRD_CUDA(h, tmp.alloc(bytes));
+    KRD_CUDA(h, cub::DeviceRadixSort::SortPairs(tmp.p, bytes, kin.as<uint32_t>(), keys_sorted_out, perm_in, perm_out, M, 0, bits_for(max_key), h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    return KRD_OK;
+}
+
+// perm sorted by (edge asc, pos asc), stable in the input index; sedge = edge keys in that order
+static krd_status sort_edge_pos(krd_handle* h, uint32_t* perm /*M*/, uint32_t* sedge /*M*/)
+{
+    const int64_t M = h->M;
+    DevBuf iota, pos_sorted, p1, tmp;
+    KRD_CUDA(h, iota.alloc((size_t)M * 4));
+    KRD_CUDA(h, pos_sorted.alloc((size_t)M * 8));
+    KRD_CUDA(h, p1.alloc((size_t)M * 4));
+    k_iota<<<nblk(M), 256, 0, h->stream>>>(iota.as<uint32_t>(), M);
+    size_t bytes = 0;
+    KRD_CUDA(h, cub::DeviceRadixSort::SortPairs(nullptr, bytes, h->d_pos, pos_sorted.as<double>(), iota.as<uint32_t>(), p1.as<uint32_t>(), M, 0, 64, h->stream));
+    KRD_CUDA(h, tmp.alloc(bytes));
+    KRD_CUDA(h, cub::DeviceRadixSort::SortPairs(tmp.p, bytes, h->d_pos, pos_sorted.as<double>(), iota.as<uint32_t>(), p1.as<uint32_t>(), M, 0, 64, h->stream));
+    return stable_pass_u32<int32_t>(h, h->d_edge, (uint32_t)std::max(h->E - 1, 1), M, p1.as<uint32_t>(), perm, sedge);
+}
+
+krd_status prepare_masses(krd_handle* h)
+{
+    const int64_t M = h->M;
+    const int E = h->E, N = h->N;
+    h->F_valid = false;
+    if (M >= (int64_t)0xFFFFFFF0u) return fail(h, KRD_ERR_INVALID_ARGUMENT, "more than 2^32 masses are not supported");
+
+    // --- canonical order check (edge asc, pos asc per sample = MassTree iteration order) ---
+    DevBuf sid, flags;
+    KRD_CUDA(h, sid.alloc((size_t)M * 4));
+    KRD_CUDA(h, flags.alloc(sizeof(int)));
+    KRD_CUDA(h, cudaMemsetAsync(flags.p, 0, sizeof(int), h->stream));
+    if (M > 0) {
+        k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, sid.as<uint32_t>());
+        k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(sid.as<uint32_t>(), h->d_edge, h->d_pos, M, E, flags.as<int>());
+    }
+    int hflags = 0;
+    KRD_CUDA(h, cudaMemcpyAsync(&hflags, flags.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (hflags & 2) return fail(h, KRD_ERR_INVALID_ARGUMENT, "mass entry refers to an edge outside the tree");
+    if (hflags & 1) {
+        // sort by (sample, edge, pos), stable: three LSD passes, then gather into owned buffers
+        DevBuf perm2, sedge, perm3, skeys;
+        KRD_CUDA(h, perm2.alloc((size_t)M * 4)); KRD_CUDA(h, sedge.alloc((size_t)M * 4));
+        KRD_CUDA(h, perm3.alloc((size_t)M * 4)); KRD_CUDA(h, skeys.alloc((size_t)M * 4));
+        krd_status st = sort_edge_pos(h, perm2.as<uint32_t>(), sedge.as<uint32_t>());
+        if (st != KRD_OK) return st;
+        st = stable_pass_u32<uint32_t>(h, sid.as<uint32_t>(), (uint32_t)std::max(N - 1, 1), M, perm2.as<uint32_t>(), perm3.as<uint32_t>(), skeys.as<uint32_t>());
+        if (st != KRD_OK) return st;
+        int32_t* ne; double *np, *nm;
+        KRD_CUDA(h, cudaMalloc(&ne, (size_t)M * 4)); KRD_CUDA(h, cudaMalloc(&np, (size_t)M * 8)); KRD_CUDA(h, cudaMalloc(&nm, (size_t)M * 8));
+        k_gather<int32_t, int32_t><<<nblk(M), 256, 0, h->stream>>>(h->d_edge, perm3.as<uint32_t>(), M, ne);
+        k_gather<double, double><<<nblk(M), 256, 0, h->stream>>>(h->d_pos, perm3.as<uint32_t>(), M, np);
+        k_gather<double, double><<<nblk(M), 256, 0, h->stream>>>(h->d_mass, perm3.as<uint32_t>(), M, nm);
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        for (void* q : h->d_owned) if (q) cudaFree(q);
+        h->d_owned[0] = ne; h->d_owned[1] = np; h->d_owned[2] = nm;
+        h->d_edge = ne; h->d_pos = np; h->d_mass = nm;
+    }
+
+    cudaFree(h->d_slot); h->d_slot = nullptr;
+    cudaFree(h->d_seg_off); h->d_seg_off = nullptr;
+    cudaFree(h->d_len); h->d_len = nullptr;
+    cudaFree(h->d_sqrt_len); h->d_sqrt_len = nullptr;
+    KRD_CUDA(h, cudaMalloc(&h->d_slot, (size_t)std::max<int64_t>(M, 1) * 4));
+    KRD_CUDA(h, cudaMalloc(&h->d_seg_off, (size_t)(E + 1) * 4));
+
+    auto alloc_len = [&](int64_t S) -> krd_status {
+        h->S = S;
+        h->S_pad = ((S + KC - 1) / KC) * KC;
+        if (h->S_pad == 0) h->S_pad = KC;
+        KRD_CUDA(h, cudaMalloc(&h->d_len, (size_t)h->S_pad * 8));
+        KRD_CUDA(h, cudaMalloc(&h->d_sqrt_len, (size_t)h->S_pad * 8));
+        KRD_CUDA(h, cudaMemsetAsync(h->d_len, 0, (size_t)h->S_pad * 8, h->stream));
+        return KRD_OK;
+    };
+
+    if (h->cfg.bins > 0) {
+        const int B = h->cfg.bins;
+        if ((int64_t)E * (B + 1) > 0x7FFFFFF0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "too many segments");
+        krd_status st = alloc_len((int64_t)E * (B + 1));
+        if (st != KRD_OK) return st;
+        double nb = (double)B;
+        if (M > 0) k_slots_binned<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, h->d_pos, h->d_bl, M, nb, std::nextafter(nb, 0.0), h->d_slot);
+        k_len_binned<<<nblk((int64_t)E * (B + 1) + 1), 256, 0, h->stream>>>(h->d_bl, E, B, h->d_len, h->d_seg_off);
+    } else {
+        DevBuf perm, sedge, head, rank, uidx, upos, uedge, cnt, ubase, tmp;
+        const int64_t Mx = std::max<int64_t>(M, 1);
+        KRD_CUDA(h, perm.alloc(Mx * 4)); KRD_CUDA(h, sedge.alloc(Mx * 4)); KRD_CUDA(h, head.alloc(Mx * 4));
+        KRD_CUDA(h, rank.alloc(Mx * 4)); KRD_CUDA(h, uidx.alloc(Mx * 4)); KRD_CUDA(h, upos.alloc(Mx * 8));
+        KRD_CUDA(h, uedge.alloc(Mx * 4)); KRD_CUDA(h, cnt.alloc((size_t)(E + 1) * 4)); KRD_CUDA(h, ubase.alloc((size_t)(E + 1) * 4));
+        KRD_CUDA(h, cudaMemsetAsync(cnt.p, 0, (size_t)(E + 1) * 4, h->stream));
+        uint32_t U = 0;
+        if (M > 0) {
+            krd_status st = sort_edge_pos(h, perm.as<uint32_t>(), sedge.as<uint32_t>());
+            if (st != KRD_OK) return st;
+            k_heads<<<nblk(M), 256, 0, h->stream>>>(sedge.as<uint32_t>(), perm.as<uint32_t>(), h->d_pos, M, head.as<uint32_t>());
+            size_t bytes = 0;
+            KRD_CUDA(h, cub::DeviceScan::InclusiveSum(nullptr, bytes, head.as<uint32_t>(), rank.as<uint32_t>(), M, h->stream));
+            KRD_CUDA(h, tmp.alloc(bytes));
+            KRD_CUDA(h, cub::DeviceScan::InclusiveSum(tmp.p, bytes, head.as<uint32_t>(), rank.as<uint32_t>(), M, h->stream));
+            k_unique_scatter<<<nblk(M), 256, 0, h->stream>>>(sedge.as<uint32_t>(), perm.as<uint32_t>(), h->d_pos, head.as<uint32_t>(), rank.as<uint32_t>(), M,
+                                                             uidx.as<uint32_t>(), upos.as<double>(), uedge.as<uint32_t>(), cnt.as<uint32_t>());
+            KRD_CUDA(h, cudaMemcpyAsync(&U, rank.as<uint32_t>() + (M - 1), 4, cudaMemcpyDeviceToHost, h->stream));
+        }
+        {
+            DevBuf tmp2; size_t bytes = 0;
+            KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(nullptr, bytes, cnt.as<uint32_t>(), ubase.as<uint32_t>(), E + 1, h->stream));
+            KRD_CUDA(h, tmp2.alloc(bytes));
+            KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(tmp2.p, bytes, cnt.as<uint32_t>(), ubase.as<uint32_t>(), E + 1, h->stream));
+            KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        }
+        if ((int64_t)U + E > 0x7FFFFFF0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "too many segments");
+        krd_status st = alloc_len((int64_t)U + E);
+        if (st != KRD_OK) return st;
+        if (M > 0) {
+            k_exact_slots<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, uidx.as<uint32_t>(), ubase.as<uint32_t>(), M, h->d_slot);
+            k_exact_len_unique<<<nblk(U), 256, 0, h->stream>>>(upos.as<double>(), uedge.as<uint32_t>(), ubase.as<uint32_t>(), U, h->d_len);
+        }
+        k_exact_len_last<<<nblk(E + 1), 256, 0, h->stream>>>(upos.as<double>(), ubase.as<uint32_t>(), h->d_bl, E, h->d_len, h->d_seg_off);
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));  // scratch buffers die here
+    }
+    k_sqrt<<<nblk(h->S_pad), 256, 0, h->stream>>>(h->d_len, h->S_pad, h->d_sqrt_len);
+    KRD_CUDA(h, cudaGetLastError());
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+
+    h->ld = ((N + TILE - 1) / TILE) * TILE;
+    h->stats.n_segments = h->S;
+    h->stats.ld_samples = h->ld;
+    h->stats.f_bytes = (int64_t)h->S_pad * h->ld * 8;
+    return KRD_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+//  K1: level-synchronous postorder scan -> F[S_pad][ld]
+// ------------------------------------------------------------------------------------------------
+//
+// One thread per (edge e of the current level, sample i).  Levels are heights of the edge's child
+// node, so every child edge was finished by an earlier launch.  The thread
+//   1. starts from the subtree mass below e: sum over child edges c of F[seg_off[c]][i]
+//      (= mass at the proximal end of c; emd.cpp:145,167 node_masses[] without the array),
+//   2. walks e's segments distal -> proximal (emd.cpp:149-166), adding sample i's own masses
+//      when their slot is reached, and stores the running value — coalesced over i.
+// Threads with i >= N carry no masses and write the zero padding columns.
+__global__ void __launch_bounds__(128)
+k_build_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count,
+              const int32_t* __restrict__ kid_off, const int32_t* __restrict__ kid_edge,
+              const int32_t* __restrict__ seg_off, const int64_t* __restrict__ off,
+              const int32_t* __restrict__ edge, const int32_t* __restrict__ slot,
+              const double* __restrict__ mass, int N, int ld, double* __restrict__ F)
+{
+    const int i = blockIdx.y * blockDim.x + threadIdx.x;
+    if (i >= ld) return;
+    for (int le = blockIdx.x; le < lvl_count; le += gridDim.x) {
+        const int e = lvl_edges[lvl_begin + le];
+        double acc = 0.0;
+        for (int k = kid_off[e]; k < kid_off[e + 1]; ++k)
+            acc += F[(int64_t)seg_off[kid_edge[k]] * ld + i];
+        int64_t lo = 0, hi = 0;
+        if (i < N) {
+            // [lo,hi) = sample i's entries on edge e (entries are sorted by edge)
+            const int64_t b = off[i], t = off[i + 1];
+            int64_t l = b, r = t;
+            while (l < r) { int64_t m = (l + r) >> 1; if (edge[m] < e) l = m + 1; else r = m; }
+            lo = l; r = t;
+            while (l < r) { int64_t m = (l + r) >> 1; if (edge[m] <= e) l = m + 1; else r = m; }
+            hi = l;
+        }
+        const int s0 = seg_off[e], k_e = seg_off[e + 1] - s0 - 1;
+        int64_t mp = hi - 1;
+        for (int t = k_e; t >= 0; --t) {
+            while (mp >= lo && slot[mp] >= t) { acc += mass[mp]; --mp; }
+            F[(int64_t)(s0 + t) * ld + i] = acc;
+        }
+    }
+}
+
+krd_status build_F(krd_handle* h)
+{
+    const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
+    if (need > h->F_capacity) {
+        cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
+        KRD_CUDA(h, cudaMalloc(&h->d_F, need));
+        h->F_capacity = need;
+    }
+    // zero the padding rows [S, S_pad)
+    if (h->S_pad > h->S)
+        KRD_CUDA(h, cudaMemsetAsync(h->d_F + (size_t)h->S * h->ld, 0, (size_t)(h->S_pad - h->S) * h->ld * 8, h->stream));
+    const int L = (int)h->lvl_off.size() - 1;
+    dim3 block(128);
+    for (int l = 0; l < L; ++l) {
+        int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
+        dim3 grid((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ld / 128));
+        k_build_level<<<grid, block, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge,
+                                                     h->d_seg_off, h->d_off, h->d_edge, h->d_slot, h->d_mass,
+                                                     h->N, h->ld, h->d_F);
+    }
+    KRD_CUDA(h, cudaGetLastError());
+    h->F_valid = true;
+    return KRD_OK;
+}
+
+}  // namespace krd

@@ -1,0 +1,103 @@
+// Shared internals of libkrd_b200.so (sm_100a only).  See include/krd_b200.h for the C ABI and
+// DESIGN.md for the data layout.  Reference semantics: genesis tree/mass_tree/emd.cpp:60-235.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/krd_b200.h"
+
+namespace krd {
+
+constexpr int TILE = 128;  // samples per tile edge (pair kernel CTA tile is TILE x TILE)
+constexpr int KC   = 16;   // segments per pipeline stage
+constexpr int NUM_SMS_FALLBACK = 148;
+
+enum PairMode : int {
+    MODE_P1 = 0,      // p == 1      : acc += len * |a-b|
+    MODE_P2 = 1,      // p == 2      : acc += (sqrt(len)*(a-b))^2   (direct, FP64 cores)
+    MODE_PHALF = 2,   // p == 0.5    : acc += len * sqrt(|a-b|)
+    MODE_GENERIC = 3  // any p > 0   : acc += len * |a-b|^p
+};
+
+struct Tile { int32_t i, j; };  // tile-block coordinates, i <= j
+
+}  // namespace krd
+
+struct krd_handle {
+    krd_config cfg{};
+    int device = 0;
+    int num_sms = krd::NUM_SMS_FALLBACK;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // ---- tree (host copies + device arrays) ----
+    int32_t E = 0, root = 0;
+    bool have_tree = false;
+    std::vector<int32_t> parent, child;
+    std::vector<double> bl;
+    std::vector<int32_t> lvl_off;     // host: edges of level L are lvl_edges[lvl_off[L]..lvl_off[L+1])
+    int32_t* d_lvl_edges = nullptr;   // edges sorted by level (level = height of the child node)
+    int32_t* d_kid_off = nullptr;     // E+1: child edges of edge e's child node
+    int32_t* d_kid_edge = nullptr;
+    double*  d_bl = nullptr;
+
+    // ---- masses ----
+    int32_t N = 0;
+    int64_t M = 0;
+    bool have_masses = false;
+    bool owns_masses = false;
+    int64_t* d_off = nullptr;   // N+1
+    int32_t* d_edge = nullptr;  // M
+    double*  d_pos = nullptr;   // M
+    double*  d_mass = nullptr;  // M
+    int32_t* d_slot = nullptr;  // M: segment index within the edge that receives this mass
+    void*    d_owned[3] = {nullptr, nullptr, nullptr};  // edge/pos/mass buffers we allocated
+
+    // ---- segments + dense matrix ----
+    int64_t S = 0, S_pad = 0;
+    int32_t ld = 0;              // padded sample count (multiple of TILE)
+    int32_t* d_seg_off = nullptr;  // E+1
+    double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
+    double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
+    double*  d_F = nullptr;        // S_pad x ld, row = segment, N contiguous
+    size_t   F_capacity = 0;
+    bool F_valid = false;
+
+    // ---- pair kernel workspace ----
+    double* d_ws = nullptr;
+    size_t  ws_capacity = 0;
+    krd::Tile* d_tiles = nullptr;
+    int64_t n_tiles_alloc = 0;
+    double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
+    size_t  out_tmp_capacity = 0;
+
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    krd_stats stats{};
+};
+
+namespace krd {
+
+krd_status fail(krd_handle* h, krd_status st, const std::string& msg);
+krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what);
+
+#define KRD_CUDA(h, call)                                              \
+    do {                                                               \
+        cudaError_t _e = (call);                                       \
+        if (_e != cudaSuccess) return krd::cuda_fail((h), _e, #call);  \
+    } while (0)
+
+// krd_build.cu
+krd_status build_tree(krd_handle* h);                 // host preprocessing + upload
+krd_status prepare_masses(krd_handle* h);             // canonical order, slots, segment table
+krd_status build_F(krd_handle* h);                    // K1
+
+// krd_pairs.cu
+krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
+                     double* d_out_matrix, double* d_out_packed);
+krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
+int64_t tiles_per_rank(int64_t n_tiles, int world);
+
+}  // namespace krd

@@ -1,0 +1,227 @@
+"""ctypes binding of libkrd_b200.so (the C ABI in include/krd_b200.h) plus a thin host-side mirror
+of the reference operator
+
+    genesis::tree::earth_movers_distance(std::vector<MassTree> const&, double p)
+        libs/genesis/lib/genesis/tree/mass_tree/emd.hpp:124, emd.cpp:183-235
+
+There is NO CPU fallback: if the CUDA library is missing or no B200 is visible, every entry point
+raises.  Nothing under oracle/ is imported here.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkrd_b200.so")
+
+KRD_OK = 0
+KRD_ERR_INVALID_EXPONENT = 1
+KRD_ERR_INCOMPATIBLE_TREES = 2
+KRD_ERR_TOO_FEW_SAMPLES = 3
+KRD_ERR_INVALID_ARGUMENT = 4
+KRD_ERR_CUDA = 5
+KRD_ERR_STATE = 6
+KRD_ERR_NO_DEVICE = 7
+
+EXPORTS = [
+    "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
+    "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
+    "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
+    "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+]
+
+
+class KrdConfig(C.Structure):
+    _fields_ = [("device", C.c_int), ("bins", C.c_int), ("split", C.c_int), ("reserved", C.c_int * 5)]
+
+
+class KrdStats(C.Structure):
+    _fields_ = [("n_samples", C.c_int64), ("n_edges", C.c_int64), ("n_masses", C.c_int64),
+                ("n_segments", C.c_int64), ("ld_samples", C.c_int64), ("f_bytes", C.c_int64),
+                ("n_tiles", C.c_int64), ("split", C.c_int32), ("pair_ctas", C.c_int32),
+                ("levels", C.c_int32), ("launches", C.c_int32), ("ms_build", C.c_float),
+                ("ms_pairs", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class KrdError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(message)
+        self.status = status
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fails loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). gappa_b200 has no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    L.krd_create.restype = C.c_int
+    L.krd_create.argtypes = [C.POINTER(KrdConfig), C.POINTER(vp)]
+    L.krd_destroy.restype = None
+    L.krd_destroy.argtypes = [vp]
+    L.krd_last_error.restype = C.c_char_p
+    L.krd_last_error.argtypes = [vp]
+    L.krd_set_stream.restype = C.c_int
+    L.krd_set_stream.argtypes = [vp, vp]
+    L.krd_set_tree.restype = C.c_int
+    L.krd_set_tree.argtypes = [vp, i32, vp, vp, vp, i32]
+    L.krd_set_masses.restype = C.c_int
+    L.krd_set_masses.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.krd_set_masses_device.restype = C.c_int
+    L.krd_set_masses_device.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.krd_compute.restype = C.c_int
+    L.krd_compute.argtypes = [vp, dbl, dbl, vp]
+    L.krd_compute_device.restype = C.c_int
+    L.krd_compute_device.argtypes = [vp, dbl, dbl, vp]
+    L.krd_shard_doubles.restype = i64
+    L.krd_shard_doubles.argtypes = [vp, i32]
+    L.krd_compute_shard.restype = C.c_int
+    L.krd_compute_shard.argtypes = [vp, dbl, dbl, i32, i32, vp]
+    L.krd_unpack_shards.restype = C.c_int
+    L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
+    L.krd_get_stats.restype = C.c_int
+    L.krd_get_stats.argtypes = [vp, C.POINTER(KrdStats)]
+    L.krd_debug_copy_F.restype = C.c_int
+    L.krd_debug_copy_F.argtypes = [vp, vp, vp]
+    L.krd_host_alloc.restype = vp
+    L.krd_host_alloc.argtypes = [i64]
+    L.krd_host_free.restype = None
+    L.krd_host_free.argtypes = [vp]
+    L.krd_measure_fp64_peak.restype = dbl
+    L.krd_measure_fp64_peak.argtypes = [C.c_int, C.c_int, dbl]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    """Raw address of a numpy array / torch tensor / int."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+class KrdPlan:
+    """One handle of the C ABI: tree + masses resident in HBM, distance matrices on demand."""
+
+    def __init__(self, device=0, bins=0, split=0):
+        self._L = lib()
+        self._h = C.c_void_p()
+        cfg = KrdConfig(device=device, bins=bins, split=split)
+        st = self._L.krd_create(C.byref(cfg), C.byref(self._h))
+        if st != KRD_OK:
+            raise KrdError(st, self._L.krd_last_error(None).decode())
+        self.device = device
+        self.bins = bins
+        self.n_samples = 0
+        self._keep = []
+
+    def _check(self, st):
+        if st != KRD_OK:
+            raise KrdError(st, self._L.krd_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            self._L.krd_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream):
+        self._check(self._L.krd_set_stream(self._h, cuda_stream))
+
+    def set_tree(self, parent, child, branch_length, root):
+        parent = np.ascontiguousarray(parent, np.int32)
+        child = np.ascontiguousarray(child, np.int32)
+        bl = np.ascontiguousarray(branch_length, np.float64)
+        self._check(self._L.krd_set_tree(self._h, len(bl), _ptr(parent), _ptr(child), _ptr(bl), int(root)))
+
+    def set_masses(self, off, edge, pos, mass):
+        """HOST arrays (numpy, or pinned CPU torch tensors of the right dtype)."""
+        if isinstance(off, np.ndarray) or isinstance(off, (list, tuple)):
+            off = np.ascontiguousarray(off, np.int64)
+        if isinstance(edge, np.ndarray):
+            edge = np.ascontiguousarray(edge, np.int32)
+            pos = np.ascontiguousarray(pos, np.float64)
+            mass = np.ascontiguousarray(mass, np.float64)
+        n = len(off) - 1
+        self._check(self._L.krd_set_masses(self._h, n, _ptr(off), _ptr(edge), _ptr(pos), _ptr(mass)))
+        self.n_samples = n
+
+    def set_masses_device(self, off, d_edge, d_pos, d_mass):
+        """off: host int64; the rest are CUDA tensors that must outlive the plan's use of them."""
+        off = np.ascontiguousarray(off, np.int64)
+        n = len(off) - 1
+        self._keep = [d_edge, d_pos, d_mass]
+        self._check(self._L.krd_set_masses_device(self._h, n, _ptr(off), _ptr(d_edge), _ptr(d_pos), _ptr(d_mass)))
+        self.n_samples = n
+
+    def compute(self, p=1.0, divisor=1.0, out=None):
+        """Host result (numpy n x n)."""
+        n = self.n_samples
+        if out is None:
+            out = np.zeros((n, n), np.float64)
+        self._check(self._L.krd_compute(self._h, float(p), float(divisor), _ptr(out)))
+        return out
+
+    def compute_device(self, d_out, p=1.0, divisor=1.0):
+        self._check(self._L.krd_compute_device(self._h, float(p), float(divisor), _ptr(d_out)))
+        return d_out
+
+    def shard_doubles(self, world):
+        return int(self._L.krd_shard_doubles(self._h, world))
+
+    def compute_shard(self, d_packed, rank, world, p=1.0, divisor=1.0):
+        self._check(self._L.krd_compute_shard(self._h, float(p), float(divisor), rank, world, _ptr(d_packed)))
+
+    def unpack_shards(self, d_gathered, d_out, world):
+        self._check(self._L.krd_unpack_shards(self._h, world, _ptr(d_gathered), _ptr(d_out)))
+
+    def stats(self):
+        s = KrdStats()
+        self._check(self._L.krd_get_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    def debug_F(self):
+        s = self.stats()
+        F = np.zeros((s["n_segments"], s["ld_samples"]), np.float64)
+        ln = np.zeros(s["n_segments"], np.float64)
+        self._check(self._L.krd_debug_copy_F(self._h, _ptr(F), _ptr(ln)))
+        return F, ln
+
+
+def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):
+    """Mirror of genesis `earth_movers_distance(std::vector<MassTree> const&, double p)`
+    (tree/mass_tree/emd.cpp:183-235) on the flat data model:
+    tree = dict(parent, child, bl, root); masses = dict(off, edge, pos, mass).
+    Raises KrdError with the reference's message for p <= 0 (emd.cpp:186-190)."""
+    plan = KrdPlan(device=device, bins=bins)
+    try:
+        plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+        plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
+        return plan.compute(p=p, divisor=divisor)
+    finally:
+        plan.close()
+
+
+def measure_fp64_peak(device=0, mode=0, ms=200.0):
+    return float(lib().krd_measure_fp64_peak(device, mode, ms))

@@ -1,0 +1,212 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on
+the same seeded inputs and against the committed golden fixtures of the compiled reference.
+Tolerance: 1e-10 relative (BASELINE.json north_star, FP64)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def gb():
+    import gappa_b200
+    return gappa_b200
+
+
+def dense_F_numpy(tree, mass_canon, seg_off, slot_of):
+    """Plain restatement of F for small cases: F[s][i] = subtree mass below + own masses at slots >= t."""
+    E = len(tree["bl"])
+    n = len(mass_canon["off"]) - 1
+    S = seg_off[-1]
+    F = np.zeros((S, n))
+    kids = [[] for _ in range(E + 1)]
+    for e in range(E):
+        kids[tree["parent"][e]].append(e)
+    import oracle
+    order = np.zeros(E, np.int32)
+    oracle.port().okrd_postorder(E, np.ascontiguousarray(tree["parent"], np.int32),
+                                 np.ascontiguousarray(tree["child"], np.int32), int(tree["root"]), order)
+    for i in range(n):
+        lo, hi = mass_canon["off"][i], mass_canon["off"][i + 1]
+        per_edge = {}
+        for m in range(lo, hi):
+            per_edge.setdefault(int(mass_canon["edge"][m]), []).append(m)
+        top = np.zeros(E)
+        for e in order:
+            acc = sum(top[c] for c in kids[tree["child"][e]])
+            k = seg_off[e + 1] - seg_off[e] - 1
+            ms = per_edge.get(int(e), [])
+            mp = len(ms) - 1
+            for t in range(k, -1, -1):
+                while mp >= 0 and slot_of(ms[mp]) >= t:
+                    acc += mass_canon["mass"][ms[mp]]
+                    mp -= 1
+                F[seg_off[e] + t, i] = acc
+            top[e] = acc
+    return F
+
+
+def test_golden_test_ab(gb):
+    tree, mass, z = load_golden("test_ab.npz")
+    for p in (1.0, 2.0, 0.5):
+        got = gb.earth_movers_distance(tree, mass, p=p)
+        assert rel_err(got, z[f"m_p{p}"]) <= TOL
+        assert got[0, 0] == 0.0 and got[0, 1] == got[1, 0]
+    assert np.float32(gb.earth_movers_distance(tree, mass, p=1.0)[0, 1]) == np.float32(2.8458333)
+
+
+@pytest.mark.parametrize("p", [1.0, 2.0, 0.5])
+def test_golden_cfg1_exact_mode(gb, p):
+    tree, mass, z = load_golden("cfg1.npz")
+    plan = gb.KrdPlan(bins=0)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    got = plan.compute(p=p)
+    assert rel_err(got, z[f"m_p{p}"]) <= TOL
+    assert np.array_equal(got, got.T) and np.all(np.diag(got) == 0)
+    # --normalize: krd.cpp:144-150 divides by the diameter
+    dia = float(z["diameter"])
+    assert rel_err(plan.compute(p=p, divisor=dia), z[f"m_p{p}"] / dia) <= TOL
+    st = plan.stats()
+    assert st["n_samples"] == 30 and st["n_edges"] == 597 and st["n_segments"] > 597
+    plan.close()
+
+
+def test_golden_cfg1_point_mass(gb):
+    tree, mass, z = load_golden("cfg1_pm.npz")
+    assert rel_err(gb.earth_movers_distance(tree, mass, p=1.0), z["m_p1.0"]) <= TOL
+
+
+@pytest.mark.parametrize("bins", [0, 1, 4])
+@pytest.mark.parametrize("p", [1.0, 2.0, 0.5, 1.7])
+def test_golden_synth_small(gb, bins, p):
+    tree, mass, z = load_golden("synth_small.npz")
+    assert rel_err(gb.earth_movers_distance(tree, mass, p=p, bins=bins), z[f"m_b{bins}_p{p}"]) <= TOL
+
+
+def test_F_matrix_matches_restatement_binned(gb, oracle_mod):
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(61, seed=5)
+    mass = synth.sample_masses(tree, 9, 120, seed=5)
+    B = 3
+    plan = gb.KrdPlan(bins=B)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    F, ln = plan.debug_F()
+    E = len(tree["bl"])
+    seg_off = np.arange(E + 1) * (B + 1)
+    L = oracle_mod.port()
+    slot = [L.okrd_bin_index(float(mass["pos"][m]), float(tree["bl"][mass["edge"][m]]), B) for m in range(len(mass["pos"]))]
+    want = dense_F_numpy(tree, mass, seg_off, lambda m: slot[m])
+    assert F.shape[0] == E * (B + 1)
+    assert np.max(np.abs(F[:, :9] - want)) <= 1e-15
+    assert np.all(F[:, 9:] == 0.0)
+    assert abs(ln.sum() - tree["bl"].sum()) < 1e-12
+    # every sample's total mass arrives at the root: sum over root child edges of F[seg0]
+    root_edges = [e for e in range(E) if tree["parent"][e] == tree["root"]]
+    tot = sum(F[seg_off[e], :9] for e in root_edges)
+    assert np.max(np.abs(tot - 1.0)) < 1e-12
+    plan.close()
+
+
+@pytest.mark.parametrize("n,E,P,bins", [(2, 3, 5, 0), (1, 9, 4, 0), (129, 33, 40, 2), (257, 17, 25, 1), (130, 5, 0, 0)])
+def test_ragged_shapes_vs_oracle(gb, oracle_mod, n, E, P, bins):
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(E, seed=11)
+    mass = synth.sample_masses(tree, n, P, seed=11) if P > 0 else dict(
+        off=np.zeros(n + 1, np.int64), edge=np.zeros(0, np.int32), pos=np.zeros(0), mass=np.zeros(0))
+    for p in (1.0, 3.0):
+        got = gb.earth_movers_distance(tree, mass, p=p, bins=bins)
+        want = oracle_mod.port_matrix(tree, mass, p=p, bins=bins)
+        assert got.shape == (n, n)
+        assert np.max(np.abs(got - want)) <= TOL * max(1.0, np.max(want))
+        if np.max(want) > 0:
+            assert rel_err(got[want > 1e-6], want[want > 1e-6]) <= TOL
+
+
+def test_unsorted_and_duplicate_input(gb, oracle_mod):
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(41, seed=2)
+    mass = synth.sample_masses(tree, 20, 200, seed=2)
+    rng = np.random.default_rng(1)
+    # duplicates: copy some positions inside each sample, then shuffle each sample
+    e, x, m = mass["edge"].copy(), mass["pos"].copy(), mass["mass"].copy()
+    for i in range(20):
+        s = slice(mass["off"][i], mass["off"][i + 1])
+        idx = np.arange(s.start, s.stop)
+        x[idx[1::7]] = x[idx[0::7][: len(idx[1::7])]]
+        e[idx[1::7]] = e[idx[0::7][: len(idx[1::7])]]
+        perm = rng.permutation(idx)
+        e[s], x[s], m[s] = e[perm], x[perm], m[perm]
+    shuf = dict(off=mass["off"], edge=e, pos=x, mass=m)
+    for bins in (0, 2):
+        got = gb.earth_movers_distance(tree, shuf, p=1.0, bins=bins)
+        want = oracle_mod.port_matrix(tree, shuf, p=1.0, bins=bins)
+        assert rel_err(got, want) <= TOL
+
+
+def test_split_invariance_and_determinism(gb):
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(301, seed=9)
+    mass = synth.sample_masses(tree, 140, 500, seed=9)
+    res = []
+    for split in (1, 3, 0, 0):
+        plan = gb.KrdPlan(bins=4, split=split)
+        plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+        plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+        res.append(plan.compute(p=1.0))
+        plan.close()
+    assert rel_err(res[0], res[1]) <= 1e-13 and rel_err(res[0], res[2]) <= 1e-13
+    assert np.array_equal(res[2], res[3])  # bit-identical run to run
+
+
+def test_errors_through_the_abi(gb):
+    tree, mass, _ = load_golden("test_ab.npz")
+    plan = gb.KrdPlan()
+    with pytest.raises(gb.KrdError) as ei:
+        plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    assert ei.value.status == gb.krd.KRD_ERR_STATE
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    for bad in (0.0, -1.0, float("nan")):
+        with pytest.raises(gb.KrdError, match="Invalid exponent value p") as ei:
+            plan.compute(p=bad)
+        assert ei.value.status == gb.krd.KRD_ERR_INVALID_EXPONENT
+    bad_edge = mass["edge"].copy(); bad_edge[0] = 99
+    with pytest.raises(gb.KrdError):
+        plan.set_masses(mass["off"], bad_edge, mass["pos"], mass["mass"])
+    with pytest.raises(gb.KrdError) as ei:   # two parents for one node
+        plan.set_tree(np.array([0, 0, 1], np.int32), np.array([1, 2, 2], np.int32), np.ones(3), 0)
+    assert ei.value.status == gb.krd.KRD_ERR_INCOMPATIBLE_TREES
+    plan.close()
+
+
+def test_full_size_properties_cfg2_shape(gb):
+    """BASELINE cfg2 shape (N=1000, E=9999, bins=4) with fewer placements: properties that need no
+    oracle — symmetry, zero diagonal, triangle inequality (p=1 KR is a metric), scaling linearity in
+    branch length, and an oracle spot check on a 24-sample subset."""
+    import oracle
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(9999, seed=42)
+    mass = synth.sample_masses(tree, 1000, 2000, seed=42)
+    plan = gb.KrdPlan(bins=4)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    D = plan.compute(p=1.0)
+    assert np.array_equal(D, D.T) and np.all(np.diag(D) == 0) and np.all(D[np.triu_indices(1000, 1)] > 0)
+    rng = np.random.default_rng(0)
+    i, j, k = rng.integers(0, 1000, (3, 20000))
+    assert np.all(D[i, j] <= D[i, k] + D[k, j] + 1e-12)
+    sub = dict(off=mass["off"][:25] - mass["off"][0], edge=mass["edge"][: mass["off"][24]],
+               pos=mass["pos"][: mass["off"][24]], mass=mass["mass"][: mass["off"][24]])
+    want = oracle.port_matrix(tree, sub, 1.0, bins=4)
+    assert rel_err(D[:24, :24], want) <= TOL
+    # scaling all branch lengths and positions by 2 doubles every distance (p = 1)
+    plan2 = gb.KrdPlan(bins=4)
+    plan2.set_tree(tree["parent"], tree["child"], tree["bl"] * 2.0, tree["root"])
+    plan2.set_masses(mass["off"], mass["edge"], mass["pos"] * 2.0, mass["mass"])
+    assert rel_err(plan2.compute(p=1.0), 2.0 * D) <= 1e-12
+    plan.close(); plan2.close()

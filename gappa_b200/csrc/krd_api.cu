@@ -181,7 +181,7 @@ static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank
     cudaEventRecord(h->ev[1], h->stream);
     krd_status st = run_pairs(h, p, divisor, rank, world, d_out, d_packed);
     if (st != KRD_OK) return st;
-    cudaEventRecord(h->ev[2], h->stream);
+    cudaEventRecord(h->ev[3], h->stream);
     return KRD_OK;
 }
 
@@ -243,12 +243,20 @@ krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
     if (!hc || !out) return KRD_ERR_INVALID_ARGUMENT;
     krd_handle* h = const_cast<krd_handle*>(hc);
     cudaSetDevice(h->device);
-    if (h->ev[2] && cudaEventQuery(h->ev[2]) == cudaSuccess && h->stats.launches > 0) {
+    if (h->ev[3] && cudaEventQuery(h->ev[3]) == cudaSuccess && h->stats.launches > 0 && h->stats.pair_ctas > 0) {
         cudaEventElapsedTime(&h->stats.ms_build, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&h->stats.ms_pairs, h->ev[1], h->ev[2]);
+        cudaEventElapsedTime(&h->stats.ms_epilogue, h->ev[2], h->ev[3]);
     }
     cudaGetLastError();
     *out = h->stats;
+    return KRD_OK;
+}
+
+krd_status krd_invalidate_F(krd_handle* h)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    h->F_valid = false;
     return KRD_OK;
 }
 

@@ -316,6 +316,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         default: e = launch_pairs<MODE_GENERIC>(P, grid, h->stream); break;
     }
     if (e != cudaSuccess) return cuda_fail(h, e, "k_pairs launch");
+    cudaEventRecord(h->ev[2], h->stream);
 
     EpiParams Q;
     Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.n_tiles = n_tiles; Q.split = split; Q.N = h->N;

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -41,7 +41,7 @@ class KrdStats(C.Structure):
                 ("n_segments", C.c_int64), ("ld_samples", C.c_int64), ("f_bytes", C.c_int64),
                 ("n_tiles", C.c_int64), ("split", C.c_int32), ("pair_ctas", C.c_int32),
                 ("levels", C.c_int32), ("launches", C.c_int32), ("ms_build", C.c_float),
-                ("ms_pairs", C.c_float)]
+                ("ms_pairs", C.c_float), ("ms_epilogue", C.c_float), ("reserved_f", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -93,6 +93,8 @@ def lib():
     L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
     L.krd_get_stats.restype = C.c_int
     L.krd_get_stats.argtypes = [vp, C.POINTER(KrdStats)]
+    L.krd_invalidate_F.restype = C.c_int
+    L.krd_invalidate_F.argtypes = [vp]
     L.krd_debug_copy_F.restype = C.c_int
     L.krd_debug_copy_F.argtypes = [vp, vp, vp]
     L.krd_host_alloc.restype = vp
@@ -195,6 +197,9 @@ class KrdPlan:
 
     def unpack_shards(self, d_gathered, d_out, world):
         self._check(self._L.krd_unpack_shards(self._h, world, _ptr(d_gathered), _ptr(d_out)))
+
+    def invalidate_F(self):
+        self._check(self._L.krd_invalidate_F(self._h))
 
     def stats(self):
         s = KrdStats()

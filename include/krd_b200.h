@@ -66,7 +66,9 @@ typedef struct krd_stats {
     int32_t levels;         /* tree levels = launches of the F builder */
     int32_t launches;       /* kernels launched by the last krd_compute* call */
     float   ms_build;       /* device time of the F builder in the last compute (CUDA events) */
-    float   ms_pairs;       /* device time of pair kernel + epilogue in the last compute */
+    float   ms_pairs;       /* device time of the pair kernel alone in the last compute */
+    float   ms_epilogue;    /* device time of the split-sum / root / mirror epilogue */
+    float   reserved_f;
 } krd_stats;
 
 krd_status  krd_create(const krd_config* cfg, krd_handle** out);
@@ -109,6 +111,10 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
 /* Scatter the all-gathered packed tiles (world * krd_shard_doubles doubles, DEVICE) into the
  * full symmetric n x n DEVICE matrix. */
 krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out);
+
+/* Drop the dense matrix F so that the next krd_compute* rebuilds it from the resident masses
+ * (bench: one "step" = F build + pair kernel + epilogue). */
+krd_status krd_invalidate_F(krd_handle* h);
 
 /* Introspection for parity tests: copy the dense cumulative-mass matrix F (n_segments x
  * ld_samples doubles) and the segment lengths (n_segments doubles) to HOST buffers. */

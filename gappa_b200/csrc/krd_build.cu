@@ -273,13 +273,14 @@ krd_status prepare_masses(krd_handle* h)
     if (M >= (int64_t)0xFFFFFFF0u) return fail(h, KRD_ERR_INVALID_ARGUMENT, "more than 2^32 masses are not supported");
 
     // --- canonical order check (edge asc, pos asc per sample = MassTree iteration order) ---
-    DevBuf sid, flags;
-    KRD_CUDA(h, sid.alloc((size_t)M * 4));
+    DevBuf flags;
+    cudaFree(h->d_sid); h->d_sid = nullptr;
+    KRD_CUDA(h, cudaMalloc(&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4));
     KRD_CUDA(h, flags.alloc(sizeof(int)));
     KRD_CUDA(h, cudaMemsetAsync(flags.p, 0, sizeof(int), h->stream));
     if (M > 0) {
-        k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, sid.as<uint32_t>());
-        k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(sid.as<uint32_t>(), h->d_edge, h->d_pos, M, E, flags.as<int>());
+        k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
+        k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, M, E, flags.as<int>());
     }
     int hflags = 0;
     KRD_CUDA(h, cudaMemcpyAsync(&hflags, flags.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -292,7 +293,7 @@ krd_status prepare_masses(krd_handle* h)
         KRD_CUDA(h, perm3.alloc((size_t)M * 4)); KRD_CUDA(h, skeys.alloc((size_t)M * 4));
         krd_status st = sort_edge_pos(h, perm2.as<uint32_t>(), sedge.as<uint32_t>());
         if (st != KRD_OK) return st;
-        st = stable_pass_u32<uint32_t>(h, sid.as<uint32_t>(), (uint32_t)std::max(N - 1, 1), M, perm2.as<uint32_t>(), perm3.as<uint32_t>(), skeys.as<uint32_t>());
+        st = stable_pass_u32<uint32_t>(h, h->d_sid, (uint32_t)std::max(N - 1, 1), M, perm2.as<uint32_t>(), perm3.as<uint32_t>(), skeys.as<uint32_t>());
         if (st != KRD_OK) return st;
         int32_t* ne; double *np, *nm;
         KRD_CUDA(h, cudaMalloc(&ne, (size_t)M * 4)); KRD_CUDA(h, cudaMalloc(&np, (size_t)M * 8)); KRD_CUDA(h, cudaMalloc(&nm, (size_t)M * 8));
@@ -380,46 +381,56 @@ krd_status prepare_masses(krd_handle* h)
 
 
 // ------------------------------------------------------------------------------------------------
-//  K1: level-synchronous postorder scan -> F[S_pad][ld]
+//  K1: scatter + level-synchronous postorder scan -> F[S_pad][ld]
 // ------------------------------------------------------------------------------------------------
 //
-// One thread per (edge e of the current level, sample i).  Levels are heights of the edge's child
-// node, so every child edge was finished by an earlier launch.  The thread
-//   1. starts from the subtree mass below e: sum over child edges c of F[seg_off[c]][i]
-//      (= mass at the proximal end of c; emd.cpp:145,167 node_masses[] without the array),
-//   2. walks e's segments distal -> proximal (emd.cpp:149-166), adding sample i's own masses
-//      when their slot is reached, and stores the running value — coalesced over i.
-// Threads with i >= N carry no masses and write the zero padding columns.
-__global__ void __launch_bounds__(128)
-k_build_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count,
-              const int32_t* __restrict__ kid_off, const int32_t* __restrict__ kid_edge,
-              const int32_t* __restrict__ seg_off, const int64_t* __restrict__ off,
-              const int32_t* __restrict__ edge, const int32_t* __restrict__ slot,
-              const double* __restrict__ mass, int N, int ld, double* __restrict__ F)
+// Phase A (k_scatter, one thread per mass entry, coalesced reads): entries of one sample that fall
+// on the same segment slot are adjacent (canonical order), so the first entry of each run sums the
+// run and stores it — one writer per cell, no atomics, bit-reproducible.
+// Phase B (k_scan_level, one thread per (edge of the level, sample), all traffic coalesced over
+// the sample axis): levels are heights of the edge's child node, so every child edge was finished
+// by an earlier launch.  The thread starts from the subtree mass below the edge
+//     sum over child edges c of F[seg_off[c]][i]        (emd.cpp:145,167 without node_masses[])
+// and turns the per-slot masses into the running distal -> proximal sum (emd.cpp:149-166).
+__global__ void __launch_bounds__(256)
+k_scatter(const uint32_t* __restrict__ sid, const int64_t* __restrict__ off, const int32_t* __restrict__ edge,
+          const int32_t* __restrict__ slot, const double* __restrict__ mass, const int32_t* __restrict__ seg_off,
+          int64_t M, int64_t ld, double* __restrict__ F)
 {
-    const int i = blockIdx.y * blockDim.x + threadIdx.x;
-    if (i >= ld) return;
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const uint32_t i = sid[m];
+    const int e = edge[m], s = slot[m];
+    if (m > off[i] && edge[m - 1] == e && slot[m - 1] == s) return;   // not the head of its run
+    const int64_t end = off[i + 1];
+    double sum = mass[m];
+    for (int64_t q = m + 1; q < end && edge[q] == e && slot[q] == s; ++q) sum += mass[q];
+    F[(int64_t)(seg_off[e] + s) * ld + i] = sum;
+}
+
+__global__ void __launch_bounds__(128)
+k_scan_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count,
+             const int32_t* __restrict__ kid_off, const int32_t* __restrict__ kid_edge,
+             const int32_t* __restrict__ seg_off, int64_t ld, double* __restrict__ F)
+{
+    const int64_t i = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
     for (int le = blockIdx.x; le < lvl_count; le += gridDim.x) {
         const int e = lvl_edges[lvl_begin + le];
+        const int k0 = kid_off[e], k1 = kid_off[e + 1];
+        const int s0 = seg_off[e], s1 = seg_off[e + 1];
         double acc = 0.0;
-        for (int k = kid_off[e]; k < kid_off[e + 1]; ++k)
-            acc += F[(int64_t)seg_off[kid_edge[k]] * ld + i];
-        int64_t lo = 0, hi = 0;
-        if (i < N) {
-            // [lo,hi) = sample i's entries on edge e (entries are sorted by edge)
-            const int64_t b = off[i], t = off[i + 1];
-            int64_t l = b, r = t;
-            while (l < r) { int64_t m = (l + r) >> 1; if (edge[m] < e) l = m + 1; else r = m; }
-            lo = l; r = t;
-            while (l < r) { int64_t m = (l + r) >> 1; if (edge[m] <= e) l = m + 1; else r = m; }
-            hi = l;
+        for (int k = k0; k < k1; ++k) acc += F[(int64_t)seg_off[kid_edge[k]] * ld + i];
+        double* col = F + i;
+        int t = s1 - 1;
+        for (; t - 3 >= s0; t -= 4) {   // four loads in flight before the dependent adds
+            const double v0 = col[(int64_t)t * ld], v1 = col[(int64_t)(t - 1) * ld];
+            const double v2 = col[(int64_t)(t - 2) * ld], v3 = col[(int64_t)(t - 3) * ld];
+            acc += v0; col[(int64_t)t * ld] = acc;
+            acc += v1; col[(int64_t)(t - 1) * ld] = acc;
+            acc += v2; col[(int64_t)(t - 2) * ld] = acc;
+            acc += v3; col[(int64_t)(t - 3) * ld] = acc;
         }
-        const int s0 = seg_off[e], k_e = seg_off[e + 1] - s0 - 1;
-        int64_t mp = hi - 1;
-        for (int t = k_e; t >= 0; --t) {
-            while (mp >= lo && slot[mp] >= t) { acc += mass[mp]; --mp; }
-            F[(int64_t)(s0 + t) * ld + i] = acc;
-        }
+        for (; t >= s0; --t) { acc += col[(int64_t)t * ld]; col[(int64_t)t * ld] = acc; }
     }
 }
 
@@ -431,17 +442,16 @@ krd_status build_F(krd_handle* h)
         KRD_CUDA(h, cudaMalloc(&h->d_F, need));
         h->F_capacity = need;
     }
-    // zero the padding rows [S, S_pad)
-    if (h->S_pad > h->S)
-        KRD_CUDA(h, cudaMemsetAsync(h->d_F + (size_t)h->S * h->ld, 0, (size_t)(h->S_pad - h->S) * h->ld * 8, h->stream));
+    KRD_CUDA(h, cudaMemsetAsync(h->d_F, 0, need, h->stream));
+    if (h->M > 0)
+        k_scatter<<<nblk(h->M), 256, 0, h->stream>>>(h->d_sid, h->d_off, h->d_edge, h->d_slot, h->d_mass, h->d_seg_off, h->M, h->ld, h->d_F);
     const int L = (int)h->lvl_off.size() - 1;
     dim3 block(128);
     for (int l = 0; l < L; ++l) {
         int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
         dim3 grid((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ld / 128));
-        k_build_level<<<grid, block, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge,
-                                                     h->d_seg_off, h->d_off, h->d_edge, h->d_slot, h->d_mass,
-                                                     h->N, h->ld, h->d_F);
+        k_scan_level<<<grid, block, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge,
+                                                    h->d_seg_off, h->ld, h->d_F);
     }
     KRD_CUDA(h, cudaGetLastError());
     h->F_valid = true;

@@ -53,6 +53,7 @@ struct krd_handle {
     int32_t* d_edge = nullptr;  // M
     double*  d_pos = nullptr;   // M
     double*  d_mass = nullptr;  // M
+    uint32_t* d_sid = nullptr;  // M: sample of each mass entry
     int32_t* d_slot = nullptr;  // M: segment index within the edge that receives this mass
     void*    d_owned[3] = {nullptr, nullptr, nullptr};  // edge/pos/mass buffers we allocated
 

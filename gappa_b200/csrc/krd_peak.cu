@@ -24,6 +24,13 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double seed, int iters, doubl
             for (int i = 0; i < ILP; ++i) {
                 if (MODE == 0) {
                     x[i] = fma(x[i], b, a);
+                } else if (MODE == 3) {
+                    x[i] = x[i] + fabs(y[(i + k) % ILP]);
+                } else if (MODE == 4) {
+                    double d = x[i] - y[(i + k) % ILP];
+                    x[i] = x[i] + fabs(d);
+                } else if (MODE == 5) {
+                    x[i] = fma(a, b, x[i]);
                 } else {
                     double d = x[i] - y[(i + k) % ILP];
                     x[i] = fma(a, fabs(d), x[i]);
@@ -75,11 +82,16 @@ extern "C" double krd_measure_fp64_peak(int device, int mode, double ms_target)
     auto launch = [&](int iters) {
         if (mode == 0) k_fp64_peak<0><<<grid, block>>>(1.000001, iters, sink);
         else if (mode == 1) k_fp64_peak<1><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 3) k_fp64_peak<3><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 4) k_fp64_peak<4><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 5) k_fp64_peak<5><<<grid, block>>>(1.000001, iters, sink);
         else k_dmma_peak<<<grid, block>>>(1.000001, iters, sink);
     };
     auto flops = [&](int iters) -> double {
         const double threads = (double)grid * block;
-        if (mode == 0) return threads * iters * (double)INNER * ILP * 2.0;
+        if (mode == 0 || mode == 5) return threads * iters * (double)INNER * ILP * 2.0;
+        if (mode == 3) return threads * iters * (double)INNER * ILP * 1.0;            // DADD only, 1 flop each
+        if (mode == 4) return threads * iters * (double)INNER * ILP * 2.0;            // DADD + DADD
         if (mode == 1) return threads * iters * (double)INNER * ILP * 3.0;        // DADD (1) + DFMA (2)
         return (threads / 32.0) * iters * (double)(INNER / 4) * ILP * (8 * 8 * 4 * 2.0);
     };

@@ -249,7 +249,8 @@ def main():
         peak_dmma = gappa_b200.measure_fp64_peak(local, 2, 200.0)
         peak = max(peak_dfma, peak_dmma)
         achieved = flops / t_pairs / 1e12
-        executed = 3.0 * (st["pair_ctas"] * 128.0 * 128.0) * (((S + 15) // 16 * 16) / max(st["split"], 1))
+        T = st["ld_samples"] // 128                          # executed: full tiles + 5/8 of each diagonal tile
+        executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((st["n_tiles"] - T) + 0.625 * T) * share
         line = {
             "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",

@@ -80,7 +80,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
-    cudaFree(h->d_ws); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
+    cudaFree(h->d_ws); cudaFree(h->d_sched); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     delete h;
 }

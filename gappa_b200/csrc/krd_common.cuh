@@ -71,6 +71,9 @@ struct krd_handle {
     double* d_ws = nullptr;
     size_t  ws_capacity = 0;
     krd::Tile* d_tiles = nullptr;
+    std::vector<krd::Tile> h_tiles;
+    void* d_sched = nullptr;      // work items + per-CTA offsets + per-tile offsets of the pair kernel
+    int64_t sched_key = -1, sched_items = 0, sched_cta_bytes = 0;
     int64_t n_tiles_alloc = 0;
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     size_t  out_tmp_capacity = 0;

@@ -5,11 +5,16 @@
 // for every i < j, written symmetrically with a zero diagonal (emd.cpp:193,214-215).
 //
 // Shape: a "GEMM with a different inner operator".  CTA tile 128 x 128 pairs, 256 threads, each
-// thread an 8 x 8 register tile (64 FP64 accumulators), K (= segment) axis streamed through a
-// 4-stage shared-memory ring filled by the TMA engine (cp.async.bulk, 1 KB rows, completion on an
-// mbarrier).  The upper triangle of tiles is crossed with a split of the segment axis so that the
-// grid fills 148 SMs in whole waves; partial tiles go to a workspace and a small deterministic
-// epilogue kernel sums the splits in fixed order, applies the outer root / divisor and mirrors.
+// thread an 8 x 8 register tile (64 FP64 accumulators).  The segment axis is streamed through a
+// shared-memory ring filled by the TMA engine (cp.async.bulk, 1 KB rows, completion counted on a
+// "full" mbarrier per stage; consumer warps release a stage on its "empty" mbarrier, so warps drift
+// instead of meeting at a CTA barrier).
+//
+// Scheduling is persistent "stream-K": the (tile, chunk) iteration space of the upper triangle is
+// cut into one contiguous, equal-cost span per SM (diagonal tiles are cheaper: their all-lower
+// 16x32 blocks are skipped warp-uniformly).  A span is a short list of work items (tile, chunk
+// range); each item leaves a partial 128x128 tile in a workspace and a small deterministic epilogue
+// kernel adds the partials of a tile in fixed order, applies the outer root / divisor and mirrors.
 // FP64 CUDA cores only: per (pair, segment) p = 1 costs DADD + DFMA, the floor for this operator.
 #include <algorithm>
 #include <cmath>
@@ -18,20 +23,23 @@
 
 namespace krd {
 
-constexpr int ST = 4;          // pipeline stages
-constexpr int NT = 256;        // threads per CTA
+constexpr int ST = 6;          // ring stages
+constexpr int LAG = 2;         // a stage is refilled LAG chunks after it was consumed
+constexpr int NT = 256;        // threads per CTA (8 warps; all compute, the TMA-issue role rotates)
 constexpr int STAGE_DOUBLES = 2 * KC * TILE + KC;  // A rows, B rows, len
-constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + ST * sizeof(uint64_t);
+constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * ST * sizeof(uint64_t);
+constexpr double DIAG_COST = 0.68;  // measured cost of a diagonal-tile chunk relative to a full one (5/8 of the math)
+
+struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
 struct PairParams {
     const double* F;
     const double* len;     // len or sqrt(len) (MODE_P2)
     const Tile* tiles;
-    double* ws;            // [split][n_tiles][TILE*TILE]
+    const WorkItem* items;
+    const int32_t* cta_item_off;   // gridDim.x + 1
+    double* ws;            // [item][TILE*TILE]
     int64_t ld;
-    int n_chunks;          // S_pad / KC
-    int chunks_per_split;
-    int n_tiles;
     double p;
 };
 
@@ -46,6 +54,10 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 {
@@ -77,7 +89,40 @@ __device__ __forceinline__ double pair_op(double a, double b, double l, double p
     return fma(l, pow(fabs(a - b), p), acc);
 }
 
-// ---- the tile kernel ------------------------------------------------------------------------------
+// One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
+// (diagonal tiles: blocks that lie entirely below the diagonal).
+template <int MODE, int QMIN>
+__device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const double* __restrict__ pb,
+                                           const double* __restrict__ sL, double p, double (&acc)[8][8])
+{
+#pragma unroll 4
+    for (int kk = 0; kk < KC; ++kk) {
+        double a[8], b[8];
+        const double l = sL[kk];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
+            a[2 * q] = va.x; a[2 * q + 1] = va.y;
+        }
+#pragma unroll
+        for (int q = QMIN; q < 4; ++q) {
+            const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
+            b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
+        }
+        if (MODE == MODE_P2) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) a[q] *= l;
+#pragma unroll
+            for (int q = 2 * QMIN; q < 8; ++q) b[q] *= l;
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, acc[r][cc]);
+    }
+}
+
+// ---- the persistent tile kernel -------------------------------------------------------------------
 
 template <int MODE>
 __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
@@ -85,101 +130,104 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stage_base = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)ST * STAGE_DOUBLES * sizeof(double));
+    uint64_t* empty = full + ST;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tx = tid & 15, ty = tid >> 4;
-    const Tile tile = P.tiles[blockIdx.x];
-    const bool diag = (tile.i == tile.j);
-    const int c0 = blockIdx.y * P.chunks_per_split;
-    const int c1 = min(c0 + P.chunks_per_split, P.n_chunks);
-    const int nc = max(c1 - c0, 0);
+    const int tx = lane & 15;
+    // row group of the warp: SM sub-partition s hosts warps s and s+4 -> row groups s and 7-s, which
+    // together skip 3 of 8 column blocks on a diagonal tile (balanced FP64 pipes)
+    const int rg = (warp < 4) ? warp : 11 - warp;
+    const int row0 = 16 * rg + 8 * (lane >> 4);
+
+    const int it0 = P.cta_item_off[blockIdx.x], it1 = P.cta_item_off[blockIdx.x + 1];
+    if (it0 == it1) return;
 
     if (tid == 0) {
-        for (int s = 0; s < ST; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NT / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     __syncthreads();
 
-    const double* gA = P.F + (int64_t)tile.i * TILE;
-    const double* gB = P.F + (int64_t)tile.j * TILE;
-    const uint32_t stage_bytes = (uint32_t)((diag ? 1 : 2) * KC * TILE * 8 + KC * 8);
-
-    // producer: warp 0; lane r < 16 fetches A row r, lane 16 + r fetches B row r, lane 0 also len
-    auto issue = [&](int chunk_local) {
-        const int s = chunk_local % ST;
-        double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
-        double* sB = sA + KC * TILE;
-        double* sL = sB + KC * TILE;
-        const int64_t k0 = (int64_t)(c0 + chunk_local) * KC;
-        if (lane == 0) mbar_expect_tx(&full[s], stage_bytes);
-        __syncwarp();
-        const int r = lane & 15;
-        if (lane < 16) tma_load_1d(sA + r * TILE, gA + (k0 + r) * P.ld, TILE * 8, &full[s]);
-        else if (!diag) tma_load_1d(sB + r * TILE, gB + (k0 + r) * P.ld, TILE * 8, &full[s]);
-        if (lane == 0) tma_load_1d(sL, P.len + k0, KC * 8, &full[s]);
+    // ---- producer role, rotated over the 8 warps (chunk j of the flattened sequence is issued by
+    // warp j % 8) so that no warp carries extra work and falls behind its sub-partition mate.  Every
+    // warp walks the same (item, chunk) sequence; only the owner waits for the stage and issues.
+    int p_item = it0, p_flat = 0;
+    WorkItem p_w = P.items[it0];
+    int p_chunk = p_w.c0;
+    auto produce_one = [&]() {   // advance the flattened sequence by one chunk; issue it if it is ours
+        if (p_item >= it1) return;
+        if ((p_flat & 7) == warp) {
+            const int s = p_flat % ST;
+            if (p_flat >= ST) mbar_wait(&empty[s], (uint32_t)(((p_flat / ST) - 1) & 1));
+            const Tile t = P.tiles[p_w.tile];
+            const bool dg = (t.i == t.j);
+            double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
+            double* sB = sA + KC * TILE;
+            double* sL = sB + KC * TILE;
+            const int64_t k0 = (int64_t)p_chunk * KC;
+            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((dg ? 1 : 2) * KC * TILE * 8 + KC * 8));
+            __syncwarp();
+            const int r = lane & 15;
+            if (lane < 16) tma_load_1d(sA + r * TILE, P.F + (int64_t)t.i * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
+            else if (!dg) tma_load_1d(sB + r * TILE, P.F + (int64_t)t.j * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
+            if (lane == 0) tma_load_1d(sL, P.len + k0, KC * 8, &full[s]);
+        }
+        ++p_flat;
+        if (++p_chunk >= p_w.c1) {
+            if (++p_item < it1) { p_w = P.items[p_item]; p_chunk = p_w.c0; }
+        }
     };
-
-    if (warp == 0) {
-        for (int c = 0; c < min(ST - 1, nc); ++c) issue(c);
-    }
+    for (int c = 0; c < ST - LAG; ++c) produce_one();
 
     double acc[8][8];
+    int flat = 0;
+    for (int item = it0; item < it1; ++item) {
+        const WorkItem w = P.items[item];
+        const Tile t = P.tiles[w.tile];
+        const bool diag = (t.i == t.j);
+        const int qmin = diag ? (rg >> 1) : 0;
 #pragma unroll
-    for (int r = 0; r < 8; ++r)
+        for (int r = 0; r < 8; ++r)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[r][c] = 0.0;
+            for (int c = 0; c < 8; ++c) acc[r][c] = 0.0;
 
-    for (int c = 0; c < nc; ++c) {
-        // every warp has finished chunk c-1 -> its stage may be refilled with chunk c+ST-1
-        __syncthreads();
-        if (warp == 0 && c + ST - 1 < nc) issue(c + ST - 1);
-
-        const int s = c % ST;
-        mbar_wait(&full[s], (uint32_t)((c / ST) & 1));
-        const double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
-        const double* sB = diag ? sA : sA + KC * TILE;
-        const double* sL = sA + 2 * KC * TILE;
-        const double* pa = sA + 8 * ty;
-        const double* pb = sB + 2 * tx;
-
-#pragma unroll 4
-        for (int kk = 0; kk < KC; ++kk) {
-            double a[8], b[8];
-            const double l = sL[kk];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
-                const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
-                a[2 * q] = va.x; a[2 * q + 1] = va.y;
-                b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
+        for (int c = w.c0; c < w.c1; ++c, ++flat) {
+            produce_one();   // (owner warp) refills the stage consumed LAG chunks ago
+            const int s = flat % ST;
+            mbar_wait(&full[s], (uint32_t)((flat / ST) & 1));
+            const double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
+            const double* sB = diag ? sA : sA + KC * TILE;
+            const double* sL = sA + 2 * KC * TILE;
+            const double* pa = sA + row0;
+            const double* pb = sB + 2 * tx;
+            switch (qmin) {
+                case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, acc); break;
+                case 1: chunk_math<MODE, 1>(pa, pb, sL, P.p, acc); break;
+                case 2: chunk_math<MODE, 2>(pa, pb, sL, P.p, acc); break;
+                default: chunk_math<MODE, 3>(pa, pb, sL, P.p, acc); break;
             }
-            if (MODE == MODE_P2) {
-#pragma unroll
-                for (int q = 0; q < 8; ++q) { a[q] *= l; b[q] *= l; }
-            }
-#pragma unroll
-            for (int r = 0; r < 8; ++r)
-#pragma unroll
-                for (int cc = 0; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, P.p, acc[r][cc]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
         }
-    }
 
-    // partial tile -> workspace; row = 8*ty + r, col = 32*q + 2*tx + {0,1}
-    double* w = P.ws + ((size_t)blockIdx.y * P.n_tiles + blockIdx.x) * (size_t)(TILE * TILE);
+        // partial tile -> workspace; row = row0 + r, col = 32*q + 2*tx + {0,1}
+        double* wout = P.ws + (size_t)item * (size_t)(TILE * TILE);
 #pragma unroll
-    for (int r = 0; r < 8; ++r)
+        for (int r = 0; r < 8; ++r)
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            *reinterpret_cast<double2*>(w + (8 * ty + r) * TILE + 32 * q + 2 * tx) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
+            for (int q = 0; q < 4; ++q)
+                *reinterpret_cast<double2*>(wout + (row0 + r) * TILE + 32 * q + 2 * tx) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
+    }
 }
 
-// ---- epilogue: sum splits in fixed order, outer root, divisor, mirror ---------------------------
+// ---- epilogue: sum a tile's partials in fixed order, outer root, divisor, mirror ------------------
 
 struct EpiParams {
     const double* ws;
     const Tile* tiles;
-    int n_tiles, split, N;
+    const int32_t* tile_item_off;   // n_tiles + 1
+    int n_tiles, N;
     double p, divisor;
     double* out;        // N x N row-major or nullptr
     double* packed;     // [n_tiles][TILE*TILE] or nullptr
@@ -188,10 +236,11 @@ struct EpiParams {
 __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
 {
     const Tile tile = P.tiles[blockIdx.x];
+    const int i0 = P.tile_item_off[blockIdx.x], i1 = P.tile_item_off[blockIdx.x + 1];
     const double inv_p = 1.0 / P.p;
     for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
         double v = 0.0;
-        for (int s = 0; s < P.split; ++s) v += P.ws[((size_t)s * P.n_tiles + blockIdx.x) * (size_t)(TILE * TILE) + idx];
+        for (int s = i0; s < i1; ++s) v += P.ws[(size_t)s * (size_t)(TILE * TILE) + idx];
         if (P.p > 1.0) v = (P.p == 2.0) ? sqrt(v) : pow(v, inv_p);
         v = v / P.divisor;
         const int r = idx / TILE, c = idx % TILE;
@@ -206,13 +255,14 @@ __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
 
 // gathered packed tiles of all ranks -> full matrix
 __global__ void __launch_bounds__(256) k_unpack(const double* __restrict__ gathered, const Tile* __restrict__ tiles,
-                                                int64_t n_tiles, int64_t per_rank, int N, double* __restrict__ out)
+                                                int64_t n_tiles, int N, double* __restrict__ out)
 {
-    // blockIdx.x = global tile number t; it lives on rank t / per_rank at slot t % per_rank
+    // blockIdx.x = global tile number t; rank r holds tiles [r*per_rank, (r+1)*per_rank) contiguously,
+    // and the all-gather concatenates ranks in order, so tile t sits at offset t.
     const int64_t t = blockIdx.x;
     if (t >= n_tiles) return;
     const Tile tile = tiles[t];
-    const double* src = gathered + (size_t)t * (TILE * TILE);  // ranks are contiguous: rank*per_rank + slot == t
+    const double* src = gathered + (size_t)t * (TILE * TILE);
     for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
         const int r = idx / TILE, c = idx % TILE;
         const int64_t i = (int64_t)tile.i * TILE + r, j = (int64_t)tile.j * TILE + c;
@@ -221,7 +271,6 @@ __global__ void __launch_bounds__(256) k_unpack(const double* __restrict__ gathe
             else if (i == j) out[i * N + i] = 0.0;
         }
     }
-    (void)per_rank;
 }
 
 // ---- host side ------------------------------------------------------------------------------------
@@ -233,36 +282,57 @@ static krd_status ensure_tiles(krd_handle* h)
     const int T = h->ld / TILE;
     const int64_t n_tiles = (int64_t)T * (T + 1) / 2;
     if (h->n_tiles_alloc == n_tiles && h->d_tiles) return KRD_OK;
-    std::vector<Tile> tiles; tiles.reserve((size_t)n_tiles);
+    h->h_tiles.clear(); h->h_tiles.reserve((size_t)n_tiles);
     // diagonal-major order: every contiguous range of tiles mixes rows and columns evenly, so a
-    // contiguous per-rank share has equal cost and concurrently running CTAs share F row blocks.
+    // contiguous per-rank share has near-equal cost.
     for (int d = 0; d < T; ++d)
-        for (int i = 0; i + d < T; ++i) tiles.push_back(Tile{i, i + d});
+        for (int i = 0; i + d < T; ++i) h->h_tiles.push_back(Tile{i, i + d});
     cudaFree(h->d_tiles); h->d_tiles = nullptr;
     KRD_CUDA(h, cudaMalloc(&h->d_tiles, (size_t)std::max<int64_t>(n_tiles, 1) * sizeof(Tile)));
-    KRD_CUDA(h, cudaMemcpyAsync(h->d_tiles, tiles.data(), (size_t)n_tiles * sizeof(Tile), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_tiles, h->h_tiles.data(), (size_t)n_tiles * sizeof(Tile), cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
     h->n_tiles_alloc = n_tiles;
     h->stats.n_tiles = n_tiles;
+    h->sched_key = -1;
     return KRD_OK;
 }
 
-// Split of the segment axis: minimise waves * chunks_per_split (time in chunk units).
-static int choose_split(int64_t n_tiles, int n_chunks, int sms)
+// Stream-K schedule: cut the cost axis (tiles x chunks, diagonal tiles cheaper) into `G` equal spans.
+static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, std::vector<WorkItem>& items,
+                          std::vector<int32_t>& cta_off, std::vector<int32_t>& tile_off)
 {
-    int best = 1; int64_t best_cost = INT64_MAX;
-    const int max_split = std::max(1, std::min(n_chunks / 8, 512));
-    for (int s = 1; s <= max_split; ++s) {
-        int64_t cps = (n_chunks + s - 1) / s;
-        int64_t waves = (n_tiles * s + sms - 1) / sms;
-        int64_t cost = waves * (cps + 6);   // +6 chunks ~ prologue/epilogue of a CTA
-        if (cost < best_cost) { best_cost = cost; best = s; }
+    items.clear(); cta_off.assign(G + 1, 0); tile_off.assign(n_tiles + 1, 0);
+    std::vector<double> pre(n_tiles + 1, 0.0);
+    for (int t = 0; t < n_tiles; ++t)
+        pre[t + 1] = pre[t] + ((tiles[t].i == tiles[t].j) ? DIAG_COST : 1.0) * n_chunks;
+    const double total = pre[n_tiles];
+    const int min_chunks = 8;   // do not create slivers: snap cuts that close to a tile border
+    int g = 0;                  // CTA that owns the current position
+    std::vector<int32_t> item_cta;
+    for (int t = 0; t < n_tiles; ++t) {
+        const double w = (tiles[t].i == tiles[t].j) ? DIAG_COST : 1.0;
+        int c = 0;
+        while (c < n_chunks) {
+            // end of CTA g's span, in chunks of this tile
+            const double bound = total * (g + 1) / G;
+            int ce = (g + 1 >= G) ? n_chunks : (int)std::llround((bound - pre[t]) / w);
+            if (ce >= n_chunks - min_chunks) ce = n_chunks;
+            if (ce <= c + min_chunks && ce < n_chunks) ce = std::min(n_chunks, c + min_chunks);
+            if (ce <= c) { ++g; continue; }
+            items.push_back(WorkItem{t, c, ce, 0});
+            item_cta.push_back(g);
+            c = ce;
+            if (c < n_chunks || pre[t + 1] >= bound - 1e-9) { if (g + 1 < G) ++g; }
+        }
+        tile_off[t + 1] = (int32_t)items.size();
     }
-    return best;
+    // items are in (tile, chunk) order and CTA ids are non-decreasing
+    for (size_t k = 0; k < items.size(); ++k) cta_off[item_cta[k] + 1] = (int32_t)(k + 1);
+    for (int q = 1; q <= G; ++q) cta_off[q] = std::max(cta_off[q], cta_off[q - 1]);
 }
 
 template <int MODE>
-static cudaError_t launch_pairs(const PairParams& P, dim3 grid, cudaStream_t stream)
+static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stream)
 {
     static bool configured = false;
     if (!configured) {
@@ -287,13 +357,30 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     if (d_out_packed && n_tiles < per_rank)   // ragged tail: keep the all-gather payload defined
         KRD_CUDA(h, cudaMemsetAsync(d_out_packed + (size_t)n_tiles * TILE * TILE, 0, (size_t)(per_rank - n_tiles) * TILE * TILE * 8, h->stream));
     h->stats.pair_ctas = 0;
-    if (n_tiles == 0) return KRD_OK;
+    if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
 
     const int n_chunks = (int)(h->S_pad / KC);
-    int split = h->cfg.split > 0 ? std::min(h->cfg.split, n_chunks) : choose_split(n_tiles, n_chunks, h->num_sms);
-    const int cps = (n_chunks + split - 1) / split;
-    split = (n_chunks + cps - 1) / cps;   // drop empty splits
-    const size_t ws_need = (size_t)split * n_tiles * TILE * TILE * sizeof(double);
+    const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
+    const int64_t key = ((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G;
+    if (key != h->sched_key) {
+        std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
+        make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, items, cta_off, tile_off);
+        cudaFree(h->d_sched); h->d_sched = nullptr;
+        const size_t b_items = items.size() * sizeof(WorkItem), b_cta = cta_off.size() * 4, b_tile = tile_off.size() * 4;
+        KRD_CUDA(h, cudaMalloc(&h->d_sched, b_items + b_cta + b_tile));
+        char* base = static_cast<char*>(h->d_sched);
+        KRD_CUDA(h, cudaMemcpyAsync(base, items.data(), b_items, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(base + b_items, cta_off.data(), b_cta, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(base + b_items + b_cta, tile_off.data(), b_tile, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        h->sched_items = (int64_t)items.size(); h->sched_cta_bytes = (int64_t)b_cta; h->sched_key = key;
+    }
+    const size_t b_items = (size_t)h->sched_items * sizeof(WorkItem);
+    const WorkItem* d_items = reinterpret_cast<const WorkItem*>(h->d_sched);
+    const int32_t* d_cta_off = reinterpret_cast<const int32_t*>(static_cast<char*>(h->d_sched) + b_items);
+    const int32_t* d_tile_off = reinterpret_cast<const int32_t*>(static_cast<char*>(h->d_sched) + b_items + h->sched_cta_bytes);
+
+    const size_t ws_need = (size_t)h->sched_items * TILE * TILE * sizeof(double);
     if (ws_need > h->ws_capacity) {
         cudaFree(h->d_ws); h->d_ws = nullptr; h->ws_capacity = 0;
         KRD_CUDA(h, cudaMalloc(&h->d_ws, ws_need));
@@ -305,26 +392,24 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
 
     PairParams P;
     P.F = h->d_F; P.len = (mode == MODE_P2) ? h->d_sqrt_len : h->d_len;
-    P.tiles = h->d_tiles + t0; P.ws = h->d_ws; P.ld = h->ld;
-    P.n_chunks = n_chunks; P.chunks_per_split = cps; P.n_tiles = n_tiles; P.p = p;
-    dim3 grid((unsigned)n_tiles, (unsigned)split);
+    P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p;
     cudaError_t e;
     switch (mode) {
-        case MODE_P1: e = launch_pairs<MODE_P1>(P, grid, h->stream); break;
-        case MODE_P2: e = launch_pairs<MODE_P2>(P, grid, h->stream); break;
-        case MODE_PHALF: e = launch_pairs<MODE_PHALF>(P, grid, h->stream); break;
-        default: e = launch_pairs<MODE_GENERIC>(P, grid, h->stream); break;
+        case MODE_P1: e = launch_pairs<MODE_P1>(P, G, h->stream); break;
+        case MODE_P2: e = launch_pairs<MODE_P2>(P, G, h->stream); break;
+        case MODE_PHALF: e = launch_pairs<MODE_PHALF>(P, G, h->stream); break;
+        default: e = launch_pairs<MODE_GENERIC>(P, G, h->stream); break;
     }
     if (e != cudaSuccess) return cuda_fail(h, e, "k_pairs launch");
     cudaEventRecord(h->ev[2], h->stream);
 
     EpiParams Q;
-    Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.n_tiles = n_tiles; Q.split = split; Q.N = h->N;
+    Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.tile_item_off = d_tile_off; Q.n_tiles = n_tiles; Q.N = h->N;
     Q.p = p; Q.divisor = divisor; Q.out = d_out_matrix; Q.packed = d_out_packed;
     k_epilogue<<<(unsigned)n_tiles, 256, 0, h->stream>>>(Q);
     KRD_CUDA(h, cudaGetLastError());
-    h->stats.split = split;
-    h->stats.pair_ctas = n_tiles * split;
+    h->stats.split = (int32_t)((h->sched_items + n_tiles - 1) / n_tiles);
+    h->stats.pair_ctas = G;
     h->stats.launches += 2;
     return KRD_OK;
 }
@@ -335,7 +420,8 @@ krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, dou
     if (st != KRD_OK) return st;
     const int64_t n_tiles = h->n_tiles_alloc;
     if (n_tiles == 0) return KRD_OK;
-    k_unpack<<<(unsigned)n_tiles, 256, 0, h->stream>>>(d_gathered, h->d_tiles, n_tiles, tiles_per_rank(n_tiles, world), h->N, d_out);
+    (void)world;
+    k_unpack<<<(unsigned)n_tiles, 256, 0, h->stream>>>(d_gathered, h->d_tiles, n_tiles, h->N, d_out);
     KRD_CUDA(h, cudaGetLastError());
     return KRD_OK;
 }

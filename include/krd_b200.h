@@ -51,7 +51,7 @@ typedef struct krd_config {
     int device;        /* CUDA device ordinal */
     int bins;          /* 0 = exact positions (what `gappa analyze krd` does);
                           B>0 = mass_tree_binify_masses(tree, B) first (functions.cpp:222) */
-    int split;         /* 0 = auto; >0 forces the segment-axis split factor of the pair kernel */
+    int split;         /* 0 = auto (one persistent CTA per SM); >0 forces the CTA count of the pair kernel */
     int reserved[5];   /* must be 0 */
 } krd_config;
 
@@ -61,7 +61,7 @@ typedef struct krd_stats {
     int64_t ld_samples;     /* padded sample stride of the dense matrix F[S][ld] */
     int64_t f_bytes;        /* bytes of F resident in HBM */
     int64_t n_tiles;        /* 128x128 upper-triangular tiles (incl. diagonal) */
-    int32_t split;          /* segment-axis split used by the last pair launch */
+    int32_t split;          /* work items per tile (rounded up) in the last pair launch */
     int32_t pair_ctas;      /* CTAs of the last pair launch */
     int32_t levels;         /* tree levels = launches of the F builder */
     int32_t launches;       /* kernels launched by the last krd_compute* call */

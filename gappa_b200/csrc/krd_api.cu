@@ -22,10 +22,20 @@ krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what)
     return fail(h, KRD_ERR_CUDA, m);
 }
 
-static void free_masses(krd_handle* h)
+krd_status reserve(krd_handle* h, void** p, size_t bytes)
 {
-    for (void*& q : h->d_owned) { if (q) cudaFree(q); q = nullptr; }
-    cudaFree(h->d_off); h->d_off = nullptr;
+    if (bytes == 0) bytes = 16;
+    auto it = h->caps.find(p);
+    if (*p && it != h->caps.end() && it->second >= bytes) return KRD_OK;
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    h->caps[p] = 0;
+    KRD_CUDA(h, cudaMalloc(p, bytes));
+    h->caps[p] = bytes;
+    return KRD_OK;
+}
+
+static void free_masses(krd_handle* h)   // buffers are kept for reuse; only the state is dropped
+{
     h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr;
     h->have_masses = false; h->F_valid = false;
 }
@@ -78,6 +88,8 @@ void krd_destroy(krd_handle* h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     free_masses(h);
+    for (void* q : h->d_owned) cudaFree(q);
+    cudaFree(h->d_off);
     cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_ws); cudaFree(h->d_sched); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
@@ -123,10 +135,10 @@ krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sampl
     free_masses(h);
     h->N = n_samples; h->M = M;
     const size_t Mx = (size_t)std::max<int64_t>(M, 1);
-    KRD_CUDA(h, cudaMalloc(&h->d_off, (size_t)(n_samples + 1) * 8));
-    KRD_CUDA(h, cudaMalloc(&h->d_owned[0], Mx * 4));
-    KRD_CUDA(h, cudaMalloc(&h->d_owned[1], Mx * 8));
-    KRD_CUDA(h, cudaMalloc(&h->d_owned[2], Mx * 8));
+    if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, &h->d_owned[0], Mx * 4)) != KRD_OK) return st;
+    if ((st = reserve(h, &h->d_owned[1], Mx * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, &h->d_owned[2], Mx * 8)) != KRD_OK) return st;
     h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; h->d_mass = (double*)h->d_owned[2];
     KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaMemcpyAsync(h->d_edge, edge, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
@@ -148,7 +160,7 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
     KRD_CUDA(h, cudaSetDevice(h->device));
     free_masses(h);
     h->N = n_samples; h->M = sample_off[n_samples];
-    KRD_CUDA(h, cudaMalloc(&h->d_off, (size_t)(n_samples + 1) * 8));
+    if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
     KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     h->d_edge = const_cast<int32_t*>(d_edge); h->d_pos = const_cast<double*>(d_pos); h->d_mass = const_cast<double*>(d_mass);
     st = prepare_masses(h);

@@ -274,8 +274,7 @@ krd_status prepare_masses(krd_handle* h)
 
     // --- canonical order check (edge asc, pos asc per sample = MassTree iteration order) ---
     DevBuf flags;
-    cudaFree(h->d_sid); h->d_sid = nullptr;
-    KRD_CUDA(h, cudaMalloc(&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4));
+    { krd_status rs = reserve(h, (void**)&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
     KRD_CUDA(h, flags.alloc(sizeof(int)));
     KRD_CUDA(h, cudaMemsetAsync(flags.p, 0, sizeof(int), h->stream));
     if (M > 0) {
@@ -301,24 +300,22 @@ krd_status prepare_masses(krd_handle* h)
         k_gather<double, double><<<nblk(M), 256, 0, h->stream>>>(h->d_pos, perm3.as<uint32_t>(), M, np);
         k_gather<double, double><<<nblk(M), 256, 0, h->stream>>>(h->d_mass, perm3.as<uint32_t>(), M, nm);
         KRD_CUDA(h, cudaStreamSynchronize(h->stream));
-        for (void* q : h->d_owned) if (q) cudaFree(q);
+        for (void*& q : h->d_owned) { if (q) cudaFree(q); q = nullptr; }
         h->d_owned[0] = ne; h->d_owned[1] = np; h->d_owned[2] = nm;
+        h->caps[&h->d_owned[0]] = (size_t)M * 4; h->caps[&h->d_owned[1]] = (size_t)M * 8; h->caps[&h->d_owned[2]] = (size_t)M * 8;
         h->d_edge = ne; h->d_pos = np; h->d_mass = nm;
     }
 
-    cudaFree(h->d_slot); h->d_slot = nullptr;
-    cudaFree(h->d_seg_off); h->d_seg_off = nullptr;
-    cudaFree(h->d_len); h->d_len = nullptr;
-    cudaFree(h->d_sqrt_len); h->d_sqrt_len = nullptr;
-    KRD_CUDA(h, cudaMalloc(&h->d_slot, (size_t)std::max<int64_t>(M, 1) * 4));
-    KRD_CUDA(h, cudaMalloc(&h->d_seg_off, (size_t)(E + 1) * 4));
+    { krd_status rs = reserve(h, (void**)&h->d_slot, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
+    { krd_status rs = reserve(h, (void**)&h->d_seg_off, (size_t)(E + 1) * 4); if (rs != KRD_OK) return rs; }
 
     auto alloc_len = [&](int64_t S) -> krd_status {
         h->S = S;
         h->S_pad = ((S + KC - 1) / KC) * KC;
         if (h->S_pad == 0) h->S_pad = KC;
-        KRD_CUDA(h, cudaMalloc(&h->d_len, (size_t)h->S_pad * 8));
-        KRD_CUDA(h, cudaMalloc(&h->d_sqrt_len, (size_t)h->S_pad * 8));
+        krd_status rs = reserve(h, (void**)&h->d_len, (size_t)h->S_pad * 8);
+        if (rs != KRD_OK) return rs;
+        if ((rs = reserve(h, (void**)&h->d_sqrt_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
         KRD_CUDA(h, cudaMemsetAsync(h->d_len, 0, (size_t)h->S_pad * 8, h->stream));
         return KRD_OK;
     };

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/krd_b200.h"
@@ -78,6 +79,8 @@ struct krd_handle {
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     size_t  out_tmp_capacity = 0;
 
+    std::unordered_map<void**, size_t> caps;   // capacities of buffers managed by krd::reserve
+
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     krd_stats stats{};
 };
@@ -92,6 +95,9 @@ krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what);
         cudaError_t _e = (call);                                       \
         if (_e != cudaSuccess) return krd::cuda_fail((h), _e, #call);  \
     } while (0)
+
+// grow-only device buffer: reallocates *p only when `bytes` exceeds its recorded capacity
+krd_status reserve(krd_handle* h, void** p, size_t bytes);
 
 // krd_build.cu
 krd_status build_tree(krd_handle* h);                 // host preprocessing + upload

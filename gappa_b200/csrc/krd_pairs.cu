@@ -282,11 +282,12 @@ static krd_status ensure_tiles(krd_handle* h)
     const int T = h->ld / TILE;
     const int64_t n_tiles = (int64_t)T * (T + 1) / 2;
     if (h->n_tiles_alloc == n_tiles && h->d_tiles) return KRD_OK;
-    h->h_tiles.clear(); h->h_tiles.reserve((size_t)n_tiles);
-    // diagonal-major order: every contiguous range of tiles mixes rows and columns evenly, so a
-    // contiguous per-rank share has near-equal cost.
-    for (int d = 0; d < T; ++d)
-        for (int i = 0; i + d < T; ++i) h->h_tiles.push_back(Tile{i, i + d});
+    h->h_tiles.resize((size_t)n_tiles);
+    {
+        std::vector<int32_t> ti((size_t)n_tiles), tj((size_t)n_tiles);
+        krd_tile_list(h->N, ti.data(), tj.data());
+        for (int64_t t = 0; t < n_tiles; ++t) h->h_tiles[(size_t)t] = Tile{ti[(size_t)t], tj[(size_t)t]};
+    }
     cudaFree(h->d_tiles); h->d_tiles = nullptr;
     KRD_CUDA(h, cudaMalloc(&h->d_tiles, (size_t)std::max<int64_t>(n_tiles, 1) * sizeof(Tile)));
     KRD_CUDA(h, cudaMemcpyAsync(h->d_tiles, h->h_tiles.data(), (size_t)n_tiles * sizeof(Tile), cudaMemcpyHostToDevice, h->stream));
@@ -351,8 +352,8 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     if (st != KRD_OK) return st;
     const int64_t n_tiles_all = h->n_tiles_alloc;
     const int64_t per_rank = tiles_per_rank(n_tiles_all, world);
-    const int64_t t0 = std::min<int64_t>((int64_t)rank * per_rank, n_tiles_all);
-    const int64_t t1 = std::min<int64_t>(t0 + per_rank, n_tiles_all);
+    int64_t t0 = 0, t1 = 0;
+    krd_rank_tiles(n_tiles_all, rank, world, &t0, &t1);
     const int n_tiles = (int)(t1 - t0);
     if (d_out_packed && n_tiles < per_rank)   // ragged tail: keep the all-gather payload defined
         KRD_CUDA(h, cudaMemsetAsync(d_out_packed + (size_t)n_tiles * TILE * TILE, 0, (size_t)(per_rank - n_tiles) * TILE * TILE * 8, h->stream));
@@ -427,3 +428,32 @@ krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, dou
 }
 
 }  // namespace krd
+
+extern "C" {
+
+int64_t krd_tile_count(int32_t n_samples)
+{
+    const int64_t T = ((int64_t)n_samples + krd::TILE - 1) / krd::TILE;
+    return T * (T + 1) / 2;
+}
+
+// diagonal-major: every contiguous range mixes tile rows and columns evenly, so contiguous
+// per-rank shares have near-equal cost (only the first rank(s) hold the cheaper diagonal tiles).
+krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j)
+{
+    if (n_samples < 0 || !tile_i || !tile_j) return KRD_ERR_INVALID_ARGUMENT;
+    const int T = (n_samples + krd::TILE - 1) / krd::TILE;
+    int64_t k = 0;
+    for (int d = 0; d < T; ++d)
+        for (int i = 0; i + d < T; ++i, ++k) { tile_i[k] = i; tile_j[k] = i + d; }
+    return KRD_OK;
+}
+
+void krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1)
+{
+    const int64_t per_rank = krd::tiles_per_rank(n_tiles, world);
+    *t0 = std::min<int64_t>((int64_t)rank * per_rank, n_tiles);
+    *t1 = std::min<int64_t>(*t0 + per_rank, n_tiles);
+}
+
+}  // extern "C"

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -93,6 +93,12 @@ def lib():
     L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
     L.krd_get_stats.restype = C.c_int
     L.krd_get_stats.argtypes = [vp, C.POINTER(KrdStats)]
+    L.krd_tile_count.restype = i64
+    L.krd_tile_count.argtypes = [i32]
+    L.krd_tile_list.restype = C.c_int
+    L.krd_tile_list.argtypes = [i32, vp, vp]
+    L.krd_rank_tiles.restype = None
+    L.krd_rank_tiles.argtypes = [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)]
     L.krd_invalidate_F.restype = C.c_int
     L.krd_invalidate_F.argtypes = [vp]
     L.krd_debug_copy_F.restype = C.c_int
@@ -230,3 +236,20 @@ def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):
 
 def measure_fp64_peak(device=0, mode=0, ms=200.0):
     return float(lib().krd_measure_fp64_peak(device, mode, ms))
+
+
+TILE = 128
+
+
+def tile_list(n_samples):
+    """Upper-triangular 128x128 tile coordinates in the library's (diagonal-major) order."""
+    n = int(lib().krd_tile_count(n_samples))
+    ti = np.zeros(n, np.int32); tj = np.zeros(n, np.int32)
+    lib().krd_tile_list(n_samples, _ptr(ti), _ptr(tj))
+    return ti, tj
+
+
+def rank_tiles(n_tiles, rank, world):
+    t0, t1 = C.c_int64(), C.c_int64()
+    lib().krd_rank_tiles(n_tiles, rank, world, C.byref(t0), C.byref(t1))
+    return t0.value, t1.value

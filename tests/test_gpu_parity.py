@@ -210,3 +210,27 @@ def test_full_size_properties_cfg2_shape(gb):
     plan2.set_masses(mass["off"], mass["edge"], mass["pos"] * 2.0, mass["mass"])
     assert rel_err(plan2.compute(p=1.0), 2.0 * D) <= 1e-12
     plan.close(); plan2.close()
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_compute_equals_single(gb, world):
+    """All ranks' shares computed one after another on this GPU (no inter-rank waiting), concatenated
+    like an all-gather, unpacked: must equal the single-GPU matrix bit for bit."""
+    import torch
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(201, seed=4)
+    mass = synth.sample_masses(tree, 300, 300, seed=4)
+    plan = gb.KrdPlan(bins=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    single = torch.zeros((300, 300), dtype=torch.float64, device="cuda")
+    plan.compute_device(single, p=1.0)
+    shard = plan.shard_doubles(world)
+    gathered = torch.empty(shard * world, dtype=torch.float64, device="cuda")
+    for r in range(world):
+        plan.compute_shard(gathered[r * shard:(r + 1) * shard], r, world, p=1.0)
+    out = torch.full((300, 300), -1.0, dtype=torch.float64, device="cuda")
+    plan.unpack_shards(gathered, out, world)
+    torch.cuda.synchronize()
+    assert torch.equal(out, single)
+    plan.close()

@@ -1,0 +1,235 @@
+// gappa-b200 — `analyze krd` with the flag surface of the reference command
+// (gappa src/commands/analyze/krd.cpp:58-158) on top of the B200 library (include/krd_b200.h).
+//
+//   gappa-b200 analyze krd --jplace-path <files|dirs>... [--exponent p] [--normalize]
+//        [--point-mass] [--ignore-multiplicities] [--out-dir d] [--file-prefix s] [--file-suffix s]
+//        [--compress] [--matrix-format matrix|list|triangular] [--omit-matrix-labels]
+//        [--allow-file-overwriting] [--verbose] [--threads n] [--log-file f]
+//   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d,
+//             --write-binary f (raw row-major doubles, for full-precision comparisons)
+//
+// Exit code 0 on success; on error prints "Error: <message>" like src/main.cpp:167-173 and exits 1.
+#include <sys/stat.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+
+#include "../../include/krd_b200.h"
+#include "ingest.hpp"
+#include "matrix_writer.hpp"
+
+using namespace krdhost;
+
+namespace {
+
+struct KrdOptions {
+    std::vector<std::string> jplace_paths;
+    double exponent = 1.0;
+    bool normalize = false, point_mass = false, ignore_multiplicities = false;
+    std::string out_dir = ".", prefix, suffix, matrix_format = "matrix", log_file, write_binary;
+    bool compress = false, omit_labels = false, allow_overwrite = false, verbose = false;
+    int threads = 0, bins = 0, device = 0;
+};
+
+const char* kUsage =
+    "Usage: gappa-b200 analyze krd [OPTIONS]\n"
+    "Calculate the pairwise Kantorovich-Rubinstein (KR) distance matrix between samples.\n\n"
+    "Input:\n  --jplace-path TEXT ... REQUIRED   List of jplace files or directories to process.\n"
+    "Settings:\n  --exponent FLOAT=1                Exponent for KR integration.\n"
+    "  --normalize                       Divide the KR distance by the tree length to get normalized values.\n"
+    "  --point-mass                      Treat every pquery as a point mass on its highest-weight placement.\n"
+    "  --ignore-multiplicities           Set the multiplicity of each pquery to 1.0.\n"
+    "  --bins INT=0                      (additive) binify masses into this many bins per edge first.\n"
+    "Matrix Output:\n  --out-dir TEXT=.  --file-prefix TEXT  --file-suffix TEXT  --compress\n"
+    "  --matrix-format TEXT=matrix       matrix | list | triangular\n  --omit-matrix-labels\n"
+    "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --help\n";
+
+[[noreturn]] void usage_error(const std::string& msg)
+{
+    std::cerr << msg << "\nRun with --help for more information.\n";
+    std::exit(106);   // CLI11 ExitCodes::ExtrasError-like; any non-zero
+}
+
+bool valid_filefix(const std::string& s)
+{
+    if (s.empty()) return true;
+    if (std::isspace((unsigned char)s.front()) || std::isspace((unsigned char)s.back())) return false;
+    for (char c : s) if (!std::isprint((unsigned char)c) || std::string("<>:\"\\/|?*").find(c) != std::string::npos) return false;
+    return true;
+}
+
+KrdOptions parse_args(int argc, char** argv)
+{
+    KrdOptions o;
+    int i = 1;
+    if (argc >= 2 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) { std::cout << kUsage; std::exit(0); }
+    if (argc < 3 || std::string(argv[1]) != "analyze" || std::string(argv[2]) != "krd")
+        usage_error("gappa-b200 implements exactly one command: `analyze krd`.");
+    i = 3;
+    std::vector<std::string> args;
+    for (; i < argc; ++i) {
+        std::string a = argv[i];
+        const size_t eq = a.find('=');
+        if (a.rfind("--", 0) == 0 && eq != std::string::npos) { args.push_back(a.substr(0, eq)); args.push_back(a.substr(eq + 1)); }
+        else args.push_back(a);
+    }
+    auto is_opt = [](const std::string& s) { return s.rfind("--", 0) == 0; };
+    for (size_t k = 0; k < args.size(); ++k) {
+        const std::string& a = args[k];
+        auto value = [&]() -> std::string {
+            if (k + 1 >= args.size() || is_opt(args[k + 1])) usage_error(a + ": 1 required TEXT missing");
+            return args[++k];
+        };
+        auto number = [&](auto conv) {
+            const std::string v = value();
+            try { size_t used = 0; auto r = conv(v, &used); if (used != v.size()) throw 0; return r; }
+            catch (...) { usage_error("Could not convert: " + a + " = " + v); }
+        };
+        if (a == "--jplace-path") {
+            size_t before = o.jplace_paths.size();
+            while (k + 1 < args.size() && !is_opt(args[k + 1])) o.jplace_paths.push_back(args[++k]);
+            if (o.jplace_paths.size() == before) usage_error("--jplace-path: At least 1 required");
+        } else if (a == "--exponent" || a == "--krd-exponent") o.exponent = number([](const std::string& s, size_t* u) { return std::stod(s, u); });
+        else if (a == "--normalize") o.normalize = true;
+        else if (a == "--point-mass") o.point_mass = true;
+        else if (a == "--ignore-multiplicities") o.ignore_multiplicities = true;
+        else if (a == "--out-dir") o.out_dir = value();
+        else if (a == "--file-prefix") o.prefix = value();
+        else if (a == "--file-suffix") o.suffix = value();
+        else if (a == "--compress") o.compress = true;
+        else if (a == "--matrix-format") o.matrix_format = value();
+        else if (a == "--omit-matrix-labels") o.omit_labels = true;
+        else if (a == "--allow-file-overwriting") o.allow_overwrite = true;
+        else if (a == "--verbose") o.verbose = true;
+        else if (a == "--threads") o.threads = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
+        else if (a == "--log-file") o.log_file = value();
+        else if (a == "--bins") o.bins = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
+        else if (a == "--device") o.device = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
+        else if (a == "--write-binary") o.write_binary = value();
+        else if (a == "--help" || a == "-h") { std::cout << kUsage; std::exit(0); }
+        else usage_error("The following argument was not expected: " + a);
+    }
+    if (o.jplace_paths.empty()) usage_error("--jplace-path is required");
+    for (const auto& p : o.jplace_paths)
+        if (!is_file_path(p) && !is_dir_path(p)) usage_error("--jplace-path: Path does not exist: " + p);
+    if (!valid_filefix(o.prefix)) usage_error("--file-prefix: File prefix contains invalid characters (`<>:\"\\/|?*`), non-printable characters, or surrounding whitespace.");
+    if (!valid_filefix(o.suffix)) usage_error("--file-suffix: File suffix contains invalid characters (`<>:\"\\/|?*`), non-printable characters, or surrounding whitespace.");
+    parse_matrix_format(o.matrix_format);   // validates
+    if (o.bins < 0) usage_error("--bins: must be >= 0");
+    if (o.threads <= 0) {
+        o.threads = (int)std::thread::hardware_concurrency();
+        if (o.threads <= 0) o.threads = 1;
+    }
+    return o;
+}
+
+struct Log {
+    std::ofstream file;
+    void msg(const std::string& s) { std::cout << s << std::endl; if (file.is_open()) file << s << std::endl; }
+};
+
+void mkdirs(const std::string& dir)
+{
+    std::string cur;
+    for (size_t i = 0; i <= dir.size(); ++i) {
+        if (i == dir.size() || dir[i] == '/') {
+            if (!cur.empty() && !is_dir_path(cur) && ::mkdir(cur.c_str(), 0775) != 0 && !is_dir_path(cur))
+                throw std::runtime_error("Cannot create directory: " + cur);
+        }
+        if (i < dir.size()) cur += dir[i];
+    }
+}
+
+void check_krd(krd_handle* h, krd_status st)
+{
+    if (st == KRD_OK) return;
+    const std::string m = krd_last_error(h);
+    if (st == KRD_ERR_INCOMPATIBLE_TREES) throw std::invalid_argument(m);   // emd.cpp:78,109,123,172
+    throw std::runtime_error(m);
+}
+
+int run_krd(const KrdOptions& o, Log& log)
+{
+    using clk = std::chrono::steady_clock;
+    // krd.cpp:119-121 / file_output.cpp:229-277: fail early if the output exists
+    std::string dir = o.out_dir;
+    while (dir.size() > 1 && dir.back() == '/') dir.pop_back();
+    const std::string out_path = dir + "/" + o.prefix + "krd_matrix" + o.suffix + ".csv" + (o.compress ? ".gz" : "");
+    if (is_file_path(out_path)) {
+        if (!o.allow_overwrite)
+            throw std::runtime_error("Output file already exists: " + out_path + "\nUse --allow-file-overwriting to allow gappa to overwrite the file.");
+        log.msg("Warning: Output file already exists and will be overwritten: " + out_path);
+    }
+
+    const auto files = resolve_jplace_paths(o.jplace_paths);
+    log.msg("Found " + std::to_string(files.size()) + " jplace file" + (files.size() > 1 ? "s" : ""));   // file_input.cpp:168-170
+    if (files.size() < 2) throw std::runtime_error("Cannot run krd with fewer than 2 samples.");       // krd.cpp:131-133
+
+    auto t0 = clk::now();
+    IngestOptions io;
+    io.point_mass = o.point_mass; io.ignore_multiplicities = o.ignore_multiplicities; io.threads = o.threads;
+    MassSet ms = load_mass_set(files, io);
+    auto t1 = clk::now();
+
+    log.msg("Calculating pairwise KR distances.");
+    const int32_t n = ms.n_samples();
+    krd_config cfg{};
+    cfg.device = o.device; cfg.bins = o.bins;
+    krd_handle* h = nullptr;
+    if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
+    std::vector<double> matrix((size_t)n * (size_t)n, 0.0);
+    krd_stats st{};
+    try {
+        check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
+        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+        // krd.cpp:144-150: --normalize divides by the DIAMETER of the (averaged) tree
+        const double divisor = o.normalize ? diameter(ms.tree) : 1.0;
+        check_krd(h, krd_compute(h, o.exponent, divisor, matrix.data()));
+        krd_get_stats(h, &st);
+    } catch (...) { krd_destroy(h); throw; }
+    krd_destroy(h);
+    auto t2 = clk::now();
+
+    log.msg("Writing distance matrix.");
+    mkdirs(dir);
+    std::vector<std::string> names;
+    for (const auto& f : files) names.push_back(sample_label(f));
+    write_matrix_file(out_path, matrix.data(), (size_t)n, parse_matrix_format(o.matrix_format),
+                      o.omit_labels ? nullptr : &names, "Sample", o.compress, o.threads);
+    if (!o.write_binary.empty()) {
+        std::ofstream b(o.write_binary, std::ios::binary);
+        b.write(reinterpret_cast<const char*>(matrix.data()), (std::streamsize)(matrix.size() * sizeof(double)));
+    }
+    auto t3 = clk::now();
+    if (o.verbose) {
+        auto sec = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+        char buf[512];
+        std::snprintf(buf, sizeof buf,
+                      "samples %d, edges %lld, masses %lld, segments %lld | ingest %.3f s, device path %.3f s "
+                      "(F build %.3f ms, pair kernel %.3f ms, epilogue %.3f ms), write %.3f s",
+                      n, (long long)st.n_edges, (long long)st.n_masses, (long long)st.n_segments, sec(t0, t1), sec(t1, t2),
+                      st.ms_build, st.ms_pairs, st.ms_epilogue, sec(t2, t3));
+        log.msg(buf);
+    }
+    log.msg("Finished");
+    return 0;
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    KrdOptions o = parse_args(argc, argv);
+    Log log;
+    if (!o.log_file.empty()) log.file.open(o.log_file);
+    try {
+        return run_krd(o, log);
+    } catch (std::exception const& ex) {
+        std::cerr << "Error: " << ex.what() << std::endl;
+        if (log.file.is_open()) log.file << "Error: " << ex.what() << std::endl;
+        return 1;
+    }
+}

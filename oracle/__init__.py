@@ -83,6 +83,8 @@ def ref():
         L.ref_dump_copy.argtypes = [C.c_void_p, _i32p, _i32p, _i32p, _f64p, _i64p, _i32p, _f64p,
                                     _f64p, _f64p]
         L.ref_dump_free.argtypes = [C.c_void_p]
+        L.ref_write_matrix.restype = C.c_int
+        L.ref_write_matrix.argtypes = [C.c_char_p, _f64p, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_char_p]
         _ref = L
     return _ref
 
@@ -175,3 +177,14 @@ def ref_jplace(paths, point_mass=False, ignore_multiplicities=False):
     tree = dict(parent=parent, child=child, bl=bl, root=root.value)
     m = dict(off=off, edge=edge, pos=pos, mass=mass)
     return tree, m, dict(edge_num=en, pendant=pend, diameter=dia.value)
+
+
+def ref_write_matrix(path, matrix, fmt="matrix", labels=None, corner="Sample"):
+    """genesis MatrixWriter<double> configured like gappa's write_matrix (matrix_output.cpp:76-111)."""
+    m = np.ascontiguousarray(matrix, np.float64)
+    n = m.shape[0]
+    lab = None if labels is None else (C.c_char_p * n)(*[s.encode() for s in labels])
+    rc = ref().ref_write_matrix(os.fspath(path).encode(), m, n, {"matrix": 0, "list": 1, "triangular": 2}[fmt], lab,
+                                corner.encode())
+    if rc != 0:
+        raise RuntimeError(ref().ref_last_error().decode())

@@ -8,6 +8,8 @@
 //                          after mass_tree_binify_masses (tree/mass_tree/functions.cpp:222-265)
 //   * ref_jplace_load   -> the ingest gappa does in JplaceInputOptions::mass_tree_set()
 //                          (src/options/jplace_input.cpp:129-171,295-332), dumped to flat arrays
+//   * ref_write_matrix -> genesis::utils::MatrixWriter<double> as configured by gappa
+//                          (src/options/matrix_output.cpp:76-111), to a file
 //   * ref_diameter      -> genesis::tree::diameter (tree/common_tree/functions.cpp:178-205)
 // This file is ours; it contains no reference code, it only calls it.
 
@@ -22,7 +24,10 @@
 #include "genesis/tree/mass_tree/emd.hpp"
 #include "genesis/tree/mass_tree/functions.hpp"
 #include "genesis/tree/mass_tree/tree.hpp"
+#include "genesis/utils/containers/matrix.hpp"
+#include "genesis/utils/containers/matrix/writer.hpp"
 #include "genesis/utils/io/input_source.hpp"
+#include "genesis/utils/io/output_target.hpp"
 
 #include <omp.h>
 
@@ -251,5 +256,30 @@ void ref_dump_copy(void* h, int* parent, int* child, int* edge_num, double* bl, 
 }
 
 void ref_dump_free(void* h) { delete static_cast<Dump*>(h); }
+
+// gappa's MatrixOutputOptions::write_matrix (src/options/matrix_output.cpp:76-111) on a flat matrix:
+// format 0 = matrix, 1 = list, 2 = triangular; labels == nullptr -> --omit-matrix-labels.
+int ref_write_matrix(const char* path, const double* m, int n, int format, const char** labels, const char* corner)
+{
+    try {
+        utils::Matrix<double> mat((size_t)n, (size_t)n);
+        for (size_t r = 0; r < (size_t)n; ++r) for (size_t c = 0; c < (size_t)n; ++c) mat(r, c) = m[r * n + c];
+        auto writer = utils::MatrixWriter<double>();
+        writer.format(format == 0 ? utils::MatrixWriter<double>::Format::kMatrix
+                      : format == 1 ? utils::MatrixWriter<double>::Format::kList
+                                    : utils::MatrixWriter<double>::Format::kTriangular);
+        auto target = utils::to_file(path);
+        if (labels) {
+            std::vector<std::string> names(labels, labels + n);
+            writer.write(mat, target, names, names, corner);
+        } else {
+            writer.write(mat, target);
+        }
+        return 0;
+    } catch (std::exception const& ex) {
+        g_err = ex.what();
+        return 1;
+    }
+}
 
 } // extern "C"

@@ -1,0 +1,225 @@
+"""Host side of `analyze krd` (jplace ingest, matrix writer, CLI) against fixtures generated from the
+compiled reference (tests/golden/make_golden_host.py) and — where /root/reference is present —
+against the reference run live.  Bar: BIT-EXACT mass arrays and BYTE-IDENTICAL CSV output."""
+import ctypes
+import glob
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from gappa_b200 import host
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+JP = os.path.join(GOLD, "jplace")
+REF = "/root/reference"
+OPTS = {"default": {}, "pm": dict(point_mass=True), "im": dict(ignore_multiplicities=True)}
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLD, "host_ingest.npz"))
+
+
+def test_host_library_exports():
+    L = ctypes.CDLL(host.LIB_PATH)
+    hdr = open(os.path.join(os.path.dirname(HERE), "include", "krd_host.h")).read()
+    for name in host.EXPORTS:
+        assert name + "(" in hdr, name
+        assert hasattr(L, name), name
+
+
+@pytest.mark.parametrize("name", list(OPTS))
+def test_ingest_matches_reference_fixture(gold, name):
+    tree, masses, ex = host.load_jplace([JP], **OPTS[name])
+    for k in ("parent", "child", "bl"):
+        assert np.array_equal(gold[f"{name}_{k}"], tree[k]), k
+    assert tree["root"] == int(gold[f"{name}_root"])
+    assert np.array_equal(gold[f"{name}_edge_num"], ex["edge_num"])
+    for k in ("off", "edge", "pos", "mass"):
+        assert np.array_equal(gold[f"{name}_{k}"], masses[k]), k      # bit-exact doubles
+    assert np.array_equal(gold[f"{name}_pendant"], ex["pendant"])
+    assert float(gold[f"{name}_diameter"]) == ex["diameter"]
+    assert ex["labels"] == [str(x) for x in gold["labels"]]
+
+
+def test_paths_files_and_dirs_are_pooled_and_sorted(gold):
+    files = sorted(glob.glob(JP + "/*"))
+    t1, m1, e1 = host.load_jplace(list(reversed(files)))
+    t2, m2, e2 = host.load_jplace([JP + "/"])
+    assert e1["labels"] == e2["labels"] == [str(x) for x in gold["labels"]]
+    assert np.array_equal(m1["mass"], m2["mass"])
+
+
+def test_threads_do_not_change_result():
+    a = host.load_jplace([JP], threads=1)
+    b = host.load_jplace([JP], threads=5)
+    for k in a[1]:
+        assert np.array_equal(a[1][k], b[1][k])
+
+
+def test_number_accumulation_matches_reference_quirk():
+    # genesis utils/formats/json/reader.cpp:266-296: dx += digit * pos with pos /= 10 — not correctly rounded.
+    def model(txt):
+        ip, fp = txt.split(".")
+        dx, pos = float(int(ip)), 1.0
+        for ch in fp:
+            pos /= 10.0
+            dx += int(ch) * pos
+        return dx
+    n_diff = 0
+    rng = np.random.default_rng(5)
+    for _ in range(2000):
+        txt = "%d.%s" % (rng.integers(0, 3), "".join(str(d) for d in rng.integers(0, 10, rng.integers(1, 18))))
+        got = host.parse_number(txt)
+        assert got == model(txt), txt
+        n_diff += got != float(txt)
+    assert n_diff > 0          # the quirk is real: some values differ from strtod by an ulp
+    assert host.parse_number("17") == 17.0
+    assert host.parse_number("-3") == -3.0
+    assert host.parse_number("1.5e3") == 1500.0
+    assert host.parse_number("25E-2") == 25 * (0.1 * 0.1)
+    assert host.parse_number("-0.125") == -0.125
+
+
+def _bad(tmp_path, mutate):
+    doc = __import__("json").load(open(os.path.join(JP, "s_a.jplace")))
+    mutate(doc)
+    p = tmp_path / "bad.jplace"
+    p.write_text(__import__("json").dumps(doc))
+    return [str(p)]
+
+
+@pytest.mark.parametrize("mutate,msg", [
+    (lambda d: d.pop("tree"), "does not contain a valid Newick tree at key 'tree'"),
+    (lambda d: d.pop("fields"), "does not contain field names at key 'fields'"),
+    (lambda d: d.pop("placements"), "does not contain pqueries at key 'placements'"),
+    (lambda d: d["fields"].remove("pendant_length") or [r.pop() for q in d["placements"] for r in q["p"]],
+     "does not contain necessary field 'pendant_length'"),
+    (lambda d: d["placements"][0]["p"][0].append(1), "different size than the fields name array"),
+    (lambda d: d["placements"][0]["p"][0].__setitem__(0, 9999), "does not correspond to any edge_num"),
+    (lambda d: d["placements"][0].update(n=["a"], nm=[["a", 1]]), "both an 'n' and an 'nm' key"),
+    (lambda d: [d["placements"][0].pop(k, None) for k in ("n", "nm", "m")], "neither an 'n' nor an 'nm' key"),
+    (lambda d: d["placements"][0].__setitem__("p", []), "does not contain any placements at key 'p'"),
+])
+def test_malformed_documents_raise_reference_messages(tmp_path, mutate, msg):
+    with pytest.raises(RuntimeError, match=msg.replace("'", ".")):
+        host.load_jplace(_bad(tmp_path, mutate))
+
+
+def test_different_topology_is_rejected(tmp_path):
+    doc = __import__("json").load(open(os.path.join(JP, "s_a.jplace")))
+    doc["tree"] = "((A:1{0},B:1{1}):1{2},C:1{3});"
+    for q in doc["placements"]:
+        for r in q["p"]:
+            r[0] = 0
+    p = tmp_path / "other.jplace"
+    p.write_text(__import__("json").dumps(doc))
+    with pytest.raises(RuntimeError, match="Sample reference trees do not have identical topology."):
+        host.load_jplace([os.path.join(JP, "s_a.jplace"), str(p)])
+
+
+@pytest.mark.parametrize("fmt", ["matrix", "list", "triangular"])
+@pytest.mark.parametrize("labels", [True, False])
+def test_matrix_writer_bytes(gold, tmp_path, fmt, labels):
+    want = open(os.path.join(GOLD, "csv", fmt + ("" if labels else "_nolabels") + ".csv"), "rb").read()
+    out = tmp_path / "m.csv"
+    n = host.write_matrix(out, gold["default_m_p1.0"], fmt.upper() if fmt == "list" else fmt,
+                          [str(x) for x in gold["labels"]] if labels else None, threads=3)
+    assert out.read_bytes() == want
+    assert n == len(want)
+    gz = tmp_path / "m.csv.gz"
+    host.write_matrix(gz, gold["default_m_p1.0"], fmt, [str(x) for x in gold["labels"]] if labels else None, gzip=True)
+    assert gzip.open(gz, "rb").read() == want
+
+
+def test_cfg1_csv_is_7847_bytes(tmp_path):
+    # gappa test/scripts/analyze-krd-1.sh:7 expects krd_matrix.csv of exactly 7847 bytes
+    g = np.load(os.path.join(GOLD, "cfg1.npz"))
+    out = tmp_path / "krd_matrix.csv"
+    host.write_matrix(out, g["m_p1.0"], "matrix", [str(x) for x in g["names"]])
+    want = open(os.path.join(GOLD, "csv", "cfg1_krd_matrix.csv"), "rb").read()
+    assert len(want) == 7847 and out.read_bytes() == want
+
+
+def test_cli_errors_before_any_gpu_work(tmp_path):
+    cli = host.CLI_PATH
+    r = subprocess.run([cli, "analyze", "krd", "--jplace-path", os.path.join(JP, "s_a.jplace"), "--out-dir", str(tmp_path)],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "Cannot run krd with fewer than 2 samples." in r.stderr     # krd.cpp:131-133
+    (tmp_path / "krd_matrix.csv").write_text("x")
+    r = subprocess.run([cli, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode != 0 and "Output file already exists" in r.stderr and "--allow-file-overwriting" in r.stderr
+    r = subprocess.run([cli, "analyze", "krd", "--jplace-path", JP, "--matrix-format", "nope"], capture_output=True, text=True)
+    assert r.returncode != 0
+    r = subprocess.run([cli, "analyze", "krd", "--jplace-path", str(tmp_path / "missing")], capture_output=True, text=True)
+    assert r.returncode != 0 and "does not exist" in r.stderr
+    r = subprocess.run([cli, "analyze", "krd", "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "--exponent" in r.stdout and "--point-mass" in r.stdout
+
+
+# ---- live against the compiled reference (build container only) ----------------------------------
+
+needs_ref = pytest.mark.skipif(not os.path.isdir(REF + "/test/data/jplace"), reason="/root/reference not present")
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(OPTS))
+def test_cfg1_ingest_equals_reference_live(name):
+    import oracle
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref not built")
+    paths = sorted(glob.glob(REF + "/test/data/jplace/*.jplace.gz"))
+    t1, m1, x1 = oracle.ref_jplace(paths, **OPTS[name])
+    t2, m2, x2 = host.load_jplace([REF + "/test/data/jplace"], **OPTS[name])
+    for k in ("parent", "child", "bl"):
+        assert np.array_equal(t1[k], t2[k])
+    for k in m1:
+        assert np.array_equal(m1[k], m2[k]), k
+    assert x1["diameter"] == x2["diameter"] and np.array_equal(x1["pendant"], x2["pendant"])
+
+
+@needs_ref
+def test_genesis_unit_test_documents_live():
+    import oracle
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref not built")
+    d = REF + "/libs/genesis/test/data/placement/"
+    for f in ("test_a", "test_b", "test_c", "version_1", "version_2", "version_3", "rooted", "unrooted", "duplicates_a", "duplicates_b"):
+        t1, m1, x1 = oracle.ref_jplace([d + f + ".jplace"])
+        t2, m2, x2 = host.load_jplace([d + f + ".jplace"])
+        for k in m1:
+            assert np.array_equal(m1[k], m2[k]), (f, k)
+        assert np.array_equal(t1["parent"], t2["parent"]) and np.array_equal(t1["bl"], t2["bl"]), f
+
+
+# ---- the CLI end to end on a B200 ------------------------------------------------------------------
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("args,csv,key", [
+    ([], "matrix.csv", "default_m_p1.0"),
+    (["--matrix-format", "triangular"], "triangular.csv", "default_m_p1.0"),
+    (["--matrix-format", "list", "--omit-matrix-labels"], "list_nolabels.csv", "default_m_p1.0"),
+    (["--normalize"], "matrix_normalized.csv", None),
+    (["--point-mass", "--krd-exponent", "2"], "matrix_pm_p2.csv", "pm_m_p2.0"),
+])
+def test_cli_end_to_end(gold, tmp_path, args, csv, key):
+    r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path / "o"),
+                        "--write-binary", str(tmp_path / "m.bin"), "--verbose"] + args, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (tmp_path / "o" / "krd_matrix.csv").read_bytes() == open(os.path.join(GOLD, "csv", csv), "rb").read()
+    got = np.fromfile(tmp_path / "m.bin").reshape(5, 5)
+    want = gold[key] if key else gold["default_m_p1.0"] / float(gold["default_diameter"])
+    assert np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)) <= 1e-10   # north_star tolerance, FP64
+    assert "Finished" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_exponent_error_message(tmp_path):
+    r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path), "--exponent", "-1"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "Invalid exponent value p for earth mover's distance calculation. Has to be > 0.0." in r.stderr   # emd.cpp:186-190

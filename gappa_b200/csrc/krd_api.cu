@@ -92,6 +92,8 @@ void krd_destroy(krd_handle* h)
     cudaFree(h->d_off);
     cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
+    cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
+    for (void* q : h->d_scratch) cudaFree(q);
     cudaFree(h->d_ws); cudaFree(h->d_sched); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     delete h;
@@ -188,7 +190,7 @@ static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank
     if (!h->F_valid) {
         krd_status st = build_F(h);
         if (st != KRD_OK) return st;
-        h->stats.launches += h->stats.levels + 2;  // memset + scatter + one scan per level
+        h->stats.launches += h->build_launches;
     }
     cudaEventRecord(h->ev[1], h->stream);
     krd_status st = run_pairs(h, p, divisor, rank, world, d_out, d_packed);

@@ -265,6 +265,8 @@ static krd_status sort_edge_pos(krd_handle* h, uint32_t* perm /*M*/, uint32_t* s
     return stable_pass_u32<int32_t>(h, h->d_edge, (uint32_t)std::max(h->E - 1, 1), M, p1.as<uint32_t>(), perm, sedge);
 }
 
+static krd_status prepare_tiled(krd_handle* h);
+
 krd_status prepare_masses(krd_handle* h)
 {
     const int64_t M = h->M;
@@ -373,7 +375,8 @@ krd_status prepare_masses(krd_handle* h)
     h->stats.n_segments = h->S;
     h->stats.ld_samples = h->ld;
     h->stats.f_bytes = (int64_t)h->S_pad * h->ld * 8;
-    return KRD_OK;
+    if (h->cfg.builder == 1) { h->tiled = false; return KRD_OK; }   // forced legacy builder (A/B tests)
+    return prepare_tiled(h);
 }
 
 
@@ -431,6 +434,214 @@ k_scan_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+//  K1 tiled (binned mode): F is written exactly once, straight from the CSR
+// ------------------------------------------------------------------------------------------------
+//
+// Every edge owns B+1 consecutive segments, so the (edge block) x (64 samples) rectangle of F is a
+// shared-memory tile.  Three steps, all HBM traffic coalesced:
+//   k_tile<TOTALS>   T[e][i] = mass of sample i on edge e (warp per sample reads its contiguous CSR
+//                    slice of the edge block; one writer per cell, sums in fixed order)
+//   k_subtree_level  M[e][i] = T[e][i] + sum_kids M[kid][i], leaves first — the postorder
+//                    accumulation of emd.cpp:145,167 on the small E x N matrix only
+//   k_tile<FILL>     slot masses -> tile, running distal -> proximal sum started from the mass
+//                    below the edge (emd.cpp:141-166), tile rows streamed to F.
+// Algorithmic bytes: 8*S*ld (F, written once) + 2 * 12*M (CSR read twice) + ~5 * 8*E*ld (T/M).
+constexpr int FT = 64;           // samples per tile
+constexpr int FT_MAX_ROWS = 96;  // tile rows (segments) -> 48 KB of shared memory, 4 CTAs per SM
+
+// blk_ptr[b][i] = first entry of sample i whose edge is >= b*EB (b = n_eblocks: end of the sample)
+__global__ void k_block_ptr(const int64_t* __restrict__ off, const int32_t* __restrict__ edge, int N, int n_eblocks, int EB,
+                            int64_t* __restrict__ blk_ptr)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= (int64_t)(n_eblocks + 1) * N) return;
+    const int b = (int)(g / N), i = (int)(g % N);
+    int64_t lo = off[i], hi = off[i + 1];
+    const int e0 = b * EB;
+    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (edge[mid] < e0) lo = mid + 1; else hi = mid; }
+    blk_ptr[g] = lo;
+}
+
+__global__ void k_slice_len(const int64_t* __restrict__ blk_ptr, int64_t n, int N, int64_t* __restrict__ len)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n) len[g] = blk_ptr[g + N] - blk_ptr[g];
+    else if (g == n) len[g] = 0;
+}
+
+// Tile-major copy of the CSR payload: entries ordered by (edge block, sample, segment), so that the
+// entries of one (edge block) x (64 samples) tile are ONE contiguous range.  Per entry only what K1
+// needs: the cell of the tile it lands in (row * 64 + sample-in-tile, 16 bit) and its mass.
+__global__ void k_tile_order(const uint32_t* __restrict__ sid, const int32_t* __restrict__ edge, const int32_t* __restrict__ slot,
+                             const double* __restrict__ mass, const int64_t* __restrict__ blk_ptr,
+                             const int64_t* __restrict__ tile_ptr, int64_t M, int N, int EB, int B1,
+                             uint16_t* __restrict__ cell, double* __restrict__ tmass)
+{
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const int i = (int)sid[m], e = edge[m], b = e / EB;
+    const int64_t g = (int64_t)b * N + i;
+    const int64_t dst = tile_ptr[g] + (m - blk_ptr[g]);
+    cell[dst] = (uint16_t)((((e - b * EB) * B1 + slot[m]) << 6) | (i & (FT - 1)));
+    tmass[dst] = mass[m];
+}
+
+constexpr int FTS = FT + 1;   // shared-memory row stride (doubles): odd, so that one sample's rows spread over the banks
+
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, const int64_t* __restrict__ tile_ptr,
+       int N, int64_t ld, int E, int EB, int B1, const double* __restrict__ Dsub, double* __restrict__ Msub,
+       double* __restrict__ F)
+{
+    extern __shared__ double tile[];   // [rows][FTS]
+    const int b = blockIdx.x, i0 = blockIdx.y * FT;
+    const int e0 = b * EB, ne = min(EB, E - e0);
+    const int rows = FILL ? ne * B1 : ne;
+    const int base = FILL ? e0 * B1 : e0;      // first global segment / edge of the tile
+    const int tid = threadIdx.x;
+    int64_t r0 = 0, r1 = 0;
+    if (i0 < N) { r0 = tile_ptr[(int64_t)b * N + i0]; r1 = tile_ptr[(int64_t)b * N + min(i0 + FT, N)]; }
+    for (int k = tid; k < rows * FTS; k += 256) tile[k] = 0.0;
+    __syncthreads();
+
+    // key of an entry: FILL -> its cell (segment row, sample); TOTALS -> (edge row, sample)
+    auto key_of = [&](uint32_t c) -> uint32_t { return FILL ? c : ((((c >> 6) / (uint32_t)B1) << 6) | (c & 63u)); };
+    for (int64_t k0 = r0 + tid; k0 < r1; k0 += 256 * 4) {
+        uint32_t c[4], cn[4];
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t k = k0 + u * 256;
+            const bool ok = k < r1;
+            c[u] = ok ? cell[k] : 0xFFFFFFFFu;
+            v[u] = ok ? tmass[k] : 0.0;
+            if (FILL) cn[u] = (ok && k > r0) ? cell[k - 1] : 0xFFFFFFFEu;        // previous entry
+            else cn[u] = (ok && k + 1 < r1) ? cell[k + 1] : 0xFFFFFFFEu;          // next entry
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (c[u] == 0xFFFFFFFFu) continue;
+            const int64_t k = k0 + u * 256;
+            const uint32_t key = key_of(c[u]);
+            if (cn[u] != 0xFFFFFFFEu && key_of(cn[u]) == key) continue;   // not the owner of its run
+            double sum = v[u];
+            if (FILL) {   // first entry of a run of equal segments sums forward (ascending position)
+                for (int64_t q = k + 1; q < r1 && cell[q] == c[u]; ++q) sum += tmass[q];
+            } else {      // last entry of the edge's run sums backward (distal -> proximal)
+                for (int64_t q = k - 1; q >= r0 && key_of(cell[q]) == key; --q) sum += tmass[q];
+            }
+            tile[(key >> 6) * FTS + (key & 63u)] = sum;
+        }
+    }
+    __syncthreads();
+
+    if (FILL) {
+        // thread = (edge group, sample): running sum down each edge, started from the mass below it
+        // (emd.cpp:141 current_mass = node_masses[secondary]; :149-166 distal -> proximal)
+        const int il = tid & (FT - 1), eg = tid / FT;
+        const double* dcol = Dsub + (int64_t)e0 * ld + i0 + il;
+        for (int el = eg; el < ne; el += 2 * (256 / FT)) {
+            const int el2 = el + 256 / FT;
+            double acc = dcol[(int64_t)el * ld];
+            double acc2 = (el2 < ne) ? dcol[(int64_t)el2 * ld] : 0.0;
+            double* t = tile + (size_t)el * B1 * FTS + il;
+            for (int s = B1 - 1; s >= 0; --s) { acc += t[s * FTS]; t[s * FTS] = acc; }
+            if (el2 < ne) {
+                double* t2 = tile + (size_t)el2 * B1 * FTS + il;
+                for (int s = B1 - 1; s >= 0; --s) { acc2 += t2[s * FTS]; t2[s * FTS] = acc2; }
+            }
+        }
+        __syncthreads();
+    }
+    double* dst = (FILL ? F : Msub) + (int64_t)base * ld + i0;
+    for (int k = tid; k < rows * FT; k += 256) {
+        const int r = k / FT, cc = k % FT;
+        dst[(int64_t)r * ld + cc] = tile[r * FTS + cc];
+    }
+}
+
+// D[e][i] = sum over child edges of M[kid][i]; M[e][i] = T[e][i] + D[e][i].  One launch per tree
+// level, leaves first (their D stays 0 from prepare_tiled's memset and their M is T).
+__global__ void __launch_bounds__(128)
+k_subtree_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count, const int32_t* __restrict__ kid_off,
+                const int32_t* __restrict__ kid_edge, int64_t ld, double* __restrict__ Msub, double* __restrict__ Dsub)
+{
+    const int64_t i = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
+    for (int le = blockIdx.x; le < lvl_count; le += gridDim.x) {
+        const int e = lvl_edges[lvl_begin + le];
+        const int k0 = kid_off[e], k1 = kid_off[e + 1];
+        if (k0 == k1) continue;
+        double acc = 0.0;
+        for (int k = k0; k < k1; ++k) acc += Msub[(int64_t)kid_edge[k] * ld + i];
+        Dsub[(int64_t)e * ld + i] = acc;
+        Msub[(int64_t)e * ld + i] += acc;
+    }
+}
+
+// K0 part of the tiled path: per-entry global segment ids and per-(edge block, sample) CSR pointers
+static krd_status prepare_tiled(krd_handle* h)
+{
+    h->tiled = false;
+    const int B1 = h->cfg.bins + 1;
+    if (h->cfg.bins <= 0 || B1 > FT_MAX_ROWS || h->E == 0 || h->N == 0) return KRD_OK;
+    h->EB = std::max(1, FT_MAX_ROWS / B1);
+    h->n_eblocks = (h->E + h->EB - 1) / h->EB;
+    const int64_t n_slices = (int64_t)h->n_eblocks * h->N;
+    krd_status st;
+    if ((st = reserve(h, (void**)&h->d_cell, (size_t)std::max<int64_t>(h->M, 1) * 2)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_tmass, (size_t)std::max<int64_t>(h->M, 1) * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_tile_ptr, (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
+    KRD_CUDA(h, cudaMemsetAsync(h->d_D, 0, (size_t)h->E * h->ld * 8, h->stream));   // leaf edges: nothing below
+    // scratch lives in the handle (grow-only): no cudaMalloc/cudaFree, no host sync on this path
+    if ((st = reserve(h, &h->d_scratch[0], (size_t)(n_slices + h->N) * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, &h->d_scratch[1], (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
+    int64_t* blk = static_cast<int64_t*>(h->d_scratch[0]);
+    int64_t* len = static_cast<int64_t*>(h->d_scratch[1]);
+    k_block_ptr<<<nblk(n_slices + h->N), 256, 0, h->stream>>>(h->d_off, h->d_edge, h->N, h->n_eblocks, h->EB, blk);
+    k_slice_len<<<nblk(n_slices + 1), 256, 0, h->stream>>>(blk, n_slices, h->N, len);
+    size_t bytes = 0;
+    KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(nullptr, bytes, len, h->d_tile_ptr, n_slices + 1, h->stream));
+    if ((st = reserve(h, &h->d_scratch[2], bytes)) != KRD_OK) return st;
+    KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(h->d_scratch[2], bytes, len, h->d_tile_ptr, n_slices + 1, h->stream));
+    if (h->M > 0)
+        k_tile_order<<<nblk(h->M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_slot, h->d_mass, blk, h->d_tile_ptr,
+                                                        h->M, h->N, h->EB, B1, h->d_cell, h->d_tmass);
+    KRD_CUDA(h, cudaGetLastError());
+    h->tiled = true;
+    return KRD_OK;
+}
+
+static krd_status build_F_tiled(krd_handle* h)
+{
+    const int B1 = h->cfg.bins + 1;
+    const size_t smem_fill = (size_t)h->EB * B1 * FTS * sizeof(double), smem_tot = (size_t)h->EB * FTS * sizeof(double);
+    static bool configured = false;
+    if (!configured) {
+        KRD_CUDA(h, cudaFuncSetAttribute(k_tile<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAX_ROWS * FTS * 8));
+        configured = true;
+    }
+    if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero
+        KRD_CUDA(h, cudaMemsetAsync(h->d_F + (size_t)h->S * h->ld, 0, (size_t)(h->S_pad - h->S) * h->ld * 8, h->stream));
+    dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ld / FT));
+    k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
+                                                      nullptr, h->d_M, nullptr);
+    const int L = (int)h->lvl_off.size() - 1;
+    for (int l = 1; l < L; ++l) {   // level 0 = leaf edges: nothing below them
+        const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
+        dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ld / 128));
+        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, h->ld, h->d_M, h->d_D);
+    }
+    k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
+                                                     h->d_D, nullptr, h->d_F);
+    KRD_CUDA(h, cudaGetLastError());
+    h->build_launches = L + 1;   // totals + (L-1) level passes + fill
+    return KRD_OK;
+}
+
 krd_status build_F(krd_handle* h)
 {
     const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
@@ -438,6 +649,11 @@ krd_status build_F(krd_handle* h)
         cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
         KRD_CUDA(h, cudaMalloc(&h->d_F, need));
         h->F_capacity = need;
+    }
+    if (h->tiled) {
+        krd_status st = build_F_tiled(h);
+        if (st == KRD_OK) h->F_valid = true;
+        return st;
     }
     KRD_CUDA(h, cudaMemsetAsync(h->d_F, 0, need, h->stream));
     if (h->M > 0)
@@ -451,6 +667,7 @@ krd_status build_F(krd_handle* h)
                                                     h->d_seg_off, h->ld, h->d_F);
     }
     KRD_CUDA(h, cudaGetLastError());
+    h->build_launches = L + 2;   // memset + scatter + one scan per level
     h->F_valid = true;
     return KRD_OK;
 }

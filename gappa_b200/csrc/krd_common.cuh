@@ -68,6 +68,17 @@ struct krd_handle {
     size_t   F_capacity = 0;
     bool F_valid = false;
 
+    // ---- tiled F builder (binned mode): see krd_build.cu "K1 tiled" ----
+    int32_t  build_launches = 0;   // kernels launched by the last build_F
+    bool     tiled = false;        // fast path usable for the resident masses
+    int32_t  EB = 0, n_eblocks = 0;   // edges per tile, number of edge blocks
+    uint16_t* d_cell = nullptr;    // M, tile-major order: (row << 6 | sample-in-tile) of every mass entry
+    double*  d_tmass = nullptr;    // M, tile-major order: the masses
+    int64_t* d_tile_ptr = nullptr; // n_eblocks x N (+1): first tile-major entry of (edge block b, sample i)
+    double*  d_M = nullptr;        // E x ld: subtree mass at the proximal end of every edge
+    void*    d_scratch[3] = {nullptr, nullptr, nullptr};   // K0 scratch, grow-only
+    double*  d_D = nullptr;        // E x ld: mass strictly below every edge (sum of its child edges' M)
+
     // ---- pair kernel workspace ----
     double* d_ws = nullptr;
     size_t  ws_capacity = 0;

@@ -33,7 +33,8 @@ EXPORTS = [
 
 
 class KrdConfig(C.Structure):
-    _fields_ = [("device", C.c_int), ("bins", C.c_int), ("split", C.c_int), ("reserved", C.c_int * 5)]
+    _fields_ = [("device", C.c_int), ("bins", C.c_int), ("split", C.c_int), ("builder", C.c_int),
+                ("reserved", C.c_int * 4)]
 
 
 class KrdStats(C.Structure):
@@ -127,10 +128,10 @@ def _ptr(a):
 class KrdPlan:
     """One handle of the C ABI: tree + masses resident in HBM, distance matrices on demand."""
 
-    def __init__(self, device=0, bins=0, split=0):
+    def __init__(self, device=0, bins=0, split=0, builder=0):
         self._L = lib()
         self._h = C.c_void_p()
-        cfg = KrdConfig(device=device, bins=bins, split=split)
+        cfg = KrdConfig(device=device, bins=bins, split=split, builder=builder)
         st = self._L.krd_create(C.byref(cfg), C.byref(self._h))
         if st != KRD_OK:
             raise KrdError(st, self._L.krd_last_error(None).decode())

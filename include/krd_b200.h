@@ -52,7 +52,9 @@ typedef struct krd_config {
     int bins;          /* 0 = exact positions (what `gappa analyze krd` does);
                           B>0 = mass_tree_binify_masses(tree, B) first (functions.cpp:222) */
     int split;         /* 0 = auto (one persistent CTA per SM); >0 forces the CTA count of the pair kernel */
-    int reserved[5];   /* must be 0 */
+    int builder;       /* F builder: 0 = auto (tiled single-write builder in binned mode), 1 = force the
+                          general scatter + level-scan builder (the only one in exact mode) */
+    int reserved[4];   /* must be 0 */
 } krd_config;
 
 typedef struct krd_stats {

@@ -90,7 +90,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
-    cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);

@@ -19,6 +19,9 @@ namespace krd {
 //  Tree preprocessing (host): validate, levels, child-edge lists
 // ------------------------------------------------------------------------------------------------
 
+constexpr int TOP_MAX = 256;    // edges finished by k_subtree_top (2 x 256 x 32 doubles = 128 KB of shared memory)
+constexpr int TOP_COLS = 32;    // samples per CTA of k_subtree_top
+
 krd_status build_tree(krd_handle* h)
 {
     const int E = h->E, n_nodes = E + 1;
@@ -79,6 +82,36 @@ krd_status build_tree(krd_handle* h)
     KRD_CUDA(h, cudaMemcpyAsync(h->d_kid_off, kid_off.data(), (size_t)(E + 1) * sizeof(int), cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaMemcpyAsync(h->d_kid_edge, kid_edge.data(), (size_t)E * sizeof(int), cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaMemcpyAsync(h->d_bl, h->bl.data(), (size_t)E * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    // ---- top of the tree: the trailing levels that together hold <= TOP_MAX edges ----
+    {
+        int lt = L;
+        while (lt > 1 && E - h->lvl_off[lt - 1] <= TOP_MAX) --lt;
+        h->top_level = lt;
+        h->top_edges = (L > 0) ? E - h->lvl_off[lt] : 0;
+        h->top_levels = L - lt;
+        std::vector<int32_t> pack;
+        if (h->top_edges > 0) {
+            const int base = h->lvl_off[lt], Kt = h->top_edges;
+            std::vector<int> top_index(E, -1);
+            for (int j = 0; j < Kt; ++j) top_index[lvl_edges[base + j]] = j;
+            std::vector<int32_t> koff(Kt + 1, 0), kids2;
+            for (int j = 0; j < Kt; ++j) {
+                const int e = lvl_edges[base + j];
+                for (int k = kid_off[e]; k < kid_off[e + 1]; ++k) if (top_index[kid_edge[k]] < 0) kids2.push_back(kid_edge[k]);
+                for (int k = kid_off[e]; k < kid_off[e + 1]; ++k) if (top_index[kid_edge[k]] >= 0) kids2.push_back(~top_index[kid_edge[k]]);
+                koff[j + 1] = (int32_t)kids2.size();
+            }
+            h->top_kids = (int32_t)kids2.size();
+            for (int j = 0; j < Kt; ++j) pack.push_back(lvl_edges[base + j]);
+            pack.insert(pack.end(), koff.begin(), koff.end());
+            pack.insert(pack.end(), kids2.begin(), kids2.end());
+            for (int l = lt; l <= L; ++l) pack.push_back(h->lvl_off[l] - base);
+        }
+        cudaFree(h->d_top); h->d_top = nullptr;
+        KRD_CUDA(h, cudaMalloc(&h->d_top, std::max<size_t>(pack.size(), 1) * sizeof(int32_t)));
+        KRD_CUDA(h, cudaMemcpyAsync(h->d_top, pack.data(), pack.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));  // host vectors above go out of scope
     h->stats.levels = L;
     return KRD_OK;
@@ -472,7 +505,7 @@ __global__ void k_slice_len(const int64_t* __restrict__ blk_ptr, int64_t n, int 
 
 // Tile-major copy of the CSR payload: entries ordered by (edge block, sample, segment), so that the
 // entries of one (edge block) x (64 samples) tile are ONE contiguous range.  Per entry only what K1
-// needs: the cell of the tile it lands in (row * 64 + sample-in-tile, 16 bit) and its mass.
+// needs: where it lands in its tile, 16 bits (edge-in-block << 11 | slot << 6 | sample-in-tile), and its mass.
 __global__ void k_tile_order(const uint32_t* __restrict__ sid, const int32_t* __restrict__ edge, const int32_t* __restrict__ slot,
                              const double* __restrict__ mass, const int64_t* __restrict__ blk_ptr,
                              const int64_t* __restrict__ tile_ptr, int64_t M, int N, int EB, int B1,
@@ -483,7 +516,7 @@ __global__ void k_tile_order(const uint32_t* __restrict__ sid, const int32_t* __
     const int i = (int)sid[m], e = edge[m], b = e / EB;
     const int64_t g = (int64_t)b * N + i;
     const int64_t dst = tile_ptr[g] + (m - blk_ptr[g]);
-    cell[dst] = (uint16_t)((((e - b * EB) * B1 + slot[m]) << 6) | (i & (FT - 1)));
+    cell[dst] = (uint16_t)(((e - b * EB) << 11) | (slot[m] << 6) | (i & (FT - 1)));
     tmass[dst] = mass[m];
 }
 
@@ -506,33 +539,38 @@ k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, cons
     for (int k = tid; k < rows * FTS; k += 256) tile[k] = 0.0;
     __syncthreads();
 
-    // key of an entry: FILL -> its cell (segment row, sample); TOTALS -> (edge row, sample)
-    auto key_of = [&](uint32_t c) -> uint32_t { return FILL ? c : ((((c >> 6) / (uint32_t)B1) << 6) | (c & 63u)); };
-    for (int64_t k0 = r0 + tid; k0 < r1; k0 += 256 * 4) {
+    // The tile's entries are one contiguous range, sorted by (sample, segment).  An entry's key is its
+    // cell (FILL: segment row, sample) or the cell without the slot bits (TOTALS: edge row, sample);
+    // entries of equal key are adjacent and the first (FILL) / last (TOTALS) of a run owns the sum.
+    const uint16_t* cp = cell + r0;
+    const double* mp = tmass + r0;
+    const int n = (int)(r1 - r0);
+    constexpr uint32_t KMASK = FILL ? 0xFFFFu : 0xF83Fu;
+    for (int k0 = tid; k0 < n; k0 += 256 * 4) {
         uint32_t c[4], cn[4];
         double v[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const int64_t k = k0 + u * 256;
-            const bool ok = k < r1;
-            c[u] = ok ? cell[k] : 0xFFFFFFFFu;
-            v[u] = ok ? tmass[k] : 0.0;
-            if (FILL) cn[u] = (ok && k > r0) ? cell[k - 1] : 0xFFFFFFFEu;        // previous entry
-            else cn[u] = (ok && k + 1 < r1) ? cell[k + 1] : 0xFFFFFFFEu;          // next entry
+            const int k = k0 + u * 256;
+            const bool ok = k < n;
+            c[u] = ok ? (uint32_t)cp[k] : 0x10000u;
+            v[u] = ok ? mp[k] : 0.0;
+            if (FILL) cn[u] = (ok && k > 0) ? (uint32_t)cp[k - 1] : 0x20000u;        // previous entry
+            else cn[u] = (ok && k + 1 < n) ? (uint32_t)cp[k + 1] : 0x20000u;          // next entry
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            if (c[u] == 0xFFFFFFFFu) continue;
-            const int64_t k = k0 + u * 256;
-            const uint32_t key = key_of(c[u]);
-            if (cn[u] != 0xFFFFFFFEu && key_of(cn[u]) == key) continue;   // not the owner of its run
+            const uint32_t key = c[u] & KMASK;
+            if (c[u] == 0x10000u || (cn[u] & (KMASK | 0x30000u)) == key) continue;   // padding / not the owner of its run
+            const int k = k0 + u * 256;
             double sum = v[u];
-            if (FILL) {   // first entry of a run of equal segments sums forward (ascending position)
-                for (int64_t q = k + 1; q < r1 && cell[q] == c[u]; ++q) sum += tmass[q];
-            } else {      // last entry of the edge's run sums backward (distal -> proximal)
-                for (int64_t q = k - 1; q >= r0 && key_of(cell[q]) == key; --q) sum += tmass[q];
+            if (FILL) {   // sums forward (ascending position)
+                for (int q = k + 1; q < n && (uint32_t)cp[q] == key; ++q) sum += mp[q];
+                tile[((key >> 11) * B1 + ((key >> 6) & 31u)) * FTS + (key & 63u)] = sum;
+            } else {      // sums backward (distal -> proximal)
+                for (int q = k - 1; q >= 0 && ((uint32_t)cp[q] & KMASK) == key; --q) sum += mp[q];
+                tile[(key >> 11) * FTS + (key & 63u)] = sum;
             }
-            tile[(key >> 6) * FTS + (key & 63u)] = sum;
         }
     }
     __syncthreads();
@@ -580,13 +618,56 @@ k_subtree_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_co
     }
 }
 
+// The last `n_lvl` levels of the tree (Kt <= TOP_MAX edges) in one launch: a CTA owns 32 sample
+// columns and keeps M and D of those edges in shared memory, so the level-by-level dependency costs a
+// CTA barrier instead of a kernel launch plus a chain of DRAM round trips.
+__global__ void __launch_bounds__(256)
+k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_t ld, double* __restrict__ Msub,
+              double* __restrict__ Dsub)
+{
+    extern __shared__ double sm[];
+    double* Msm = sm;                              // [Kt][TOP_COLS]
+    double* Dsm = sm + (size_t)Kt * TOP_COLS;      // [Kt][TOP_COLS]
+    int32_t* meta = reinterpret_cast<int32_t*>(Dsm + (size_t)Kt * TOP_COLS);
+    const int n_meta = Kt + (Kt + 1) + nk + (n_lvl + 1);
+    for (int k = threadIdx.x; k < n_meta; k += 256) meta[k] = top[k];
+    __syncthreads();
+    const int32_t* edge_id = meta;
+    const int32_t* koff = meta + Kt;
+    const int32_t* kid = koff + Kt + 1;
+    const int32_t* loff = kid + nk;
+    const int col = threadIdx.x & (TOP_COLS - 1), grp = threadIdx.x / TOP_COLS;
+    const int64_t gcol = (int64_t)blockIdx.x * TOP_COLS + col;
+
+    for (int j = grp; j < Kt; j += 256 / TOP_COLS) {      // everything that comes from below the top: independent loads
+        double d = 0.0;
+        for (int k = koff[j]; k < koff[j + 1]; ++k) if (kid[k] >= 0) d += Msub[(int64_t)kid[k] * ld + gcol];
+        Dsm[j * TOP_COLS + col] = d;
+        Msm[j * TOP_COLS + col] = Msub[(int64_t)edge_id[j] * ld + gcol];   // T
+    }
+    __syncthreads();
+    for (int l = 0; l < n_lvl; ++l) {
+        for (int j = loff[l] + grp; j < loff[l + 1]; j += 256 / TOP_COLS) {
+            double d = Dsm[j * TOP_COLS + col];
+            for (int k = koff[j]; k < koff[j + 1]; ++k) if (kid[k] < 0) d += Msm[(~kid[k]) * TOP_COLS + col];
+            Dsm[j * TOP_COLS + col] = d;
+            Msm[j * TOP_COLS + col] += d;
+        }
+        __syncthreads();
+    }
+    for (int j = grp; j < Kt; j += 256 / TOP_COLS) {
+        Msub[(int64_t)edge_id[j] * ld + gcol] = Msm[j * TOP_COLS + col];
+        Dsub[(int64_t)edge_id[j] * ld + gcol] = Dsm[j * TOP_COLS + col];
+    }
+}
+
 // K0 part of the tiled path: per-entry global segment ids and per-(edge block, sample) CSR pointers
 static krd_status prepare_tiled(krd_handle* h)
 {
     h->tiled = false;
     const int B1 = h->cfg.bins + 1;
-    if (h->cfg.bins <= 0 || B1 > FT_MAX_ROWS || h->E == 0 || h->N == 0) return KRD_OK;
-    h->EB = std::max(1, FT_MAX_ROWS / B1);
+    if (h->cfg.bins <= 0 || B1 > 32 || h->E == 0 || h->N == 0) return KRD_OK;   // 5 slot bits in the entry code
+    h->EB = std::max(1, std::min(32, FT_MAX_ROWS / B1));                        // 5 edge bits
     h->n_eblocks = (h->E + h->EB - 1) / h->EB;
     const int64_t n_slices = (int64_t)h->n_eblocks * h->N;
     krd_status st;
@@ -630,15 +711,30 @@ static krd_status build_F_tiled(krd_handle* h)
     k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
                                                       nullptr, h->d_M, nullptr);
     const int L = (int)h->lvl_off.size() - 1;
-    for (int l = 1; l < L; ++l) {   // level 0 = leaf edges: nothing below them
+    const size_t smem_top = (size_t)2 * h->top_edges * TOP_COLS * 8 +
+                            (size_t)(2 * h->top_edges + 1 + h->top_kids + h->top_levels + 1) * 4;
+    const bool use_top = h->top_edges > 0 && smem_top <= 190 * 1024;   // (a huge multifurcation would not fit)
+    const int l_end = use_top ? h->top_level : L;
+    int n_launch = 2;
+    for (int l = 1; l < l_end; ++l, ++n_launch) {   // level 0 = leaf edges: nothing below them
         const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
         dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ld / 128));
         k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, h->ld, h->d_M, h->d_D);
     }
+    if (use_top) {
+        static bool top_configured = false;
+        if (!top_configured) {
+            KRD_CUDA(h, cudaFuncSetAttribute(k_subtree_top, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            top_configured = true;
+        }
+        k_subtree_top<<<(unsigned)(h->ld / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
+                                                                                 h->ld, h->d_M, h->d_D);
+        ++n_launch;
+    }
     k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
                                                      h->d_D, nullptr, h->d_F);
     KRD_CUDA(h, cudaGetLastError());
-    h->build_launches = L + 1;   // totals + (L-1) level passes + fill
+    h->build_launches = n_launch;   // totals + level passes + top-of-tree + fill
     return KRD_OK;
 }
 

@@ -44,6 +44,9 @@ struct krd_handle {
     int32_t* d_kid_off = nullptr;     // E+1: child edges of edge e's child node
     int32_t* d_kid_edge = nullptr;
     double*  d_bl = nullptr;
+    // top of the tree (the last levels, <= TOP_MAX edges together): finished by ONE launch in shared memory
+    int32_t  top_level = 0, top_edges = 0, top_kids = 0, top_levels = 0;
+    int32_t* d_top = nullptr;         // [edge ids][kid offsets][kids: >=0 edge below the top, <0 ~index in the top][level offsets]
 
     // ---- masses ----
     int32_t N = 0;

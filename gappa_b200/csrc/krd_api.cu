@@ -90,7 +90,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
-    cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
@@ -224,6 +224,19 @@ krd_status krd_compute(krd_handle* h, double p, double divisor, double* out)
     if (st != KRD_OK) return st;
     KRD_CUDA(h, cudaMemcpyAsync(out, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (h->fix_pending) {   // Gram path: if the fix-up list overflowed, redo the matrix on the direct path
+        krd_stats tmp;
+        krd_get_stats(h, &tmp);
+        if (tmp.gram_fixups < 0) {
+            const int saved = h->cfg.p2_mode;
+            h->cfg.p2_mode = 1;
+            st = compute_impl(h, p, divisor, 0, 1, h->d_out_tmp, nullptr);
+            h->cfg.p2_mode = saved;
+            if (st != KRD_OK) return st;
+            KRD_CUDA(h, cudaMemcpyAsync(out, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
+            KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        }
+    }
     return KRD_OK;
 }
 
@@ -261,6 +274,13 @@ krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
         cudaEventElapsedTime(&h->stats.ms_build, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&h->stats.ms_pairs, h->ev[1], h->ev[2]);
         cudaEventElapsedTime(&h->stats.ms_epilogue, h->ev[2], h->ev[3]);
+    }
+    if (h->fix_pending && h->d_fix) {   // synchronises with the handle's stream
+        int cnt = 0;
+        if (cudaMemcpyAsync(&cnt, h->d_fix, sizeof(int), cudaMemcpyDeviceToHost, h->stream) == cudaSuccess &&
+            cudaStreamSynchronize(h->stream) == cudaSuccess)
+            h->stats.gram_fixups = (cnt > (1 << 20)) ? -1 : cnt;
+        h->fix_pending = false;
     }
     cudaGetLastError();
     *out = h->stats;

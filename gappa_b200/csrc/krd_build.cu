@@ -740,6 +740,7 @@ static krd_status build_F_tiled(krd_handle* h)
 
 krd_status build_F(krd_handle* h)
 {
+    h->norms_valid = false;
     const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
     if (need > h->F_capacity) {
         cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;

@@ -20,7 +20,9 @@ enum PairMode : int {
     MODE_P1 = 0,      // p == 1      : acc += len * |a-b|
     MODE_P2 = 1,      // p == 2      : acc += (sqrt(len)*(a-b))^2   (direct, FP64 cores)
     MODE_PHALF = 2,   // p == 0.5    : acc += len * sqrt(|a-b|)
-    MODE_GENERIC = 3  // any p > 0   : acc += len * |a-b|^p
+    MODE_GENERIC = 3, // any p > 0   : acc += len * |a-b|^p
+    MODE_P2G = 4      // p == 2      : Gram form on the FP64 tensor cores (DMMA): acc += len * (a-c)(b-c),
+                      //               W = |a-c|^2 + |b-c|^2 - 2 acc   (c = a reference column, cancels exactly in a-b)
 };
 
 struct Tile { int32_t i, j; };  // tile-block coordinates, i <= j
@@ -67,6 +69,12 @@ struct krd_handle {
     int32_t* d_seg_off = nullptr;  // E+1
     double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
     double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
+    double*  d_center = nullptr;   // S_pad: the reference column the Gram path subtracts (F[.][0])
+    double*  d_norm = nullptr;     // ld: sum_s len (F[s][i] - center[s])^2
+    double*  d_norm_part = nullptr;
+    bool     norms_valid = false;
+    void*    d_fix = nullptr;      // int4[1 + cap]: Gram-path cells to recompute directly
+    bool     fix_pending = false;  // a Gram compute was issued; its fix-up count has not been read back yet
     double*  d_F = nullptr;        // S_pad x ld, row = segment, N contiguous
     size_t   F_capacity = 0;
     bool F_valid = false;

@@ -26,15 +26,17 @@ namespace krd {
 constexpr int ST = 6;          // ring stages
 constexpr int LAG = 2;         // a stage is refilled LAG chunks after it was consumed
 constexpr int NT = 256;        // threads per CTA (8 warps; all compute, the TMA-issue role rotates)
-constexpr int STAGE_DOUBLES = 2 * KC * TILE + KC;  // A rows, B rows, len
+constexpr int STAGE_DOUBLES = 2 * KC * TILE + 2 * KC;  // A rows, B rows, len, centre (Gram mode)
 constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * ST * sizeof(uint64_t);
-constexpr double DIAG_COST = 0.68;  // measured cost of a diagonal-tile chunk relative to a full one (5/8 of the math)
+constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
+constexpr double DIAG_COST_SKIP = 0.68;  // measured cost of a diagonal-tile chunk relative to a full one (5/8 of the math)
 
 struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
 struct PairParams {
     const double* F;
     const double* len;     // len or sqrt(len) (MODE_P2)
+    const double* center;  // MODE_P2G: reference column subtracted from both operands
     const Tile* tiles;
     const WorkItem* items;
     const int32_t* cta_item_off;   // gridDim.x + 1
@@ -122,6 +124,38 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
     }
 }
 
+// ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
+// Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
+// thread, as in the CUDA-core modes).  Fragments (PTX ISA, mma.m8n8k4 .f64): A row-major 8x4 -> the
+// thread holds A[lane/4][lane%4]; B column-major 4x8 -> B[lane%4][lane/4]; C/D 8x8 -> row lane/4,
+// columns 2*(lane%4) + {0,1}.  Both operands are F[k][sample] rows of the same shared-memory ring.
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void chunk_gram(const double* __restrict__ sA, const double* __restrict__ sB,
+                                           const double* __restrict__ sL, int wr, int wc, int lane, double (&acc)[8][8])
+{
+    const int kq = lane & 3, rq = lane >> 2;
+#pragma unroll
+    for (int kk = 0; kk < KC; kk += 4) {
+        const double l = sL[kk + kq], c = sL[KC + kk + kq];
+        const double* pa = sA + (kk + kq) * TILE + wr + rq;
+        const double* pb = sB + (kk + kq) * TILE + wc + rq;
+        double a[4], b[8];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi) a[mi] = pa[8 * mi] - c;
+#pragma unroll
+        for (int ni = 0; ni < 8; ++ni) b[ni] = (pb[8 * ni] - c) * l;
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 8; ++ni) dmma884(acc[2 * mi][ni], acc[2 * mi + 1][ni], a[mi], b[ni]);
+    }
+}
+
 // ---- the persistent tile kernel -------------------------------------------------------------------
 
 template <int MODE>
@@ -166,12 +200,13 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             double* sB = sA + KC * TILE;
             double* sL = sB + KC * TILE;
             const int64_t k0 = (int64_t)p_chunk * KC;
-            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((dg ? 1 : 2) * KC * TILE * 8 + KC * 8));
+            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((dg ? 1 : 2) * KC * TILE * 8 + (MODE == MODE_P2G ? 2 : 1) * KC * 8));
             __syncwarp();
             const int r = lane & 15;
             if (lane < 16) tma_load_1d(sA + r * TILE, P.F + (int64_t)t.i * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
             else if (!dg) tma_load_1d(sB + r * TILE, P.F + (int64_t)t.j * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
             if (lane == 0) tma_load_1d(sL, P.len + k0, KC * 8, &full[s]);
+            if (MODE == MODE_P2G && lane == 1) tma_load_1d(sL + KC, P.center + k0, KC * 8, &full[s]);
         }
         ++p_flat;
         if (++p_chunk >= p_w.c1) {
@@ -186,7 +221,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = diag ? (rg >> 1) : 0;
+        const int qmin = (diag && MODE != MODE_P2G) ? (rg >> 1) : 0;
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -201,11 +236,15 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             const double* sL = sA + 2 * KC * TILE;
             const double* pa = sA + row0;
             const double* pb = sB + 2 * tx;
-            switch (qmin) {
-                case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, acc); break;
-                case 1: chunk_math<MODE, 1>(pa, pb, sL, P.p, acc); break;
-                case 2: chunk_math<MODE, 2>(pa, pb, sL, P.p, acc); break;
-                default: chunk_math<MODE, 3>(pa, pb, sL, P.p, acc); break;
+            if (MODE == MODE_P2G) {
+                chunk_gram(sA, sB, sL, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
+            } else {
+                switch (qmin) {
+                    case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, acc); break;
+                    case 1: chunk_math<MODE, 1>(pa, pb, sL, P.p, acc); break;
+                    case 2: chunk_math<MODE, 2>(pa, pb, sL, P.p, acc); break;
+                    default: chunk_math<MODE, 3>(pa, pb, sL, P.p, acc); break;
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
@@ -213,6 +252,17 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
 
         // partial tile -> workspace; row = row0 + r, col = 32*q + 2*tx + {0,1}
         double* wout = P.ws + (size_t)item * (size_t)(TILE * TILE);
+        if (MODE == MODE_P2G) {
+            // acc[2*mi + h][ni] = C fragment half h of DMMA (mi, ni): row 8*mi + lane/4, columns 8*ni + 2*(lane%4) + {0,1}
+            const int wr = 32 * (warp & 3), wc = 64 * (warp >> 2);
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 8; ++ni)
+                    *reinterpret_cast<double2*>(wout + (wr + 8 * mi + (lane >> 2)) * TILE + wc + 8 * ni + 2 * (lane & 3)) =
+                        make_double2(acc[2 * mi][ni], acc[2 * mi + 1][ni]);
+            continue;
+        }
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -231,7 +281,14 @@ struct EpiParams {
     double p, divisor;
     double* out;        // N x N row-major or nullptr
     double* packed;     // [n_tiles][TILE*TILE] or nullptr
+    const double* norm; // Gram mode: |a_i - c|^2 per sample, else nullptr
+    int4* fix;          // Gram mode: pairs whose Gram difference cancelled too much; fix[0].x = count, entries from fix[1]
+    int fix_cap;
 };
+
+// |a-b|^2 = |a|^2 + |b|^2 - 2ab loses  eps * (|a|^2+|b|^2) / |a-b|^2  relative accuracy.  Cells below this
+// ratio are recomputed directly by k_gram_fixup, which keeps the Gram path inside the 1e-10 bar.
+constexpr double GRAM_CANCEL_RATIO = 1e-3;
 
 __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
 {
@@ -241,15 +298,53 @@ __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
     for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
         double v = 0.0;
         for (int s = i0; s < i1; ++s) v += P.ws[(size_t)s * (size_t)(TILE * TILE) + idx];
-        if (P.p > 1.0) v = (P.p == 2.0) ? sqrt(v) : pow(v, inv_p);
-        v = v / P.divisor;
         const int r = idx / TILE, c = idx % TILE;
         const int64_t i = (int64_t)tile.i * TILE + r, j = (int64_t)tile.j * TILE + c;
+        if (P.norm) {   // |a-b|^2 from the Gram entry
+            const double nn = P.norm[i] + P.norm[j];
+            v = fmax(nn - 2.0 * v, 0.0);
+            if (i < j && j < P.N && v < GRAM_CANCEL_RATIO * nn) {
+                const int pos = atomicAdd(&P.fix[0].x, 1);
+                if (pos < P.fix_cap) P.fix[1 + pos] = make_int4((int)i, (int)j, (int)blockIdx.x, idx);
+            }
+        }
+        if (P.p > 1.0) v = (P.p == 2.0) ? sqrt(v) : pow(v, inv_p);
+        v = v / P.divisor;
         if (P.packed) P.packed[(size_t)blockIdx.x * (TILE * TILE) + idx] = (i < j) ? v : 0.0;
         if (P.out && i < P.N && j < P.N) {
             if (i < j) { P.out[i * P.N + j] = v; P.out[j * P.N + i] = v; }
             else if (i == j) P.out[i * P.N + i] = 0.0;
         }
+    }
+}
+
+// Direct recomputation of the flagged pairs of the Gram path: one CTA per pair, threads stride over the
+// segments, fixed-shape reduction (deterministic).  Normally a handful of pairs, often none.
+__global__ void __launch_bounds__(256)
+k_gram_fixup(const int4* __restrict__ fix, int fix_cap, const double* __restrict__ F, const double* __restrict__ len,
+             int64_t ld, int64_t S_pad, int N, double divisor, double* __restrict__ out, double* __restrict__ packed)
+{
+    __shared__ double red[8];
+    const int count = min(fix[0].x, fix_cap);
+    for (int q = blockIdx.x; q < count; q += gridDim.x) {
+        const int4 e = fix[1 + q];
+        double acc = 0.0;
+        for (int64_t s = threadIdx.x; s < S_pad; s += 256) {
+            const double d = F[s * ld + e.x] - F[s * ld + e.y];
+            acc = fma(len[s] * d, d, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double v = 0.0;
+            for (int w = 0; w < 8; ++w) v += red[w];
+            v = sqrt(v) / divisor;
+            if (packed) packed[(size_t)e.z * (TILE * TILE) + e.w] = v;
+            if (out) { out[(int64_t)e.x * N + e.y] = v; out[(int64_t)e.y * N + e.x] = v; }
+        }
+        __syncthreads();
     }
 }
 
@@ -271,6 +366,51 @@ __global__ void __launch_bounds__(256) k_unpack(const double* __restrict__ gathe
             else if (i == j) out[i * N + i] = 0.0;
         }
     }
+}
+
+// ---- Gram mode: reference column and per-sample squared norms -------------------------------------
+__global__ void k_center_col(const double* __restrict__ F, int64_t ld, int64_t S_pad, double* __restrict__ c)
+{
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < S_pad) c[s] = F[s * ld];
+}
+
+__global__ void __launch_bounds__(128)
+k_col_norm_part(const double* __restrict__ F, const double* __restrict__ len, const double* __restrict__ c, int64_t ld,
+                int64_t S_pad, int64_t rows_per_chunk, double* __restrict__ part)
+{
+    const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S_pad, s0 + rows_per_chunk);
+    double acc = 0.0;
+    for (int64_t s = s0; s < s1; ++s) { const double d = F[s * ld + i] - c[s]; acc = fma(len[s] * d, d, acc); }
+    part[(int64_t)blockIdx.y * ld + i] = acc;
+}
+
+__global__ void k_norm_reduce(const double* __restrict__ part, int64_t ld, int n_chunks, double* __restrict__ norm)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ld) return;
+    double acc = 0.0;
+    for (int ch = 0; ch < n_chunks; ++ch) acc += part[(int64_t)ch * ld + i];
+    norm[i] = acc;
+}
+
+static krd_status ensure_norms(krd_handle* h)
+{
+    if (h->norms_valid) return KRD_OK;
+    const int NCH = 64;
+    krd_status st;
+    if ((st = reserve(h, (void**)&h->d_center, (size_t)h->S_pad * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_norm, (size_t)h->ld * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_norm_part, (size_t)NCH * h->ld * 8)) != KRD_OK) return st;
+    const int64_t rpc = (h->S_pad + NCH - 1) / NCH;
+    k_center_col<<<(unsigned)((h->S_pad + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, h->d_center);
+    k_col_norm_part<<<dim3((unsigned)(h->ld / 128), NCH), 128, 0, h->stream>>>(h->d_F, h->d_len, h->d_center, h->ld, h->S_pad, rpc, h->d_norm_part);
+    k_norm_reduce<<<(unsigned)((h->ld + 255) / 256), 256, 0, h->stream>>>(h->d_norm_part, h->ld, NCH, h->d_norm);
+    KRD_CUDA(h, cudaGetLastError());
+    h->norms_valid = true;
+    h->stats.launches += 3;
+    return KRD_OK;
 }
 
 // ---- host side ------------------------------------------------------------------------------------
@@ -299,7 +439,7 @@ static krd_status ensure_tiles(krd_handle* h)
 }
 
 // Stream-K schedule: cut the cost axis (tiles x chunks, diagonal tiles cheaper) into `G` equal spans.
-static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, std::vector<WorkItem>& items,
+static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, double DIAG_COST, std::vector<WorkItem>& items,
                           std::vector<int32_t>& cta_off, std::vector<int32_t>& tile_off)
 {
     items.clear(); cta_off.assign(G + 1, 0); tile_off.assign(n_tiles + 1, 0);
@@ -360,12 +500,18 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     h->stats.pair_ctas = 0;
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
 
+    int mode = MODE_GENERIC;
+    if (p == 1.0) mode = MODE_P1; else if (p == 0.5) mode = MODE_PHALF;
+    else if (p == 2.0) mode = (h->cfg.p2_mode == 1) ? MODE_P2 : MODE_P2G;   // auto = Gram on the tensor cores + direct fix-ups
+    const double diag_cost = (mode == MODE_P2G) ? 1.0 : DIAG_COST_SKIP;
+    if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
+
     const int n_chunks = (int)(h->S_pad / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
-    const int64_t key = ((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G;
+    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 2 + (mode == MODE_P2G ? 1 : 0);
     if (key != h->sched_key) {
         std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
-        make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, items, cta_off, tile_off);
+        make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
         cudaFree(h->d_sched); h->d_sched = nullptr;
         const size_t b_items = items.size() * sizeof(WorkItem), b_cta = cta_off.size() * 4, b_tile = tile_off.size() * 4;
         KRD_CUDA(h, cudaMalloc(&h->d_sched, b_items + b_cta + b_tile));
@@ -388,10 +534,8 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         h->ws_capacity = ws_need;
     }
 
-    int mode = MODE_GENERIC;
-    if (p == 1.0) mode = MODE_P1; else if (p == 2.0) mode = MODE_P2; else if (p == 0.5) mode = MODE_PHALF;
-
     PairParams P;
+    P.center = h->d_center;
     P.F = h->d_F; P.len = (mode == MODE_P2) ? h->d_sqrt_len : h->d_len;
     P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p;
     cudaError_t e;
@@ -399,6 +543,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         case MODE_P1: e = launch_pairs<MODE_P1>(P, G, h->stream); break;
         case MODE_P2: e = launch_pairs<MODE_P2>(P, G, h->stream); break;
         case MODE_PHALF: e = launch_pairs<MODE_PHALF>(P, G, h->stream); break;
+        case MODE_P2G: e = launch_pairs<MODE_P2G>(P, G, h->stream); break;
         default: e = launch_pairs<MODE_GENERIC>(P, G, h->stream); break;
     }
     if (e != cudaSuccess) return cuda_fail(h, e, "k_pairs launch");
@@ -407,7 +552,20 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     EpiParams Q;
     Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.tile_item_off = d_tile_off; Q.n_tiles = n_tiles; Q.N = h->N;
     Q.p = p; Q.divisor = divisor; Q.out = d_out_matrix; Q.packed = d_out_packed;
+    Q.norm = nullptr; Q.fix = nullptr; Q.fix_cap = 0;
+    if (mode == MODE_P2G) {
+        krd_status sf = reserve(h, (void**)&h->d_fix, (size_t)(FIX_CAP + 1) * sizeof(int4));
+        if (sf != KRD_OK) return sf;
+        KRD_CUDA(h, cudaMemsetAsync(h->d_fix, 0, sizeof(int4), h->stream));
+        Q.norm = h->d_norm; Q.fix = static_cast<int4*>(h->d_fix); Q.fix_cap = FIX_CAP;
+    }
     k_epilogue<<<(unsigned)n_tiles, 256, 0, h->stream>>>(Q);
+    if (mode == MODE_P2G) {
+        k_gram_fixup<<<2 * h->num_sms, 256, 0, h->stream>>>(static_cast<const int4*>(h->d_fix), FIX_CAP, h->d_F, h->d_len, h->ld, h->S_pad,
+                                                            h->N, divisor, d_out_matrix, d_out_packed);
+        h->stats.launches += 1;
+        h->fix_pending = true;
+    }
     KRD_CUDA(h, cudaGetLastError());
     h->stats.split = (int32_t)((h->sched_items + n_tiles - 1) / n_tiles);
     h->stats.pair_ctas = G;

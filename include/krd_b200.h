@@ -54,7 +54,10 @@ typedef struct krd_config {
     int split;         /* 0 = auto (one persistent CTA per SM); >0 forces the CTA count of the pair kernel */
     int builder;       /* F builder: 0 = auto (tiled single-write builder in binned mode), 1 = force the
                           general scatter + level-scan builder (the only one in exact mode) */
-    int reserved[4];   /* must be 0 */
+    int p2_mode;       /* exponent 2: 0 = auto (= 2), 1 = direct (a-b)^2 on the FP64 CUDA cores,
+                          2 = Gram contraction |a|^2+|b|^2-2ab on the FP64 tensor cores (DMMA m8n8k4) with
+                          direct recomputation of the cells where the subtraction cancels */
+    int reserved[3];   /* must be 0 */
 } krd_config;
 
 typedef struct krd_stats {
@@ -71,6 +74,9 @@ typedef struct krd_stats {
     float   ms_pairs;       /* device time of the pair kernel alone in the last compute */
     float   ms_epilogue;    /* device time of the split-sum / root / mirror epilogue */
     float   reserved_f;
+    int32_t gram_fixups;    /* exponent 2, Gram path: pairs recomputed directly because |a|^2+|b|^2-2ab cancelled
+                               (-1: more than the list holds = the result is NOT within tolerance, use p2_mode 1) */
+    int32_t reserved_i;
 } krd_stats;
 
 krd_status  krd_create(const krd_config* cfg, krd_handle** out);

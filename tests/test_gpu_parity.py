@@ -87,6 +87,52 @@ def test_golden_synth_small(gb, bins, p):
     assert rel_err(gb.earth_movers_distance(tree, mass, p=p, bins=bins), z[f"m_b{bins}_p{p}"]) <= TOL
 
 
+@pytest.mark.parametrize("p2_mode", [1, 2])   # 1 = direct on FP64 CUDA cores, 2 = Gram on the FP64 tensor cores (DMMA) + fix-ups
+@pytest.mark.parametrize("fixture,bins,key", [("cfg1.npz", 0, "m_p2.0"), ("test_ab.npz", 0, "m_p2.0"),
+                                              ("synth_small.npz", 0, "m_b0_p2.0"), ("synth_small.npz", 4, "m_b4_p2.0")])
+def test_p2_both_paths_vs_reference(gb, p2_mode, fixture, bins, key):
+    tree, mass, z = load_golden(fixture)
+    plan = gb.KrdPlan(bins=bins, p2_mode=p2_mode)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    got = plan.compute(p=2.0)
+    assert rel_err(got, z[key]) <= TOL
+    assert np.array_equal(got, got.T) and np.all(np.diag(got) == 0.0)
+    assert np.array_equal(got, plan.compute(p=2.0))       # run-to-run bit identity
+    plan.close()
+
+
+def test_p2_gram_cancellation_is_repaired(gb, oracle_mod):
+    """Near-duplicate samples: |a|^2 + |b|^2 - 2ab cancels (distance ~1e-4 of the norms); the flagged cells
+    must be recomputed directly so that the Gram path stays inside the 1e-10 bar."""
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(300, seed=41)
+    base = synth.sample_masses(tree, 6, 800, seed=41)
+    off, edge, pos, mass = [0], [], [], []
+    rng = np.random.default_rng(41)
+    for i in range(6):
+        lo, hi = base["off"][i], base["off"][i + 1]
+        for rep in range(30):                      # 30 copies of each sample with masses jittered by 1e-4
+            m = base["mass"][lo:hi] * (1.0 + 1e-4 * rng.standard_normal(hi - lo) * (rep > 0))
+            edge.append(base["edge"][lo:hi]); pos.append(base["pos"][lo:hi]); mass.append(m / m.sum())
+            off.append(off[-1] + hi - lo)
+    masses = dict(off=np.array(off, np.int64), edge=np.concatenate(edge), pos=np.concatenate(pos), mass=np.concatenate(mass))
+    want = oracle_mod.port_matrix(tree, masses, p=2.0)
+    res = {}
+    for mode in (1, 2):
+        plan = gb.KrdPlan(p2_mode=mode)
+        plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+        plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
+        res[mode] = plan.compute(p=2.0)
+        st = plan.stats()
+        plan.close()
+        assert rel_err(res[mode], want) <= TOL, mode
+    # every within-group pair was flagged and repaired — except in sample 0's own group: sample 0 is the
+    # reference column, so those norms are as small as the distances and nothing cancels
+    assert st["gram_fixups"] == 5 * 30 * 29 // 2
+    assert want[0, 1] < 1e-2 * want[0, 31]              # the test really is in the cancellation regime
+
+
 @pytest.mark.parametrize("builder", [0, 1])   # 0 = tiled single-write builder, 1 = general scatter + level scan
 def test_F_matrix_matches_restatement_binned(gb, oracle_mod, builder):
     from gappa_b200 import synth

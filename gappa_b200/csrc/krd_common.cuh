@@ -21,6 +21,9 @@ enum PairMode : int {
     MODE_P2 = 1,      // p == 2      : acc += (sqrt(len)*(a-b))^2   (direct, FP64 cores)
     MODE_PHALF = 2,   // p == 0.5    : acc += len * sqrt(|a-b|)
     MODE_GENERIC = 3, // any p > 0   : acc += len * |a-b|^p
+    MODE_INT = 5,     // p = 5..16   : |a-b|^p by repeated multiplication
+    MODE_P3 = 6,      // p == 3      : acc += len * |d| * d^2
+    MODE_P4 = 7,      // p == 4      : acc += len * (d^2)^2
     MODE_P2G = 4      // p == 2      : Gram form on the FP64 tensor cores (DMMA): acc += len * (a-c)(b-c),
                       //               W = |a-c|^2 + |b-c|^2 - 2 acc   (c = a reference column, cancels exactly in a-b)
 };

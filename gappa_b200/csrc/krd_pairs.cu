@@ -82,20 +82,85 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
 
 // ---- inner operators ----------------------------------------------------------------------------
 
+// FP64 sqrt and pow written for the FP64 pipe's issue rate (the library versions spend > 100
+// instructions and a divergent slow path on the exact zeros that |F_i - F_j| is full of).
+//
+// sqrt: MUFU.RSQ64H seed (2^-22) + two Heron steps y += (x - y*y) * (r/2): error 2^-44, then rounding level.
+__device__ __forceinline__ double kr_sqrt(double x)   // x >= 0
+{
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));   // MUFU.RSQ64H: ~2^-22, no FP32 round trip; x = 0 -> +inf
+    double y = x * r;
+    const double hr = 0.5 * r;
+    y = fma(fma(-y, y, x), hr, y);
+    y = fma(fma(-y, y, x), hr, y);
+    return x > 1e-300 ? y : 0.0;                              // zero (and flushed subnormals): 0 * inf = NaN is replaced
+}
+
+// pow(x, p) = exp2(p * log2 x), x >= 0, p > 0.  Table-driven, all in FP64, relative error < 1e-14:
+//   log2: x = 2^e * m, m in [1,2); j = top 7 mantissa bits, c_j = interval midpoint, r = m/c_j - 1 (|r| <= 2^-8),
+//         log2 x = e + log2 c_j + r (A1 + r (A2 + ... r A6))            (truncation 3e-18)
+//   exp2: t = k/32 + g, |g| <= 1/64; 2^t = 2^(k>>5) * 2^((k&31)/32) * (1 + g (C1 + ... g C5))   (truncation 2e-15)
+// tab = [invc 128][logc 128][2^(i/32) 32] in shared memory (make_pow_tables() below).
+constexpr int POW_TAB = 128 + 128 + 32;
+__device__ double g_pow_tab[POW_TAB];
+
+__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)
+{
+    const long long ix = __double_as_longlong(x);
+    const int e = (int)(ix >> 52) - 1023;
+    const int j = (int)(ix >> 45) & 127;
+    const double m = __longlong_as_double((ix & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);
+    const double r = fma(m, tab[j], -1.0);
+    double q = fma(r, -0.24044917348149393, 0.28853900817779268);    // -1/(6 ln2), 1/(5 ln2)
+    q = fma(r, q, -0.36067376022224085);                               // -1/(4 ln2)
+    q = fma(r, q, 0.48089834696298783);                                //  1/(3 ln2)
+    q = fma(r, q, -0.72134752044448170);                               // -1/(2 ln2)
+    q = fma(r, q, 1.4426950408889634);                                 //  1/ln2
+    // e as a double without an I2F conversion: 2^52 + 2^31 + e is exact in the low mantissa bits
+    const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;
+    const double L = fma(r, q, tab[128 + j]) + ed;
+    double t = fmin(fmax(p * L, -1021.0), 1023.0);
+    const double MAGIC = 6755399441055744.0;                           // 1.5 * 2^52: rounds t*32 to an integer in the low bits
+    double kd = fma(t, 32.0, MAGIC);
+    const int k = __double2loint(kd);
+    kd -= MAGIC;
+    const double g = fma(kd, -0.03125, t);
+    double w = fma(g, 1.3333558146428443e-3, 9.6181291076284772e-3);   // ln2^5/120, ln2^4/24
+    w = fma(g, w, 5.5504108664821580e-2);                              // ln2^3/6
+    w = fma(g, w, 2.4022650695910071e-1);                              // ln2^2/2
+    w = fma(g, w, 6.9314718055994531e-1);                              // ln2
+    const double s0 = tab[256 + (k & 31)];
+    const double sc = __hiloint2double(__double2hiint(s0) + ((k >> 5) << 20), __double2loint(s0));
+    const double val = fma(sc, g * w, sc);
+    return x > 0.0 ? val : 0.0;
+}
+
+__device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uniform
+{
+    double r = (n & 1) ? x : 1.0, base = x;
+    while (n >>= 1) { base *= base; if (n & 1) r *= base; }
+    return r;
+}
+
 template <int MODE>
-__device__ __forceinline__ double pair_op(double a, double b, double l, double p, double acc)
+__device__ __forceinline__ double pair_op(double a, double b, double l, double p, const double* __restrict__ tab, double acc)
 {
     if (MODE == MODE_P1) return fma(l, fabs(a - b), acc);
     if (MODE == MODE_P2) { double d = a - b; return fma(d, d, acc); }   // operands pre-scaled by sqrt(len)
-    if (MODE == MODE_PHALF) return fma(l, sqrt(fabs(a - b)), acc);
-    return fma(l, pow(fabs(a - b), p), acc);
+    if (MODE == MODE_PHALF) return fma(l, kr_sqrt(fabs(a - b)), acc);
+    if (MODE == MODE_INT) return fma(l, kr_powi(fabs(a - b), (int)p), acc);
+    if (MODE == MODE_P3) { const double d = fabs(a - b); return fma(l * d, d * d, acc); }
+    if (MODE == MODE_P4) { const double d = a - b, d2 = d * d; return fma(l * d2, d2, acc); }
+    return fma(l, kr_pow(fabs(a - b), p, tab), acc);
 }
 
 // One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
 // (diagonal tiles: blocks that lie entirely below the diagonal).
 template <int MODE, int QMIN>
 __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const double* __restrict__ pb,
-                                           const double* __restrict__ sL, double p, double (&acc)[8][8])
+                                           const double* __restrict__ sL, double p, const double* __restrict__ tab,
+                                           double (&acc)[8][8])
 {
 #pragma unroll 4
     for (int kk = 0; kk < KC; ++kk) {
@@ -120,9 +185,53 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
-            for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, acc[r][cc]);
+            for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
     }
 }
+
+// Exponents whose inner operator is long (sqrt: ~12, pow: ~40 instructions per pair and segment): a fully
+// unrolled 8x8 body would be tens of thousands of instructions and thrash the instruction cache.  The
+// body is therefore two rows (16 independent operators = enough ILP for the FP64 pipe) in a rolled loop,
+// and the accumulator rows ROTATE through the registers (register files cannot be indexed dynamically).
+template <int MODE>
+__device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa, const double* __restrict__ pb,
+                                                  const double* __restrict__ sL, double p, const double* __restrict__ tab,
+                                                  double (&acc)[8][8])
+{
+#pragma unroll 1
+    for (int kk = 0; kk < KC; ++kk) {
+        double a[8], b[8];
+        const double l = sL[kk];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
+            a[2 * q] = va.x; a[2 * q + 1] = va.y;
+            const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
+            b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
+        }
+#pragma unroll 1
+        for (int it = 0; it < 4; ++it) {
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+                acc[0][cc] = pair_op<MODE>(a[0], b[cc], l, p, tab, acc[0][cc]);
+                acc[1][cc] = pair_op<MODE>(a[1], b[cc], l, p, tab, acc[1][cc]);
+            }
+            const double a0 = a[0], a1 = a[1];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) a[r] = a[r + 2];
+            a[6] = a0; a[7] = a1;
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+                const double t0 = acc[0][cc], t1 = acc[1][cc];
+#pragma unroll
+                for (int r = 0; r < 6; ++r) acc[r][cc] = acc[r + 2][cc];
+                acc[6][cc] = t0; acc[7][cc] = t1;
+            }
+        }
+    }
+}
+
+constexpr bool mode_is_rolled(int mode) { return mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC; }
 
 // ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
 // Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
@@ -165,6 +274,9 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     double* stage_base = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)ST * STAGE_DOUBLES * sizeof(double));
     uint64_t* empty = full + ST;
+
+    __shared__ double s_tab[MODE == MODE_GENERIC ? POW_TAB : 1];
+    if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB; k += NT) s_tab[k] = g_pow_tab[k];   // visible after the barrier below
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tx = lane & 15;
@@ -221,7 +333,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G) ? (rg >> 1) : 0;
+        const int qmin = (diag && MODE != MODE_P2G && !mode_is_rolled(MODE)) ? (rg >> 1) : 0;
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -238,12 +350,14 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             const double* pb = sB + 2 * tx;
             if (MODE == MODE_P2G) {
                 chunk_gram(sA, sB, sL, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
+            } else if (mode_is_rolled(MODE)) {
+                chunk_math_rolled<MODE>(pa, pb, sL, P.p, s_tab, acc);
             } else {
                 switch (qmin) {
-                    case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, acc); break;
-                    case 1: chunk_math<MODE, 1>(pa, pb, sL, P.p, acc); break;
-                    case 2: chunk_math<MODE, 2>(pa, pb, sL, P.p, acc); break;
-                    default: chunk_math<MODE, 3>(pa, pb, sL, P.p, acc); break;
+                    case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, s_tab, acc); break;
+                    case 1: chunk_math<MODE, 1>(pa, pb, sL, P.p, s_tab, acc); break;
+                    case 2: chunk_math<MODE, 2>(pa, pb, sL, P.p, s_tab, acc); break;
+                    default: chunk_math<MODE, 3>(pa, pb, sL, P.p, s_tab, acc); break;
                 }
             }
             __syncwarp();
@@ -472,6 +586,21 @@ static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, d
     for (int q = 1; q <= G; ++q) cta_off[q] = std::max(cta_off[q], cta_off[q - 1]);
 }
 
+static cudaError_t make_pow_tables()
+{
+    static bool done = false;   // per process; the table lives in this module's device memory (per device: re-upload is cheap)
+    double tab[POW_TAB];
+    for (int j = 0; j < 128; ++j) {
+        const long double c = 1.0L + ((long double)j + 0.5L) / 128.0L;
+        const double invc = (double)(1.0L / c);
+        tab[j] = invc;
+        tab[128 + j] = (double)(-log2l((long double)invc));   // consistent with the ROUNDED 1/c
+    }
+    for (int i = 0; i < 32; ++i) tab[256 + i] = (double)exp2l((long double)i / 32.0L);
+    (void)done;
+    return cudaMemcpyToSymbol(g_pow_tab, tab, sizeof tab);
+}
+
 template <int MODE>
 static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stream)
 {
@@ -502,13 +631,16 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
 
     int mode = MODE_GENERIC;
     if (p == 1.0) mode = MODE_P1; else if (p == 0.5) mode = MODE_PHALF;
+    else if (p == 3.0) mode = MODE_P3; else if (p == 4.0) mode = MODE_P4;
+    else if (p == std::floor(p) && p >= 5.0 && p <= 16.0) mode = MODE_INT;
     else if (p == 2.0) mode = (h->cfg.p2_mode == 1) ? MODE_P2 : MODE_P2G;   // auto = Gram on the tensor cores + direct fix-ups
-    const double diag_cost = (mode == MODE_P2G) ? 1.0 : DIAG_COST_SKIP;
+    const bool full_diag = (mode == MODE_P2G) || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
+    const double diag_cost = full_diag ? 1.0 : DIAG_COST_SKIP;
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 
     const int n_chunks = (int)(h->S_pad / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
-    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 2 + (mode == MODE_P2G ? 1 : 0);
+    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 2 + (full_diag ? 1 : 0);
     if (key != h->sched_key) {
         std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
         make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
@@ -544,7 +676,13 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         case MODE_P2: e = launch_pairs<MODE_P2>(P, G, h->stream); break;
         case MODE_PHALF: e = launch_pairs<MODE_PHALF>(P, G, h->stream); break;
         case MODE_P2G: e = launch_pairs<MODE_P2G>(P, G, h->stream); break;
-        default: e = launch_pairs<MODE_GENERIC>(P, G, h->stream); break;
+        case MODE_INT: e = launch_pairs<MODE_INT>(P, G, h->stream); break;
+        case MODE_P3: e = launch_pairs<MODE_P3>(P, G, h->stream); break;
+        case MODE_P4: e = launch_pairs<MODE_P4>(P, G, h->stream); break;
+        default:
+            e = make_pow_tables();
+            if (e == cudaSuccess) e = launch_pairs<MODE_GENERIC>(P, G, h->stream);
+            break;
     }
     if (e != cudaSuccess) return cuda_fail(h, e, "k_pairs launch");
     cudaEventRecord(h->ev[2], h->stream);

@@ -85,6 +85,17 @@ class ClockSampler:
         return out
 
 
+def traffic_from_profile(spec, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the pair kernel per launch, from the committed
+    `ncu --set full` capture of this workload (profiles/pair_kernel_traffic.json); None when there is none."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "pair_kernel_traffic.json")))
+        key = "%s_p%g" % (spec["name"], spec["p"])
+        return t[key]["bytes_per_launch"] if world == 1 and spec["samples"] == t[key]["samples"] else None
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def cpu_reference_rate(tree, masses, p, bins, target_seconds, threads=0):
     """Times the reference's own CPU implementation (oracle/_ref = compiled genesis, OpenMP over
     all host threads) — or the C port when _ref is absent — on a bounded sample: the first n
@@ -126,6 +137,9 @@ def run_reference(args):
     for k in ("samples", "edges", "placements", "bins", "p"):
         if getattr(args, k) is not None:
             spec[k] = getattr(args, k)
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    if args.samples is None and world > 1:     # same weak-scaling rule as the b200 arm
+        spec["samples"] = int(round(spec["samples"] * np.sqrt(world) / 128.0)) * 128
     # a bounded sample: only as many samples as the CPU can finish in a few seconds per step
     n_gen = min(spec["samples"], 160)
     spec_b, tree, masses = workloads.build(args.workload, n_samples=n_gen, **{k: spec[k] for k in ("edges", "placements", "bins", "p")})
@@ -140,7 +154,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": pairs_total / value * 1e3,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, **spec, "note": "ms_per_step extrapolated linearly in pairs from the bounded sample"},
         "cpu_baseline": info,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -159,7 +173,13 @@ def main():
     # ---- inputs (host, before CUDA is touched: generation forks worker processes) ----
     from gappa_b200 import workloads
     ncpu = os.cpu_count() or 1
-    spec, tree, masses = workloads.build(args.workload, workers=max(1, min(32, ncpu // world)), samples=args.samples,
+    # Weak scaling: the cohort grows with the GPU count so that every GPU keeps the pair count of the 1-GPU
+    # workload (pairs ~ samples^2): samples = base * sqrt(world), rounded to whole 128-sample tiles.
+    n_samples = args.samples
+    if n_samples is None and world > 1:
+        base = workloads.WORKLOADS[args.workload]["samples"]
+        n_samples = int(round(base * np.sqrt(world) / 128.0)) * 128
+    spec, tree, masses = workloads.build(args.workload, workers=max(1, min(32, ncpu // world)), samples=n_samples,
                                          edges=args.edges, placements=args.placements, bins=args.bins, p=args.p)
     N, p, bins = spec["samples"], spec["p"], spec["bins"]
     pairs = N * (N - 1) / 2
@@ -190,6 +210,14 @@ def main():
         shard = plan.shard_doubles(world)
         d_packed = torch.empty(shard, dtype=torch.float64, device="cuda")
         d_gath = torch.empty(shard * world, dtype=torch.float64, device="cuda")
+        # e2e ingest at N GPUs: every rank uploads 1/N of the mass entries over ITS PCIe link and the ranks
+        # all-gather the rest over NVLink (the one exchange step on the input side; F itself is built replicated)
+        M = int(h_edge.numel())
+        per = (M + world - 1) // world
+        lo, hi = min(rank * per, M), min((rank + 1) * per, M)
+        d_part = [torch.zeros(per, dtype=t.dtype, device="cuda") for t in (h_edge, h_pos, h_mass)]
+        d_full = [torch.empty(per * world, dtype=t.dtype, device="cuda") for t in (h_edge, h_pos, h_mass)]
+        h2d_bytes = (hi - lo) * 20 + h_off.numel() * 8
 
     def step_device():
         plan.invalidate_F()
@@ -201,10 +229,14 @@ def main():
             plan.unpack_shards(d_gath, d_out, world)
 
     def step_e2e():
-        plan.set_masses(h_off.numpy(), h_edge, h_pos, h_mass)
         if world == 1:
+            plan.set_masses(h_off.numpy(), h_edge, h_pos, h_mass)
             plan.compute(p=p, out=h_out)
         else:
+            for part, full, src in zip(d_part, d_full, (h_edge, h_pos, h_mass)):
+                part[: hi - lo].copy_(src[lo:hi], non_blocking=True)
+                dist.all_gather_into_tensor(full, part)
+            plan.set_masses_device(h_off.numpy(), d_full[0], d_full[1], d_full[2])
             plan.compute_shard(d_packed, rank, world, p=p)
             dist.all_gather_into_tensor(d_gath, d_packed)
             plan.unpack_shards(d_gath, d_out, world)
@@ -253,18 +285,20 @@ def main():
         executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((st["n_tiles"] - T) + 0.625 * T) * share
         line = {
             "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": spec["name"], "samples": N, "edges": spec["edges"], "placements_per_sample": spec["placements"],
                        "bins": bins, "p": p, "segments": int(S), "pairs": int(pairs), "masses": int(st["n_masses"]),
                        "l2": "inputs larger than L2 (F %.0f MB + split workspace)" % (st["f_bytes"] / 1e6),
-                       "parallelism": f"tiles/{world}" if world > 1 else "1 gpu"},
+                       "parallelism": (f"upper-triangular tiles/{world}, F replicated, NCCL all-gather of result tiles; "
+                                       f"weak scaling: samples = {workloads.WORKLOADS[args.workload]['samples']}*sqrt({world}) "
+                                       "rounded to 128") if world > 1 else "1 gpu"},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(N * N * 8)},
             "gpu_launches": int(st["launches"]) * args.steps,
             "clocks": clocks,
             "roofline": {"bound": "fp64", "kernel": "k_pairs<p=%g>" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": traffic_from_profile(spec, world),
                          "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
                                         % (peak_dfma, peak_dmma),
                          "mix_ceiling": peak_mix, "frac_of_mix_ceiling": achieved / peak_mix,

@@ -7,7 +7,8 @@ spec, tree, masses = workloads.build("cfg2")
 plan = gappa_b200.KrdPlan(bins=spec["bins"])
 plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
 plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
-for p in (1.0, 2.0, 0.5, 3.0, 4.0, 7.0, 1.7, 0.3):
+ps = [float(x) for x in sys.argv[1:]] or [1.0, 2.0, 0.5, 3.0, 4.0, 7.0, 1.7, 0.3]
+for p in ps:
     for _ in range(2):
         plan.compute(p=p)
     st = plan.stats()

@@ -733,15 +733,24 @@ int64_t krd_tile_count(int32_t n_samples)
     return T * (T + 1) / 2;
 }
 
-// diagonal-major: every contiguous range mixes tile rows and columns evenly, so contiguous
-// per-rank shares have near-equal cost (only the first rank(s) hold the cheaper diagonal tiles).
+// Off-diagonal tiles in diagonal-major order ((i,i+1) for all i, then (i,i+2), ...: every contiguous
+// range mixes tile rows and columns evenly), with the T cheaper diagonal tiles spread evenly through
+// the list — so that equal-COUNT contiguous shares (one per rank) are also equal-COST shares.
 krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j)
 {
     if (n_samples < 0 || !tile_i || !tile_j) return KRD_ERR_INVALID_ARGUMENT;
-    const int T = (n_samples + krd::TILE - 1) / krd::TILE;
-    int64_t k = 0;
-    for (int d = 0; d < T; ++d)
-        for (int i = 0; i + d < T; ++i, ++k) { tile_i[k] = i; tile_j[k] = i + d; }
+    const int64_t T = (n_samples + krd::TILE - 1) / krd::TILE;
+    const int64_t n_off = T * (T - 1) / 2;
+    int64_t k = 0, q = 0;          // q: off-diagonal tiles emitted so far
+    int d = 1, i = 0;              // next off-diagonal tile (i, i+d)
+    for (int64_t g = 0; g < T; ++g) {
+        tile_i[k] = (int32_t)g; tile_j[k] = (int32_t)g; ++k;
+        const int64_t end = n_off * (g + 1) / T;
+        for (; q < end; ++q, ++k) {
+            tile_i[k] = i; tile_j[k] = i + d;
+            if (++i + d >= T) { i = 0; ++d; }
+        }
+    }
     return KRD_OK;
 }
 

@@ -244,7 +244,7 @@ TILE = 128
 
 
 def tile_list(n_samples):
-    """Upper-triangular 128x128 tile coordinates in the library's (diagonal-major) order."""
+    """Upper-triangular 128x128 tile coordinates in the library's order (diagonal tiles interleaved, see krd_b200.h)."""
     n = int(lib().krd_tile_count(n_samples))
     ti = np.zeros(n, np.int32); tj = np.zeros(n, np.int32)
     lib().krd_tile_list(n_samples, _ptr(ti), _ptr(tj))

@@ -121,8 +121,9 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
 krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out);
 
 /* Host-only helpers (no GPU needed) describing the sharding, so that callers and tests can reason
- * about it: the upper triangle of 128x128 tiles in diagonal-major order (all (i,i), then (i,i+1), ...),
- * and the contiguous share [t0,t1) of that list owned by `rank`. */
+ * about it: the upper triangle of 128x128 tiles (off-diagonal tiles in diagonal-major order (i,i+1), (i,i+2), ...
+ * with the cheaper diagonal tiles (i,i) spread evenly through the list, so that equal-count shares are
+ * equal-cost shares), and the contiguous share [t0,t1) of that list owned by `rank`. */
 int64_t    krd_tile_count(int32_t n_samples);
 krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j);
 void       krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1);

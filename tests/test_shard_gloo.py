@@ -1,5 +1,5 @@
 """CPU test (gloo, world_size 2 and 3) of the multi-GPU sharding contract: contiguous shares of the
-diagonal-major tile list (host-only C-ABI helpers), equal-size packed tiles, all-gather, unpack.
+tile list (host-only C-ABI helpers), equal-size packed tiles, all-gather, unpack.
 The per-rank tile contents come from the CPU oracle standing in for the pair kernel; what is under
 test is the partition / pack / gather / unpack logic that bench.py runs over NCCL."""
 import os

@@ -29,7 +29,7 @@ constexpr int NT = 256;        // threads per CTA (8 warps; all compute, the TMA
 constexpr int STAGE_DOUBLES = 2 * KC * TILE + 2 * KC;  // A rows, B rows, len, centre (Gram mode)
 constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * ST * sizeof(uint64_t);
 constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
-constexpr double DIAG_COST_SKIP = 0.68;  // measured cost of a diagonal-tile chunk relative to a full one (5/8 of the math)
+constexpr double DIAG_COST_SKIP = 0.705;  // measured (profiles/cta_balance.py) cost of a diagonal-tile chunk relative to a full one (5/8 of the math, same pipeline overheads)
 
 struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
@@ -102,6 +102,9 @@ __device__ __forceinline__ double kr_sqrt(double x)   // x >= 0
 //         log2 x = e + log2 c_j + r (A1 + r (A2 + ... r A6))            (truncation 3e-18)
 //   exp2: t = k/32 + g, |g| <= 1/64; 2^t = 2^(k>>5) * 2^((k&31)/32) * (1 + g (C1 + ... g C5))   (truncation 2e-15)
 // tab = [invc 128][logc 128][2^(i/32) 32] in shared memory (make_pow_tables() below).
+// per-CTA (start, end, first item, last item) of the last pair launch in %globaltimer ns — tuning aid, read by krd_debug_cta_times
+__device__ unsigned long long g_cta_time[4 * 1024];
+
 constexpr int POW_TAB = 128 + 128 + 32;
 __device__ double g_pow_tab[POW_TAB];
 
@@ -287,6 +290,10 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
 
     const int it0 = P.cta_item_off[blockIdx.x], it1 = P.cta_item_off[blockIdx.x + 1];
     if (it0 == it1) return;
+    if (threadIdx.x == 0 && blockIdx.x < 1024) {
+        unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        g_cta_time[4 * blockIdx.x] = t; g_cta_time[4 * blockIdx.x + 2] = it0; g_cta_time[4 * blockIdx.x + 3] = it1;
+    }
 
     if (tid == 0) {
         for (int s = 0; s < ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NT / 32); }
@@ -382,6 +389,11 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
 #pragma unroll
             for (int q = 0; q < 4; ++q)
                 *reinterpret_cast<double2*>(wout + (row0 + r) * TILE + 32 * q + 2 * tx) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && blockIdx.x < 1024) {
+        unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        g_cta_time[4 * blockIdx.x + 1] = t;
     }
 }
 
@@ -752,6 +764,12 @@ krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j)
         }
     }
     return KRD_OK;
+}
+
+/* tuning aid (not part of the product surface): per-CTA start/end (ns) and item range of the last pair launch */
+int krd_debug_cta_times(unsigned long long* out, int n_ctas)
+{
+    return (int)cudaMemcpyFromSymbol(out, krd::g_cta_time, sizeof(unsigned long long) * 4 * (size_t)std::min(n_ctas, 1024));
 }
 
 void krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1)

@@ -90,7 +90,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
-    cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
@@ -243,7 +243,7 @@ krd_status krd_compute(krd_handle* h, double p, double divisor, double* out)
 int64_t krd_shard_doubles(const krd_handle* h, int32_t world)
 {
     if (!h || world < 1 || !h->have_masses) return -1;
-    const int64_t T = h->ld / TILE;
+    const int64_t T = (h->N + TILE - 1) / TILE;
     return tiles_per_rank(T * (T + 1) / 2, world) * TILE * TILE;
 }
 
@@ -285,6 +285,16 @@ krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
     cudaGetLastError();
     *out = h->stats;
     return KRD_OK;
+}
+
+krd_status krd_squash(krd_handle* h, double p, krd_merger* out)
+{
+    krd_status st = check_compute(h, p, 1.0);
+    if (st != KRD_OK) return st;
+    if (h->N < 2) return fail(h, KRD_ERR_TOO_FEW_SAMPLES, "Squash clustering needs at least 2 samples.");
+    if (!out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    return run_squash(h, p, out);
 }
 
 krd_status krd_invalidate_F(krd_handle* h)

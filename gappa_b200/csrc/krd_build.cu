@@ -404,7 +404,7 @@ krd_status prepare_masses(krd_handle* h)
     KRD_CUDA(h, cudaGetLastError());
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
 
-    h->ld = ((N + TILE - 1) / TILE) * TILE;
+    h->ld = ((N + h->extra_cols + TILE - 1) / TILE) * TILE;
     h->stats.n_segments = h->S;
     h->stats.ld_samples = h->ld;
     h->stats.f_bytes = (int64_t)h->S_pad * h->ld * 8;

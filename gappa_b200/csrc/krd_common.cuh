@@ -68,7 +68,8 @@ struct krd_handle {
 
     // ---- segments + dense matrix ----
     int64_t S = 0, S_pad = 0;
-    int32_t ld = 0;              // padded sample count (multiple of TILE)
+    int32_t ld = 0;              // column stride of F: N (+ extra_cols) rounded up to TILE
+    int32_t extra_cols = 0;      // columns reserved after the samples (squash clustering: one per merged cluster)
     int32_t* d_seg_off = nullptr;  // E+1
     double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
     double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
@@ -102,6 +103,8 @@ struct krd_handle {
     int64_t sched_key = -1, sched_items = 0, sched_cta_bytes = 0;
     int64_t n_tiles_alloc = 0;
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
+    double* d_out_tmp_sq = nullptr;   // squash clustering: initial N*N distances
+    void*   d_squash = nullptr;       // squash clustering state (distance matrix of 2N-1 clusters, counts, mergers, ...)
     size_t  out_tmp_capacity = 0;
 
     std::unordered_map<void**, size_t> caps;   // capacities of buffers managed by krd::reserve
@@ -133,6 +136,9 @@ krd_status build_F(krd_handle* h);                    // K1
 krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
                      double* d_out_matrix, double* d_out_packed);
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
+
+// krd_squash.cu
+krd_status run_squash(krd_handle* h, double p, krd_merger* out);
 int64_t tiles_per_rank(int64_t n_tiles, int world);
 
 }  // namespace krd

@@ -20,6 +20,7 @@
 #include <cmath>
 
 #include "krd_common.cuh"
+#include "krd_ops.cuh"
 
 namespace krd {
 
@@ -82,81 +83,8 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
 
 // ---- inner operators ----------------------------------------------------------------------------
 
-// FP64 sqrt and pow written for the FP64 pipe's issue rate (the library versions spend > 100
-// instructions and a divergent slow path on the exact zeros that |F_i - F_j| is full of).
-//
-// sqrt: MUFU.RSQ64H seed (2^-22) + two Heron steps y += (x - y*y) * (r/2): error 2^-44, then rounding level.
-__device__ __forceinline__ double kr_sqrt(double x)   // x >= 0
-{
-    double r;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));   // MUFU.RSQ64H: ~2^-22, no FP32 round trip; x = 0 -> +inf
-    double y = x * r;
-    const double hr = 0.5 * r;
-    y = fma(fma(-y, y, x), hr, y);
-    y = fma(fma(-y, y, x), hr, y);
-    return x > 1e-300 ? y : 0.0;                              // zero (and flushed subnormals): 0 * inf = NaN is replaced
-}
-
-// pow(x, p) = exp2(p * log2 x), x >= 0, p > 0.  Table-driven, all in FP64, relative error < 1e-14:
-//   log2: x = 2^e * m, m in [1,2); j = top 7 mantissa bits, c_j = interval midpoint, r = m/c_j - 1 (|r| <= 2^-8),
-//         log2 x = e + log2 c_j + r (A1 + r (A2 + ... r A6))            (truncation 3e-18)
-//   exp2: t = k/32 + g, |g| <= 1/64; 2^t = 2^(k>>5) * 2^((k&31)/32) * (1 + g (C1 + ... g C5))   (truncation 2e-15)
-// tab = [invc 128][logc 128][2^(i/32) 32] in shared memory (make_pow_tables() below).
 // per-CTA (start, end, first item, last item) of the last pair launch in %globaltimer ns — tuning aid, read by krd_debug_cta_times
 __device__ unsigned long long g_cta_time[4 * 1024];
-
-constexpr int POW_TAB = 128 + 128 + 32;
-__device__ double g_pow_tab[POW_TAB];
-
-__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)
-{
-    const long long ix = __double_as_longlong(x);
-    const int e = (int)(ix >> 52) - 1023;
-    const int j = (int)(ix >> 45) & 127;
-    const double m = __longlong_as_double((ix & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);
-    const double r = fma(m, tab[j], -1.0);
-    double q = fma(r, -0.24044917348149393, 0.28853900817779268);    // -1/(6 ln2), 1/(5 ln2)
-    q = fma(r, q, -0.36067376022224085);                               // -1/(4 ln2)
-    q = fma(r, q, 0.48089834696298783);                                //  1/(3 ln2)
-    q = fma(r, q, -0.72134752044448170);                               // -1/(2 ln2)
-    q = fma(r, q, 1.4426950408889634);                                 //  1/ln2
-    // e as a double without an I2F conversion: 2^52 + 2^31 + e is exact in the low mantissa bits
-    const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;
-    const double L = fma(r, q, tab[128 + j]) + ed;
-    double t = fmin(fmax(p * L, -1021.0), 1023.0);
-    const double MAGIC = 6755399441055744.0;                           // 1.5 * 2^52: rounds t*32 to an integer in the low bits
-    double kd = fma(t, 32.0, MAGIC);
-    const int k = __double2loint(kd);
-    kd -= MAGIC;
-    const double g = fma(kd, -0.03125, t);
-    double w = fma(g, 1.3333558146428443e-3, 9.6181291076284772e-3);   // ln2^5/120, ln2^4/24
-    w = fma(g, w, 5.5504108664821580e-2);                              // ln2^3/6
-    w = fma(g, w, 2.4022650695910071e-1);                              // ln2^2/2
-    w = fma(g, w, 6.9314718055994531e-1);                              // ln2
-    const double s0 = tab[256 + (k & 31)];
-    const double sc = __hiloint2double(__double2hiint(s0) + ((k >> 5) << 20), __double2loint(s0));
-    const double val = fma(sc, g * w, sc);
-    return x > 0.0 ? val : 0.0;
-}
-
-__device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uniform
-{
-    double r = (n & 1) ? x : 1.0, base = x;
-    while (n >>= 1) { base *= base; if (n & 1) r *= base; }
-    return r;
-}
-
-template <int MODE>
-__device__ __forceinline__ double pair_op(double a, double b, double l, double p, const double* __restrict__ tab, double acc)
-{
-    if (MODE == MODE_P1) return fma(l, fabs(a - b), acc);
-    if (MODE == MODE_P2) { double d = a - b; return fma(d, d, acc); }   // operands pre-scaled by sqrt(len)
-    if (MODE == MODE_PHALF) return fma(l, kr_sqrt(fabs(a - b)), acc);
-    if (MODE == MODE_INT) return fma(l, kr_powi(fabs(a - b), (int)p), acc);
-    if (MODE == MODE_P3) { const double d = fabs(a - b); return fma(l * d, d * d, acc); }
-    if (MODE == MODE_P4) { const double d = a - b, d2 = d * d; return fma(l * d2, d2, acc); }
-    return fma(l, kr_pow(fabs(a - b), p, tab), acc);
-}
 
 // One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
 // (diagonal tiles: blocks that lie entirely below the diagonal).
@@ -545,7 +473,7 @@ int64_t tiles_per_rank(int64_t n_tiles, int world) { return (n_tiles + world - 1
 
 static krd_status ensure_tiles(krd_handle* h)
 {
-    const int T = h->ld / TILE;
+    const int T = (h->N + TILE - 1) / TILE;   // (ld may be wider than N: squash clustering appends cluster columns)
     const int64_t n_tiles = (int64_t)T * (T + 1) / 2;
     if (h->n_tiles_alloc == n_tiles && h->d_tiles) return KRD_OK;
     h->h_tiles.resize((size_t)n_tiles);
@@ -598,21 +526,6 @@ static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, d
     for (int q = 1; q <= G; ++q) cta_off[q] = std::max(cta_off[q], cta_off[q - 1]);
 }
 
-static cudaError_t make_pow_tables()
-{
-    static bool done = false;   // per process; the table lives in this module's device memory (per device: re-upload is cheap)
-    double tab[POW_TAB];
-    for (int j = 0; j < 128; ++j) {
-        const long double c = 1.0L + ((long double)j + 0.5L) / 128.0L;
-        const double invc = (double)(1.0L / c);
-        tab[j] = invc;
-        tab[128 + j] = (double)(-log2l((long double)invc));   // consistent with the ROUNDED 1/c
-    }
-    for (int i = 0; i < 32; ++i) tab[256 + i] = (double)exp2l((long double)i / 32.0L);
-    (void)done;
-    return cudaMemcpyToSymbol(g_pow_tab, tab, sizeof tab);
-}
-
 template <int MODE>
 static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stream)
 {
@@ -641,11 +554,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     h->stats.pair_ctas = 0;
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
 
-    int mode = MODE_GENERIC;
-    if (p == 1.0) mode = MODE_P1; else if (p == 0.5) mode = MODE_PHALF;
-    else if (p == 3.0) mode = MODE_P3; else if (p == 4.0) mode = MODE_P4;
-    else if (p == std::floor(p) && p >= 5.0 && p <= 16.0) mode = MODE_INT;
-    else if (p == 2.0) mode = (h->cfg.p2_mode == 1) ? MODE_P2 : MODE_P2G;   // auto = Gram on the tensor cores + direct fix-ups
+    const int mode = mode_for_exponent(p, h->cfg.p2_mode != 1);   // p = 2: auto = Gram on the tensor cores + direct fix-ups
     const bool full_diag = (mode == MODE_P2G) || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
     const double diag_cost = full_diag ? 1.0 : DIAG_COST_SKIP;
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -47,6 +47,21 @@ class KrdStats(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+MERGER_DTYPE = np.dtype([("index_a", np.int32), ("index_b", np.int32), ("distance_a", np.float64), ("distance_b", np.float64)])
+
+
+def squash_tree_string(labels, mergers):
+    """SquashClustering::tree_string (squash_clustering.cpp:251-274): Newick of the cluster tree; std::to_string(double) = %f."""
+    lst = list(labels)
+    n = len(lst)
+    for i, m in enumerate(mergers):
+        a = "%s:%f" % (lst[m["index_a"]], m["distance_a"])
+        b = "%s:%f" % (lst[m["index_b"]], m["distance_b"])
+        lst[m["index_a"]] = ""; lst[m["index_b"]] = ""
+        lst.append("(%s,%s)%d" % (a, b, i + n))
+    return lst[-1] + ";"
 
 
 class KrdError(RuntimeError):
@@ -93,6 +108,8 @@ def lib():
     L.krd_compute_shard.argtypes = [vp, dbl, dbl, i32, i32, vp]
     L.krd_unpack_shards.restype = C.c_int
     L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
+    L.krd_squash.restype = C.c_int
+    L.krd_squash.argtypes = [vp, dbl, vp]
     L.krd_get_stats.restype = C.c_int
     L.krd_get_stats.argtypes = [vp, C.POINTER(KrdStats)]
     L.krd_tile_count.restype = i64
@@ -205,6 +222,13 @@ class KrdPlan:
 
     def unpack_shards(self, d_gathered, d_out, world):
         self._check(self._L.krd_unpack_shards(self._h, world, _ptr(d_gathered), _ptr(d_out)))
+
+    def squash(self, p=1.0):
+        """genesis SquashClustering::run on the resident samples: returns the n-1 mergers as a structured array
+        (index_a, index_b, distance_a, distance_b), squash_clustering.hpp:98-119."""
+        out = np.zeros(max(self.n_samples - 1, 0), MERGER_DTYPE)
+        self._check(self._L.krd_squash(self._h, float(p), _ptr(out)))
+        return out
 
     def invalidate_F(self):
         self._check(self._L.krd_invalidate_F(self._h))

@@ -128,6 +128,21 @@ int64_t    krd_tile_count(int32_t n_samples);
 krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j);
 void       krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1);
 
+/* Squash clustering on the resident dense matrix:
+ *     genesis::tree::SquashClustering::run()   libs/genesis/lib/genesis/tree/mass_tree/squash_clustering.cpp:57-249
+ * as called by `gappa analyze squash` (src/commands/analyze/squash.cpp:94-130).  The n samples are the initial
+ * clusters 0..n-1; merge m (m = 0..n-2) joins the closest pair of active clusters into cluster n+m, whose mass
+ * tree is the count-weighted, re-normalised average (mass_tree_merge_trees + mass_tree_normalize_masses,
+ * tree/mass_tree/functions.cpp:60-140) — in the dense representation the same weighted average of two columns
+ * of F — and whose distances to all active clusters are computed by a one-vs-all kernel.  The whole loop runs
+ * on the device without host round trips.  `out` (HOST, n-1 entries) = SquashClustering::mergers()
+ * (squash_clustering.hpp:98-119).  Needs n >= 2. */
+typedef struct krd_merger {
+    int32_t index_a, index_b;     /* a < b: the two clusters that were merged */
+    double  distance_a, distance_b; /* their KR distances to the new cluster node */
+} krd_merger;
+krd_status krd_squash(krd_handle* h, double p, krd_merger* out);
+
 /* Drop the dense matrix F so that the next krd_compute* rebuilds it from the resident masses
  * (bench: one "step" = F build + pair kernel + epilogue). */
 krd_status krd_invalidate_F(krd_handle* h);

@@ -83,6 +83,9 @@ def ref():
         L.ref_dump_copy.argtypes = [C.c_void_p, _i32p, _i32p, _i32p, _f64p, _i64p, _i32p, _f64p,
                                     _f64p, _f64p]
         L.ref_dump_free.argtypes = [C.c_void_p]
+        L.ref_squash.restype = C.c_int
+        L.ref_squash.argtypes = [C.c_int, _i32p, _i32p, _f64p, C.c_int, C.c_int, _i64p, _i32p, _f64p, _f64p,
+                                 C.c_int, C.c_double, _i64p, _f64p, C.c_char_p, C.c_int64, C.POINTER(C.c_double)]
         L.ref_write_matrix.restype = C.c_int
         L.ref_write_matrix.argtypes = [C.c_char_p, _f64p, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_char_p]
         _ref = L
@@ -188,3 +191,15 @@ def ref_write_matrix(path, matrix, fmt="matrix", labels=None, corner="Sample"):
                                 corner.encode())
     if rc != 0:
         raise RuntimeError(ref().ref_last_error().decode())
+
+
+def ref_squash(tree, mass, p=1.0, bins=0):
+    """genesis SquashClustering::run on the flat inputs. Returns (index[n-1,2], dist[n-1,2], tree_string, seconds)."""
+    n = len(mass["off"]) - 1
+    idx = np.zeros(2 * (n - 1), np.int64); dst = np.zeros(2 * (n - 1), np.float64)
+    buf = C.create_string_buffer(64 * n + 64)
+    sec = C.c_double(0)
+    rc = ref().ref_squash(*_t(tree), *_m(mass), bins, float(p), idx, dst, buf, len(buf), C.byref(sec))
+    if rc != 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    return idx.reshape(-1, 2), dst.reshape(-1, 2), buf.value.decode(), sec.value

@@ -10,6 +10,7 @@
 //                          (src/options/jplace_input.cpp:129-171,295-332), dumped to flat arrays
 //   * ref_write_matrix -> genesis::utils::MatrixWriter<double> as configured by gappa
 //                          (src/options/matrix_output.cpp:76-111), to a file
+//   * ref_squash       -> genesis::tree::SquashClustering::run (tree/mass_tree/squash_clustering.cpp:213-249)
 //   * ref_diameter      -> genesis::tree::diameter (tree/common_tree/functions.cpp:178-205)
 // This file is ours; it contains no reference code, it only calls it.
 
@@ -23,6 +24,7 @@
 #include "genesis/tree/function/operators.hpp"
 #include "genesis/tree/mass_tree/emd.hpp"
 #include "genesis/tree/mass_tree/functions.hpp"
+#include "genesis/tree/mass_tree/squash_clustering.hpp"
 #include "genesis/tree/mass_tree/tree.hpp"
 #include "genesis/utils/containers/matrix.hpp"
 #include "genesis/utils/containers/matrix/writer.hpp"
@@ -274,6 +276,52 @@ int ref_write_matrix(const char* path, const double* m, int n, int format, const
             writer.write(mat, target, names, names, corner);
         } else {
             writer.write(mat, target);
+        }
+        return 0;
+    } catch (std::exception const& ex) {
+        g_err = ex.what();
+        return 1;
+    }
+}
+
+// SquashClustering on the same flat inputs; mergers out as (index_a, index_b, distance_a, distance_b) per merge,
+// tree_out (may be null) receives tree_string(labels "0".."n-1"), at most tree_cap bytes.
+int ref_squash(int n_edges, const int* parent, const int* child, const double* bl, int root,
+               int n_samples, const int64_t* off, const int* edge, const double* pos, const double* mass,
+               int bins, double p, int64_t* out_index /* 2*(n-1) */, double* out_dist /* 2*(n-1) */,
+               char* tree_out, int64_t tree_cap, double* seconds)
+{
+    try {
+        auto nw = flat_to_newick(n_edges, parent, child, bl, root);
+        auto ptree = placement::PlacementTreeNewickReader().read(utils::from_string(nw));
+        std::vector<size_t> e2g(n_edges);
+        for (auto const& e : ptree.edges()) e2g[e.data<placement::PlacementEdgeData>().edge_num()] = e.index();
+        auto base = tree::convert_common_tree_to_mass_tree(ptree);
+        for (int e = 0; e < n_edges; ++e) base.edge_at(e2g[e]).data<tree::MassTreeEdgeData>().branch_length = bl[e];
+        std::vector<tree::MassTree> trees(n_samples);
+        for (int i = 0; i < n_samples; ++i) {
+            trees[i] = base;
+            for (int64_t m = off[i]; m < off[i + 1]; ++m)
+                trees[i].edge_at(e2g[edge[m]]).data<tree::MassTreeEdgeData>().masses[pos[m]] += mass[m];
+            if (bins > 0) tree::mass_tree_binify_masses(trees[i], (size_t)bins);
+        }
+        tree::SquashClustering sc;
+        sc.p(p);
+        auto t0 = std::chrono::steady_clock::now();
+        sc.run(std::move(trees));
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        auto const& mg = sc.mergers();
+        for (size_t k = 0; k < mg.size(); ++k) {
+            out_index[2 * k] = (int64_t)mg[k].index_a; out_index[2 * k + 1] = (int64_t)mg[k].index_b;
+            out_dist[2 * k] = mg[k].distance_a; out_dist[2 * k + 1] = mg[k].distance_b;
+        }
+        if (tree_out && tree_cap > 0) {
+            std::vector<std::string> labels;
+            for (int i = 0; i < n_samples; ++i) labels.push_back(std::to_string(i));
+            auto ts = sc.tree_string(labels);
+            std::strncpy(tree_out, ts.c_str(), (size_t)tree_cap - 1);
+            tree_out[tree_cap - 1] = 0;
         }
         return 0;
     } catch (std::exception const& ex) {

@@ -1,10 +1,13 @@
-// gappa-b200 — `analyze krd` with the flag surface of the reference command
+// gappa-b200 — `analyze krd` (and `analyze squash`, cluster tree only) with the flag surface of the reference command
 // (gappa src/commands/analyze/krd.cpp:58-158) on top of the B200 library (include/krd_b200.h).
 //
 //   gappa-b200 analyze krd --jplace-path <files|dirs>... [--exponent p] [--normalize]
 //        [--point-mass] [--ignore-multiplicities] [--out-dir d] [--file-prefix s] [--file-suffix s]
 //        [--compress] [--matrix-format matrix|list|triangular] [--omit-matrix-labels]
 //        [--allow-file-overwriting] [--verbose] [--threads n] [--log-file f]
+//   gappa-b200 analyze squash --jplace-path ... [--exponent p] [--point-mass] [--ignore-multiplicities] [--out-dir d]
+//        [--file-prefix s] [--file-suffix s]       -> cluster.newick  (gappa src/commands/analyze/squash.cpp:94-175;
+//        the per-cluster coloured tree drawings of the reference are visualisation and out of scope)
 //   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d,
 //             --write-binary f (raw row-major doubles, for full-precision comparisons)
 //
@@ -26,6 +29,7 @@ using namespace krdhost;
 namespace {
 
 struct KrdOptions {
+    bool squash = false;      // `analyze squash` instead of `analyze krd`
     std::vector<std::string> jplace_paths;
     double exponent = 1.0;
     bool normalize = false, point_mass = false, ignore_multiplicities = false;
@@ -66,8 +70,9 @@ KrdOptions parse_args(int argc, char** argv)
     KrdOptions o;
     int i = 1;
     if (argc >= 2 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) { std::cout << kUsage; std::exit(0); }
-    if (argc < 3 || std::string(argv[1]) != "analyze" || std::string(argv[2]) != "krd")
-        usage_error("gappa-b200 implements exactly one command: `analyze krd`.");
+    if (argc < 3 || std::string(argv[1]) != "analyze" || (std::string(argv[2]) != "krd" && std::string(argv[2]) != "squash"))
+        usage_error("gappa-b200 implements `analyze krd` and `analyze squash`.");
+    o.squash = std::string(argv[2]) == "squash";
     i = 3;
     std::vector<std::string> args;
     for (; i < argc; ++i) {
@@ -218,6 +223,61 @@ int run_krd(const KrdOptions& o, Log& log)
     return 0;
 }
 
+// SquashClustering::tree_string (genesis tree/mass_tree/squash_clustering.cpp:251-274)
+std::string squash_tree_string(std::vector<std::string> list, const std::vector<krd_merger>& mergers)
+{
+    const size_t n = list.size();
+    for (size_t i = 0; i < mergers.size(); ++i) {
+        const auto& cm = mergers[i];
+        const std::string a = list[(size_t)cm.index_a] + ":" + std::to_string(cm.distance_a);
+        const std::string b = list[(size_t)cm.index_b] + ":" + std::to_string(cm.distance_b);
+        list[(size_t)cm.index_a].clear(); list[(size_t)cm.index_b].clear();
+        list.push_back("(" + a + "," + b + ")" + std::to_string(i + n));
+    }
+    return list.back() + ";";
+}
+
+int run_squash(const KrdOptions& o, Log& log)
+{
+    if (o.exponent <= 0.0)   // squash.cpp:98-103
+        throw std::runtime_error("--exponent (" + std::to_string(o.exponent) + "): Invalid exponent value for KR distance calculation. Has to be > 0.0.");
+    std::string dir = o.out_dir;
+    while (dir.size() > 1 && dir.back() == '/') dir.pop_back();
+    const std::string out_path = dir + "/" + o.prefix + "cluster" + o.suffix + ".newick";
+    if (is_file_path(out_path)) {
+        if (!o.allow_overwrite)
+            throw std::runtime_error("Output file already exists: " + out_path + "\nUse --allow-file-overwriting to allow gappa to overwrite the file.");
+        log.msg("Warning: Output file already exists and will be overwritten: " + out_path);
+    }
+    const auto files = resolve_jplace_paths(o.jplace_paths);
+    log.msg("Found " + std::to_string(files.size()) + " jplace file" + (files.size() > 1 ? "s" : ""));
+    IngestOptions io;
+    io.point_mass = o.point_mass; io.ignore_multiplicities = o.ignore_multiplicities; io.threads = o.threads;
+    MassSet ms = load_mass_set(files, io);
+    log.msg("Running Squash Clustering");
+    const int32_t n = ms.n_samples();
+    krd_config cfg{};
+    cfg.device = o.device; cfg.bins = o.bins;
+    krd_handle* h = nullptr;
+    if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
+    std::vector<krd_merger> mergers((size_t)std::max(n - 1, 0));
+    try {
+        check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
+        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+        check_krd(h, krd_squash(h, o.exponent, mergers.data()));
+    } catch (...) { krd_destroy(h); throw; }
+    krd_destroy(h);
+    log.msg("Writing output files");
+    mkdirs(dir);
+    std::vector<std::string> names;
+    for (const auto& f : files) names.push_back(sample_label(f));
+    std::ofstream out(out_path, std::ios::binary);
+    if (!out) throw std::runtime_error("Cannot open output file '" + out_path + "'.");
+    out << squash_tree_string(names, mergers);
+    log.msg("Finished");
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv)
@@ -226,7 +286,7 @@ int main(int argc, char** argv)
     Log log;
     if (!o.log_file.empty()) log.file.open(o.log_file);
     try {
-        return run_krd(o, log);
+        return o.squash ? run_squash(o, log) : run_krd(o, log);
     } catch (std::exception const& ex) {
         std::cerr << "Error: " << ex.what() << std::endl;
         if (log.file.is_open()) log.file << "Error: " << ex.what() << std::endl;

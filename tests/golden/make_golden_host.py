@@ -12,6 +12,7 @@ Writes
   host_ingest.npz          reference mass_tree_set() arrays for the option combinations
                            (default / --point-mass / --ignore-multiplicities) + diameter + pendant,
                            reference matrices p = 1, 2, 0.5.
+  csv/cluster.newick       `analyze squash`: reference SquashClustering mergers as the Newick text squash.cpp writes
   csv/*.csv                reference MatrixWriter output of the reference p = 1 matrix in the three
                            formats (with/without labels), plus the normalised one; and cfg1's
                            krd_matrix.csv (7847 bytes, test/scripts/analyze-krd-1.sh:7).
@@ -144,6 +145,13 @@ def main():
         oracle.ref_write_matrix(os.path.join(cd, f"{fmt}_nolabels.csv"), m, fmt, None)
     oracle.ref_write_matrix(os.path.join(cd, "matrix_normalized.csv"), m / out["default_diameter"], "matrix", labels)
     oracle.ref_write_matrix(os.path.join(cd, "matrix_pm_p2.csv"), out["pm_m_p2.0"], "matrix", labels)
+    # `analyze squash` on the same documents: reference mergers -> cluster.newick text (squash.cpp:171-174)
+    from gappa_b200 import krd
+    tree, mass, ex = oracle.ref_jplace(paths)
+    idx, dst, _, _ = oracle.ref_squash(tree, mass, p=1.0)
+    mg = np.zeros(len(idx), krd.MERGER_DTYPE)
+    mg["index_a"], mg["index_b"], mg["distance_a"], mg["distance_b"] = idx[:, 0], idx[:, 1], dst[:, 0], dst[:, 1]
+    open(os.path.join(cd, "cluster.newick"), "w").write(krd.squash_tree_string(labels, mg))
     g = np.load(os.path.join(HERE, "cfg1.npz"))
     oracle.ref_write_matrix(os.path.join(cd, "cfg1_krd_matrix.csv"), g["m_p1.0"], "matrix", [str(x) for x in g["names"]])
     print("cfg1 csv bytes", os.path.getsize(os.path.join(cd, "cfg1_krd_matrix.csv")))

@@ -218,6 +218,17 @@ def test_cli_end_to_end(gold, tmp_path, args, csv, key):
 
 
 @pytest.mark.gpu
+def test_cli_squash_end_to_end(tmp_path):
+    r = subprocess.run([host.CLI_PATH, "analyze", "squash", "--jplace-path", JP, "--out-dir", str(tmp_path / "o")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (tmp_path / "o" / "cluster.newick").read_text() == open(os.path.join(GOLD, "csv", "cluster.newick")).read()
+    r = subprocess.run([host.CLI_PATH, "analyze", "squash", "--jplace-path", JP, "--out-dir", str(tmp_path / "o")],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "Output file already exists" in r.stderr
+
+
+@pytest.mark.gpu
 def test_cli_exponent_error_message(tmp_path):
     r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path), "--exponent", "-1"],
                        capture_output=True, text=True)

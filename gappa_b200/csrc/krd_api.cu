@@ -90,7 +90,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
-    cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_kmeans); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
@@ -295,6 +295,22 @@ krd_status krd_squash(krd_handle* h, double p, krd_merger* out)
     if (!out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
     KRD_CUDA(h, cudaSetDevice(h->device));
     return run_squash(h, p, out);
+}
+
+krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids, int32_t* assignments,
+                      double* distances, int32_t* iterations)
+{
+    krd_status st = check_compute(h, 1.0, 1.0);
+    if (st != KRD_OK) return st;
+    if (h->cfg.bins < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means needs binned masses (krd_config.bins >= 1): without bins the reference centres the centroid masses on the branches (kmeans.cpp:75-78), which the dense layout does not represent");
+    if (k > h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "Cannot run Kmeans with more clusters (k) than data points.");   // kmeans.hpp:538-544
+    if (k < 1 || k > 32) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: k must be in 1..32");
+    if (max_iterations < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: max_iterations must be >= 1");
+    if (!init_centroids || !assignments || !distances) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null argument");
+    for (int c = 0; c < k; ++c)
+        if (init_centroids[c] < 0 || init_centroids[c] >= h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: initial centroid is not a sample index");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    return run_kmeans(h, k, max_iterations, init_centroids, assignments, distances, iterations);
 }
 
 krd_status krd_invalidate_F(krd_handle* h)

@@ -105,6 +105,7 @@ struct krd_handle {
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     double* d_out_tmp_sq = nullptr;   // squash clustering: initial N*N distances
     void*   d_squash = nullptr;       // squash clustering state (distance matrix of 2N-1 clusters, counts, mergers, ...)
+    void*   d_kmeans = nullptr;       // k-means state (distance partials, assignments, member lists)
     size_t  out_tmp_capacity = 0;
 
     std::unordered_map<void**, size_t> caps;   // capacities of buffers managed by krd::reserve
@@ -140,5 +141,9 @@ krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, dou
 // krd_squash.cu
 krd_status run_squash(krd_handle* h, double p, krd_merger* out);
 int64_t tiles_per_rank(int64_t n_tiles, int world);
+
+// krd_kmeans.cu
+krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, int32_t* assignments,
+                      double* distances, int32_t* iterations_out);
 
 }  // namespace krd

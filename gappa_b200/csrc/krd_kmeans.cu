@@ -1,0 +1,232 @@
+// Phylogenetic k-means on the dense matrix F — SURVEY §8f rank 4.
+//
+// Reference: genesis::tree::MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) on the generic Lloyd loop of
+// utils/math/kmeans.hpp:118-168, as run by `gappa analyze phylogenetic-kmeans --bins B`
+// (src/commands/analyze/kmeans_phylogenetic.cpp:134-175).  With binned masses a centroid is the
+// re-normalised SUM of its members' mass trees (update_centroids, kmeans.cpp:106-150) — in the dense
+// representation the sum of the members' columns of F divided by the members' total mass — and the
+// assignment step is a rectangular N x k version of the KR reduction (distance = earth_movers_distance with
+// p = 1, kmeans.cpp:204-207).  Both steps are one pass over F each (HBM-bound).  Centroids live in the k
+// columns after the samples.
+#include <algorithm>
+#include <vector>
+
+#include "krd_common.cuh"
+
+namespace krd {
+
+constexpr int KM_CHUNKS = 64;   // segment chunks of the assignment reduction (partials summed in fixed order)
+
+__global__ void k_km_copy_cols(double* __restrict__ F, int64_t ld, int64_t S_pad, const int32_t* __restrict__ src, int N, int k)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= S_pad * k) return;
+    const int64_t s = g / k; const int c = (int)(g % k);
+    F[s * ld + N + c] = F[s * ld + src[c]];
+}
+
+__global__ void k_km_totals(const double* __restrict__ F, int64_t ld, const int32_t* __restrict__ root_seg, int n_root, int N,
+                            double* __restrict__ total)
+{
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= N) return;
+    double t = 0.0;
+    for (int r = 0; r < n_root; ++r) t += F[(int64_t)root_seg[r] * ld + d];
+    total[d] = t;
+}
+
+// part[chunk][c][d] = sum over the chunk's segments of len * |F[s][d] - C[s][c]|
+template <int KMAX>
+__global__ void __launch_bounds__(128)
+k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, int64_t ld, int64_t S_pad, int64_t rows_per_chunk,
+                 int N, int k, double* __restrict__ part)
+{
+    const int64_t d = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S_pad, s0 + rows_per_chunk);
+    double acc[KMAX];
+#pragma unroll
+    for (int c = 0; c < KMAX; ++c) acc[c] = 0.0;
+    for (int64_t s = s0; s < s1; ++s) {
+        const double x = F[s * ld + d], l = len[s];
+        const double* crow = F + s * ld + N;      // the k centroid values of this segment (same address for the whole warp)
+#pragma unroll
+        for (int c = 0; c < KMAX; ++c) if (c < k) acc[c] = fma(l, fabs(x - crow[c]), acc[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < KMAX; ++c)
+        if (c < k) part[((int64_t)blockIdx.y * k + c) * ld + d] = acc[c];
+}
+
+// nearest centroid per sample, first minimum wins (find_nearest_cluster, kmeans.hpp:365-382);
+// reassign = 0: only the distance to the CURRENT assignment (cluster_info, kmeans.hpp:384-424)
+__global__ void k_km_assign_final(const double* __restrict__ part, int64_t ld, int N, int k, int reassign,
+                                  int32_t* __restrict__ assign, double* __restrict__ dist, int* __restrict__ changed)
+{
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= N) return;
+    int best = -1; double best_v = 1.7976931348623157e308;
+    const int cur = assign[d];
+    for (int c = 0; c < k; ++c) {
+        if (!reassign && c != cur) continue;
+        double v = 0.0;
+        for (int ch = 0; ch < KM_CHUNKS; ++ch) v += part[((int64_t)ch * k + c) * ld + d];
+        if (v < best_v) { best_v = v; best = c; }
+    }
+    dist[d] = best_v;
+    if (reassign && best != cur) { assign[d] = best; atomicOr(changed, 1); }
+}
+
+// centroid c = (sum of its members' columns, in sample order) / (sum of the members' total masses)
+// (mass_tree_merge_trees_inplace per member, then mass_tree_normalize_masses: kmeans.cpp:124-149)
+__global__ void __launch_bounds__(256)
+k_km_update(double* __restrict__ F, int64_t ld, int64_t S_pad, int N, int k, const int32_t* __restrict__ mem_off,
+            const int32_t* __restrict__ mem, const double* __restrict__ ctot)
+{
+    extern __shared__ double row[];   // one segment row of the samples
+    for (int64_t s = blockIdx.x; s < S_pad; s += gridDim.x) {
+        for (int d = threadIdx.x; d < N; d += 256) row[d] = F[s * ld + d];
+        __syncthreads();
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (int c = warp; c < k; c += 8) {
+            double acc = 0.0;
+            for (int q = mem_off[c] + lane; q < mem_off[c + 1]; q += 32) acc += row[mem[q]];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+            if (lane == 0) F[s * ld + N + c] = (ctot[c] == 0.0) ? acc : acc / ctot[c];
+        }
+        __syncthreads();
+    }
+}
+
+template <int KMAX>
+static void launch_assign(krd_handle* h, int k, int64_t rpc, double* part)
+{
+    k_km_assign_part<KMAX><<<dim3((unsigned)((h->N + 127) / 128), KM_CHUNKS), 128, 0, h->stream>>>(h->d_F, h->d_len, h->ld, h->S_pad, rpc, h->N, k, part);
+}
+
+krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, int32_t* assignments,
+                      double* distances, int32_t* iterations_out)
+{
+    const int N = h->N;
+    if (h->ld < N + k) {     // room for the centroid columns
+        h->extra_cols = std::max(h->extra_cols, k);
+        krd_status st = prepare_masses(h);
+        if (st != KRD_OK) return st;
+    }
+    krd_status st = build_F(h);   // always rebuild: earlier clusterings leave their columns behind
+    if (st != KRD_OK) return st;
+
+    std::vector<int32_t> seg_off((size_t)h->E + 1), root_seg;
+    KRD_CUDA(h, cudaMemcpyAsync(seg_off.data(), h->d_seg_off, seg_off.size() * 4, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int e = 0; e < h->E; ++e) if (h->parent[(size_t)e] == h->root) root_seg.push_back(seg_off[(size_t)e]);
+
+    auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t b_part = (size_t)KM_CHUNKS * k * h->ld * 8, b_n8 = (size_t)N * 8, b_n4 = (size_t)N * 4, b_k = (size_t)(k + 1) * 8;
+    const size_t b_root = std::max<size_t>(root_seg.size(), 1) * 4;
+    if ((st = reserve(h, &h->d_kmeans, al(b_part) + 2 * al(b_n8) + 2 * al(b_n4) + 3 * al(b_k) + al(b_root) + 256)) != KRD_OK) return st;
+    char* q = static_cast<char*>(h->d_kmeans);
+    double* part = (double*)q; q += al(b_part);
+    double* d_dist = (double*)q; q += al(b_n8);
+    double* d_total = (double*)q; q += al(b_n8);
+    int32_t* d_assign = (int32_t*)q; q += al(b_n4);
+    int32_t* d_mem = (int32_t*)q; q += al(b_n4);
+    int32_t* d_mem_off = (int32_t*)q; q += al(b_k);
+    double* d_ctot = (double*)q; q += al(b_k);
+    int32_t* d_init = (int32_t*)q; q += al(b_k);
+    int32_t* d_root = (int32_t*)q; q += al(b_root);
+    int* d_changed = (int*)q;
+
+    KRD_CUDA(h, cudaMemcpyAsync(d_root, root_seg.data(), root_seg.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(d_init, init_centroids, (size_t)k * 4, cudaMemcpyHostToDevice, h->stream));
+    std::vector<int32_t> a((size_t)N, 0);   // kmeans.hpp:303-305: assignments start at 0 when only centroids are given
+    KRD_CUDA(h, cudaMemcpyAsync(d_assign, a.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
+    k_km_totals<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, d_root, (int)root_seg.size(), N, d_total);
+    k_km_copy_cols<<<(unsigned)((h->S_pad * k + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, d_init, N, k);
+    std::vector<double> total((size_t)N);
+    KRD_CUDA(h, cudaMemcpyAsync(total.data(), d_total, b_n8, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+
+    const int64_t rpc = (h->S_pad + KM_CHUNKS - 1) / KM_CHUNKS;
+    auto assign_pass = [&](int reassign) {
+        if (k <= 4) launch_assign<4>(h, k, rpc, part);
+        else if (k <= 8) launch_assign<8>(h, k, rpc, part);
+        else if (k <= 16) launch_assign<16>(h, k, rpc, part);
+        else launch_assign<32>(h, k, rpc, part);
+        k_km_assign_final<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
+    };
+    static bool configured = false;
+    const size_t smem_row = (size_t)N * 8;
+    if (smem_row > 200 * 1024) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: more than 25,600 samples are not supported");
+    if (!configured) { KRD_CUDA(h, cudaFuncSetAttribute(k_km_update, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); configured = true; }
+
+    int iteration = 0, changed = 0, launches = 2;
+    std::vector<int32_t> mem((size_t)N), mem_off((size_t)k + 1);
+    std::vector<double> ctot((size_t)k), dist((size_t)N);
+    // update_centroids from the host copy of the assignments: member lists in sample order + the members'
+    // total mass per centroid (host: N integers), then one pass over F.  A centroid without members becomes
+    // all-zero (mass_tree_normalize_masses returns early on an empty tree, functions.cpp:126-132).
+    auto update = [&]() -> krd_status {
+        std::fill(mem_off.begin(), mem_off.end(), 0);
+        for (int d = 0; d < N; ++d) mem_off[(size_t)a[(size_t)d] + 1]++;
+        for (int c = 0; c < k; ++c) mem_off[(size_t)c + 1] += mem_off[(size_t)c];
+        std::vector<int32_t> fill(mem_off.begin(), mem_off.end() - 1);
+        std::fill(ctot.begin(), ctot.end(), 0.0);
+        for (int d = 0; d < N; ++d) { mem[(size_t)fill[(size_t)a[(size_t)d]]++] = d; ctot[(size_t)a[(size_t)d]] += total[(size_t)d]; }
+        KRD_CUDA(h, cudaMemcpyAsync(d_mem, mem.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(d_mem_off, mem_off.data(), (size_t)(k + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(d_ctot, ctot.data(), (size_t)k * 8, cudaMemcpyHostToDevice, h->stream));
+        k_km_update<<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, smem_row, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));   // the host vectors are reused
+        launches += 1;
+        return KRD_OK;
+    };
+    do {
+        // lloyd_step (kmeans.hpp:324-336): assign, then update
+        KRD_CUDA(h, cudaMemsetAsync(d_changed, 0, sizeof(int), h->stream));
+        assign_pass(1);
+        KRD_CUDA(h, cudaMemcpyAsync(a.data(), d_assign, b_n4, cudaMemcpyDeviceToHost, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(&changed, d_changed, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        launches += 2;
+        if ((st = update()) != KRD_OK) return st;
+
+        // treat_empty_centroids (kmeans.hpp:426-500): give each empty centroid the sample that is furthest from
+        // the centroid of the cluster with the largest variance.  The reference walks a std::unordered_set of
+        // the empty indices; libstdc++ yields small sets of integers in reverse insertion order, so highest first.
+        std::vector<int> empties;
+        for (int c = k - 1; c >= 0; --c) if (mem_off[(size_t)c + 1] == mem_off[(size_t)c]) empties.push_back(c);
+        bool treated = false;
+        for (size_t ei = 0; ei < empties.size(); ++ei) {
+            assign_pass(0);
+            KRD_CUDA(h, cudaMemcpyAsync(dist.data(), d_dist, b_n8, cudaMemcpyDeviceToHost, h->stream));
+            KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+            launches += 2;
+            std::vector<double> var((size_t)k, 0.0); std::vector<int64_t> cnt((size_t)k, 0);
+            for (int d = 0; d < N; ++d) { var[(size_t)a[(size_t)d]] += dist[(size_t)d] * dist[(size_t)d]; cnt[(size_t)a[(size_t)d]]++; }
+            for (int c = 0; c < k; ++c) if (cnt[(size_t)c] > 0) var[(size_t)c] /= (double)cnt[(size_t)c];
+            const int mv = (int)(std::max_element(var.begin(), var.end()) - var.begin());
+            if (var[(size_t)mv] == 0.0) { treated = false; break; }   // the reference returns false here
+            int far = -1; double far_d = -1.7976931348623157e308;
+            for (int d = 0; d < N; ++d) if (a[(size_t)d] == mv && dist[(size_t)d] > far_d) { far = d; far_d = dist[(size_t)d]; }
+            a[(size_t)far] = empties[ei];
+            KRD_CUDA(h, cudaMemcpyAsync(d_assign, a.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
+            if ((st = update()) != KRD_OK) return st;
+            treated = true;
+        }
+        if (treated) changed = 1;
+        ++iteration;
+    } while (changed && iteration < max_iterations);
+
+    assign_pass(0);   // cluster_info: distance of every sample to its (final) centroid
+    KRD_CUDA(h, cudaGetLastError());
+    KRD_CUDA(h, cudaMemcpyAsync(distances, d_dist, b_n8, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    std::copy(a.begin(), a.end(), assignments);
+    if (iterations_out) *iterations_out = iteration;
+    h->F_valid = false;      // the centroid columns are scratch
+    h->stats.launches = launches + 2;
+    return KRD_OK;
+}
+
+}  // namespace krd

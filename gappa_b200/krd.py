@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -108,6 +108,8 @@ def lib():
     L.krd_compute_shard.argtypes = [vp, dbl, dbl, i32, i32, vp]
     L.krd_unpack_shards.restype = C.c_int
     L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
+    L.krd_kmeans.restype = C.c_int
+    L.krd_kmeans.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(C.c_int32)]
     L.krd_squash.restype = C.c_int
     L.krd_squash.argtypes = [vp, dbl, vp]
     L.krd_get_stats.restype = C.c_int
@@ -229,6 +231,23 @@ class KrdPlan:
         out = np.zeros(max(self.n_samples - 1, 0), MERGER_DTYPE)
         self._check(self._L.krd_squash(self._h, float(p), _ptr(out)))
         return out
+
+    def kmeans(self, k, init_centroids, max_iterations=100):
+        """genesis MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) via Kmeans::run (utils/math/kmeans.hpp:118-168) on
+        the resident binned samples, started from the given samples as centroids.  Returns (assignments[n] int32,
+        distances[n] of every sample to its centroid, cluster variances[k], iterations); the variances are
+        KmeansClusteringInfo::variances (kmeans.hpp:384-424)."""
+        init = np.ascontiguousarray(init_centroids, np.int32)
+        if init.shape != (k,):
+            raise ValueError("init_centroids must hold k sample indices")
+        a = np.zeros(self.n_samples, np.int32); d = np.zeros(self.n_samples, np.float64)
+        it = C.c_int32(0)
+        self._check(self._L.krd_kmeans(self._h, int(k), int(max_iterations), _ptr(init), _ptr(a), _ptr(d), C.byref(it)))
+        cnt = np.bincount(a, minlength=k)
+        var = np.zeros(k, np.float64)
+        np.add.at(var, a, d * d)     # sample order, like the reference's serial accumulation
+        var = np.where(cnt > 0, var / np.maximum(cnt, 1), var)
+        return a, d, var, int(it.value)
 
     def invalidate_F(self):
         self._check(self._L.krd_invalidate_F(self._h))

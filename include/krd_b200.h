@@ -143,6 +143,19 @@ typedef struct krd_merger {
 } krd_merger;
 krd_status krd_squash(krd_handle* h, double p, krd_merger* out);
 
+/* Phylogenetic k-means (`gappa analyze phylogenetic-kmeans`, src/commands/analyze/kmeans_phylogenetic.cpp:134-175)
+ * = genesis::tree::MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) on the Lloyd loop of
+ * utils/math/kmeans.hpp:118-168, run on the resident dense matrix: centroids are extra columns of F (the
+ * re-normalised sum of their members' columns), the assignment step is the p = 1 KR reduction of every
+ * sample against the k centroids, first minimum wins.  Empty centroids are treated as in kmeans.hpp:426-500.
+ * `init_centroids` (HOST, k sample indices) are the initial centroids, i.e. the state after the reference's
+ * initialisation (kmeans.hpp:254-306: random samples or k-means++, both pick data points); all assignments
+ * start at 0.  Outputs (HOST): assignments[n], distances[n] = KR distance of every sample to its centroid
+ * (KmeansClusteringInfo::distances, kmeans.hpp:384-424), *iterations = Kmeans::run()'s return value.
+ * 1 <= k <= min(n, 32); max_iterations = the reference's default is 100 (kmeans.hpp:699). */
+krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids,
+                      int32_t* assignments, double* distances, int32_t* iterations);
+
 /* Drop the dense matrix F so that the next krd_compute* rebuilds it from the resident masses
  * (bench: one "step" = F build + pair kernel + epilogue). */
 krd_status krd_invalidate_F(krd_handle* h);

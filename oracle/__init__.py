@@ -83,6 +83,9 @@ def ref():
         L.ref_dump_copy.argtypes = [C.c_void_p, _i32p, _i32p, _i32p, _f64p, _i64p, _i32p, _f64p,
                                     _f64p, _f64p]
         L.ref_dump_free.argtypes = [C.c_void_p]
+        L.ref_kmeans.restype = C.c_int
+        L.ref_kmeans.argtypes = [C.c_int, _i32p, _i32p, _f64p, C.c_int, C.c_int, _i64p, _i32p, _f64p, _f64p,
+                                 C.c_int, C.c_int, C.c_int, _i32p, _i64p, _f64p, _f64p, _i64p, C.POINTER(C.c_double)]
         L.ref_squash.restype = C.c_int
         L.ref_squash.argtypes = [C.c_int, _i32p, _i32p, _f64p, C.c_int, C.c_int, _i64p, _i32p, _f64p, _f64p,
                                  C.c_int, C.c_double, _i64p, _f64p, C.c_char_p, C.c_int64, C.POINTER(C.c_double)]
@@ -191,6 +194,20 @@ def ref_write_matrix(path, matrix, fmt="matrix", labels=None, corner="Sample"):
                                 corner.encode())
     if rc != 0:
         raise RuntimeError(ref().ref_last_error().decode())
+
+
+def ref_kmeans(tree, mass, k, init_centroids, bins=0, max_iterations=100):
+    """genesis MassTreeKmeans::run started from data points as centroids.
+    Returns (assignments[n], distances[n], variances[k], iterations, seconds)."""
+    n = len(mass["off"]) - 1
+    a = np.zeros(n, np.int64); d = np.zeros(n, np.float64); v = np.zeros(k, np.float64); it = np.zeros(1, np.int64)
+    init = np.ascontiguousarray(init_centroids, np.int32)
+    assert len(init) == k
+    sec = C.c_double(0)
+    rc = ref().ref_kmeans(*_t(tree), *_m(mass), bins, k, max_iterations, init, a, d, v, it, C.byref(sec))
+    if rc != 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    return a, d, v, int(it[0]), sec.value
 
 
 def ref_squash(tree, mass, p=1.0, bins=0):

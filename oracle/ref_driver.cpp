@@ -11,6 +11,8 @@
 //   * ref_write_matrix -> genesis::utils::MatrixWriter<double> as configured by gappa
 //                          (src/options/matrix_output.cpp:76-111), to a file
 //   * ref_squash       -> genesis::tree::SquashClustering::run (tree/mass_tree/squash_clustering.cpp:213-249)
+//   * ref_kmeans       -> genesis::tree::MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) via utils::Kmeans::run
+//                          (utils/math/kmeans.hpp:118-168) as set up by gappa (src/commands/analyze/kmeans_phylogenetic.cpp:155-175)
 //   * ref_diameter      -> genesis::tree::diameter (tree/common_tree/functions.cpp:178-205)
 // This file is ours; it contains no reference code, it only calls it.
 
@@ -24,6 +26,7 @@
 #include "genesis/tree/function/operators.hpp"
 #include "genesis/tree/mass_tree/emd.hpp"
 #include "genesis/tree/mass_tree/functions.hpp"
+#include "genesis/tree/mass_tree/kmeans.hpp"
 #include "genesis/tree/mass_tree/squash_clustering.hpp"
 #include "genesis/tree/mass_tree/tree.hpp"
 #include "genesis/utils/containers/matrix.hpp"
@@ -323,6 +326,49 @@ int ref_squash(int n_edges, const int* parent, const int* child, const double* b
             std::strncpy(tree_out, ts.c_str(), (size_t)tree_cap - 1);
             tree_out[tree_cap - 1] = 0;
         }
+        return 0;
+    } catch (std::exception const& ex) {
+        g_err = ex.what();
+        return 1;
+    }
+}
+
+// MassTreeKmeans on the same flat inputs, started from given data points as centroids (what both of the
+// reference's initialisation strategies produce).  bins as in gappa: binify the data and accumulate_centroid_masses.
+int ref_kmeans(int n_edges, const int* parent, const int* child, const double* bl, int root,
+               int n_samples, const int64_t* off, const int* edge, const double* pos, const double* mass,
+               int bins, int k, int max_iterations, const int* init_centroids,
+               int64_t* out_assign /* n */, double* out_dist /* n */, double* out_var /* k */, int64_t* out_iterations, double* seconds)
+{
+    try {
+        auto nw = flat_to_newick(n_edges, parent, child, bl, root);
+        auto ptree = placement::PlacementTreeNewickReader().read(utils::from_string(nw));
+        std::vector<size_t> e2g(n_edges);
+        for (auto const& e : ptree.edges()) e2g[e.data<placement::PlacementEdgeData>().edge_num()] = e.index();
+        auto base = tree::convert_common_tree_to_mass_tree(ptree);
+        for (int e = 0; e < n_edges; ++e) base.edge_at(e2g[e]).data<tree::MassTreeEdgeData>().branch_length = bl[e];
+        std::vector<tree::MassTree> trees(n_samples);
+        for (int i = 0; i < n_samples; ++i) {
+            trees[i] = base;
+            for (int64_t m = off[i]; m < off[i + 1]; ++m)
+                trees[i].edge_at(e2g[edge[m]]).data<tree::MassTreeEdgeData>().masses[pos[m]] += mass[m];
+            if (bins > 0) tree::mass_tree_binify_masses(trees[i], (size_t)bins);
+        }
+        tree::MassTreeKmeans km;
+        if (bins > 0) km.accumulate_centroid_masses((size_t)bins);
+        km.max_iterations((size_t)max_iterations);
+        km.initialization_strategy(utils::KmeansInitializationStrategy::kNone);
+        std::vector<tree::MassTree> cents;
+        for (int c = 0; c < k; ++c) cents.push_back(trees[init_centroids[c]]);
+        km.centroids(cents);
+        auto t0 = std::chrono::steady_clock::now();
+        auto const it = km.run(trees, (size_t)k);
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        auto const info = km.cluster_info(trees);
+        for (int i = 0; i < n_samples; ++i) { out_assign[i] = (int64_t)km.assignments()[i]; out_dist[i] = info.distances[i]; }
+        for (int c = 0; c < k; ++c) out_var[c] = info.variances[c];
+        *out_iterations = (int64_t)it;
         return 0;
     } catch (std::exception const& ex) {
         g_err = ex.what();

@@ -15,7 +15,7 @@
 
 namespace krd {
 
-constexpr int KM_CHUNKS = 64;   // segment chunks of the assignment reduction (partials summed in fixed order)
+constexpr int KM_CHUNKS = 128;   // segment chunks of the assignment reduction (partials summed in fixed order)
 
 __global__ void k_km_copy_cols(double* __restrict__ F, int64_t ld, int64_t S_pad, const int32_t* __restrict__ src, int N, int k)
 {
@@ -36,21 +36,41 @@ __global__ void k_km_totals(const double* __restrict__ F, int64_t ld, const int3
 }
 
 // part[chunk][c][d] = sum over the chunk's segments of len * |F[s][d] - C[s][c]|
+// The k centroid values and the length of KM_ROWS segments are staged in shared memory (read by every thread);
+// the sample values stream from HBM with KM_UNROLL independent row loads in flight per thread.
+constexpr int KM_ROWS = 64, KM_UNROLL = 8;
 template <int KMAX>
 __global__ void __launch_bounds__(128)
 k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, int64_t ld, int64_t S_pad, int64_t rows_per_chunk,
                  int N, int k, double* __restrict__ part)
 {
+    __shared__ double sc[KM_ROWS][KMAX];
+    __shared__ double sl[KM_ROWS];
     const int64_t d = (int64_t)blockIdx.x * 128 + threadIdx.x;
     const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S_pad, s0 + rows_per_chunk);
     double acc[KMAX];
 #pragma unroll
     for (int c = 0; c < KMAX; ++c) acc[c] = 0.0;
-    for (int64_t s = s0; s < s1; ++s) {
-        const double x = F[s * ld + d], l = len[s];
-        const double* crow = F + s * ld + N;      // the k centroid values of this segment (same address for the whole warp)
+    for (int64_t r0 = s0; r0 < s1; r0 += KM_ROWS) {
+        const int nr = (int)min((int64_t)KM_ROWS, s1 - r0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < KM_ROWS * KMAX; i += 128) {
+            const int r = i / KMAX, c = i % KMAX;
+            sc[r][c] = (r < nr && c < k) ? F[(r0 + r) * ld + N + c] : 0.0;
+        }
+        if (threadIdx.x < KM_ROWS) sl[threadIdx.x] = (threadIdx.x < nr) ? len[r0 + threadIdx.x] : 0.0;   // rows past the chunk: length 0
+        __syncthreads();
+        for (int r = 0; r < nr; r += KM_UNROLL) {
+            double x[KM_UNROLL];
 #pragma unroll
-        for (int c = 0; c < KMAX; ++c) if (c < k) acc[c] = fma(l, fabs(x - crow[c]), acc[c]);
+            for (int u = 0; u < KM_UNROLL; ++u) x[u] = F[(r0 + min(r + u, nr - 1)) * ld + d];
+#pragma unroll
+            for (int u = 0; u < KM_UNROLL; ++u) {
+                const double l = sl[r + u];
+#pragma unroll
+                for (int c = 0; c < KMAX; ++c) if (c < k) acc[c] = fma(l, fabs(x[u] - sc[r + u][c]), acc[c]);
+            }
+        }
     }
 #pragma unroll
     for (int c = 0; c < KMAX; ++c)
@@ -58,22 +78,27 @@ k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, i
 }
 
 // nearest centroid per sample, first minimum wins (find_nearest_cluster, kmeans.hpp:365-382);
-// reassign = 0: only the distance to the CURRENT assignment (cluster_info, kmeans.hpp:384-424)
+// reassign = 0: only the distance to the CURRENT assignment (cluster_info, kmeans.hpp:384-424).
+// Block = 32 samples x k centroids: thread (x, c) sums the chunk partials of one (sample, centroid) in fixed order.
 __global__ void k_km_assign_final(const double* __restrict__ part, int64_t ld, int N, int k, int reassign,
                                   int32_t* __restrict__ assign, double* __restrict__ dist, int* __restrict__ changed)
 {
-    const int d = blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= N) return;
-    int best = -1; double best_v = 1.7976931348623157e308;
-    const int cur = assign[d];
-    for (int c = 0; c < k; ++c) {
-        if (!reassign && c != cur) continue;
-        double v = 0.0;
+    __shared__ double val[32][33];
+    const int d = blockIdx.x * 32 + threadIdx.x, c = threadIdx.y;
+    double v = 0.0;
+    if (d < N) {
+#pragma unroll 8
         for (int ch = 0; ch < KM_CHUNKS; ++ch) v += part[((int64_t)ch * k + c) * ld + d];
-        if (v < best_v) { best_v = v; best = c; }
     }
+    val[c][threadIdx.x] = v;
+    __syncthreads();
+    if (c != 0 || d >= N) return;
+    const int cur = assign[d];
+    if (!reassign) { dist[d] = val[cur][threadIdx.x]; return; }
+    int best = -1; double best_v = 1.7976931348623157e308;
+    for (int q = 0; q < k; ++q) if (val[q][threadIdx.x] < best_v) { best_v = val[q][threadIdx.x]; best = q; }
     dist[d] = best_v;
-    if (reassign && best != cur) { assign[d] = best; atomicOr(changed, 1); }
+    if (best != cur) { assign[d] = best; atomicOr(changed, 1); }
 }
 
 // centroid c = (sum of its members' columns, in sample order) / (sum of the members' total masses)
@@ -153,7 +178,7 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
         else if (k <= 8) launch_assign<8>(h, k, rpc, part);
         else if (k <= 16) launch_assign<16>(h, k, rpc, part);
         else launch_assign<32>(h, k, rpc, part);
-        k_km_assign_final<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
+        k_km_assign_final<<<(unsigned)((N + 31) / 32), dim3(32, (unsigned)k), 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
     };
     static bool configured = false;
     const size_t smem_row = (size_t)N * 8;

@@ -8,6 +8,9 @@
 //   gappa-b200 analyze squash --jplace-path ... [--exponent p] [--point-mass] [--ignore-multiplicities] [--out-dir d]
 //        [--file-prefix s] [--file-suffix s]       -> cluster.newick  (gappa src/commands/analyze/squash.cpp:94-175;
 //        the per-cluster coloured tree drawings of the reference are visualisation and out of scope)
+//   gappa-b200 analyze phylogenetic-kmeans --jplace-path ... --k "1-5,8" --bins B [--write-overview-file] [--point-mass]
+//        [--ignore-multiplicities] [--out-dir d] [--file-prefix s] [--file-suffix s]  -> k_<k>_assignments.csv, overview.csv
+//        (gappa src/commands/analyze/kmeans_phylogenetic.cpp:134-199; additive: --seed n, --init-centroids i,j,...)
 //   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d,
 //             --write-binary f (raw row-major doubles, for full-precision comparisons)
 //
@@ -19,6 +22,10 @@
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <limits>
+#include <random>
+#include <sstream>
+#include <algorithm>
 
 #include "../../include/krd_b200.h"
 #include "ingest.hpp"
@@ -30,6 +37,10 @@ namespace {
 
 struct KrdOptions {
     bool squash = false;      // `analyze squash` instead of `analyze krd`
+    bool kmeans = false;      // `analyze phylogenetic-kmeans`
+    std::string ks, init_centroids;   // --k range list; --init-centroids (additive): explicit sample indices instead of k-means++
+    bool overview_file = false;
+    long long seed = -1;      // --seed (additive): k-means++ random seed; default: clock, like the reference's Options::random_engine
     std::vector<std::string> jplace_paths;
     double exponent = 1.0;
     bool normalize = false, point_mass = false, ignore_multiplicities = false;
@@ -39,7 +50,7 @@ struct KrdOptions {
 };
 
 const char* kUsage =
-    "Usage: gappa-b200 analyze krd [OPTIONS]\n"
+    "Usage: gappa-b200 analyze krd | squash | phylogenetic-kmeans [OPTIONS]\n"
     "Calculate the pairwise Kantorovich-Rubinstein (KR) distance matrix between samples.\n\n"
     "Input:\n  --jplace-path TEXT ... REQUIRED   List of jplace files or directories to process.\n"
     "Settings:\n  --exponent FLOAT=1                Exponent for KR integration.\n"
@@ -47,6 +58,8 @@ const char* kUsage =
     "  --point-mass                      Treat every pquery as a point mass on its highest-weight placement.\n"
     "  --ignore-multiplicities           Set the multiplicity of each pquery to 1.0.\n"
     "  --bins INT=0                      (additive) binify masses into this many bins per edge first.\n"
+    "  --k TEXT  --write-overview-file   (phylogenetic-kmeans) values of k, e.g. 1-5,8; needs --bins >= 1.\n"
+    "  --seed INT  --init-centroids LIST (phylogenetic-kmeans, additive) k-means++ seed / explicit start samples.\n"
     "Matrix Output:\n  --out-dir TEXT=.  --file-prefix TEXT  --file-suffix TEXT  --compress\n"
     "  --matrix-format TEXT=matrix       matrix | list | triangular\n  --omit-matrix-labels\n"
     "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --help\n";
@@ -70,9 +83,10 @@ KrdOptions parse_args(int argc, char** argv)
     KrdOptions o;
     int i = 1;
     if (argc >= 2 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) { std::cout << kUsage; std::exit(0); }
-    if (argc < 3 || std::string(argv[1]) != "analyze" || (std::string(argv[2]) != "krd" && std::string(argv[2]) != "squash"))
-        usage_error("gappa-b200 implements `analyze krd` and `analyze squash`.");
+    if (argc < 3 || std::string(argv[1]) != "analyze" || (std::string(argv[2]) != "krd" && std::string(argv[2]) != "squash" && std::string(argv[2]) != "phylogenetic-kmeans"))
+        usage_error("gappa-b200 implements `analyze krd`, `analyze squash` and `analyze phylogenetic-kmeans`.");
     o.squash = std::string(argv[2]) == "squash";
+    o.kmeans = std::string(argv[2]) == "phylogenetic-kmeans";
     i = 3;
     std::vector<std::string> args;
     for (; i < argc; ++i) {
@@ -114,6 +128,10 @@ KrdOptions parse_args(int argc, char** argv)
         else if (a == "--bins") o.bins = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--device") o.device = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--write-binary") o.write_binary = value();
+        else if (a == "--k") o.ks = value();
+        else if (a == "--write-overview-file") o.overview_file = true;
+        else if (a == "--init-centroids") o.init_centroids = value();
+        else if (a == "--seed") o.seed = number([](const std::string& s, size_t* u) { return std::stoll(s, u); });
         else if (a == "--help" || a == "-h") { std::cout << kUsage; std::exit(0); }
         else usage_error("The following argument was not expected: " + a);
     }
@@ -278,6 +296,140 @@ int run_squash(const KrdOptions& o, Log& log)
     return 0;
 }
 
+// genesis::utils::split_range_list ("1-5,8,10,12" -> sorted unique numbers), as used by get_k_values (kmeans.cpp:138-161)
+std::vector<int> parse_k_values(const std::string& ks)
+{
+    const std::string msg = "--k (" + ks + "): Invalid list of values for k. Needs to be a comma-separated list of positive numbers or ranges, e.g., 5-10,12,15";
+    std::vector<int> out;
+    size_t i = 0;
+    auto num = [&](size_t& q) -> long {
+        while (q < ks.size() && ks[q] == ' ') ++q;
+        size_t b = q; long v = 0;
+        while (q < ks.size() && std::isdigit((unsigned char)ks[q])) { v = v * 10 + (ks[q] - '0'); if (v > 1000000) throw std::runtime_error(msg); ++q; }
+        if (q == b) throw std::runtime_error(msg);
+        while (q < ks.size() && ks[q] == ' ') ++q;
+        return v;
+    };
+    while (i < ks.size()) {
+        long a = num(i), b = a;
+        if (i < ks.size() && ks[i] == '-') { ++i; b = num(i); }
+        if (b < a) throw std::runtime_error(msg);
+        for (long v = a; v <= b; ++v) out.push_back((int)v);
+        if (i < ks.size()) { if (ks[i] != ',') throw std::runtime_error(msg); ++i; if (i == ks.size()) throw std::runtime_error(msg); }
+    }
+    std::sort(out.begin(), out.end());
+    out.erase(std::unique(out.begin(), out.end()), out.end());
+    if (out.empty() || out[0] == 0) throw std::runtime_error(msg);
+    return out;
+}
+
+std::string fmt_g(double v) { char b[64]; std::snprintf(b, sizeof b, "%g", v); return b; }   // default ostream << double
+
+// `analyze phylogenetic-kmeans` (src/commands/analyze/kmeans_phylogenetic.cpp:134-199, kmeans.cpp:163-269): assignment
+// tables k_<k>_assignments.csv and, with --write-overview-file, overview.csv.  The centroid tree drawings
+// (write_pkmeans_cluster_trees: svg / nexus / phyloxml colour trees) are not produced.
+int run_kmeans(const KrdOptions& o, Log& log)
+{
+    const std::vector<int> ks = parse_k_values(o.ks);
+    if (o.bins < 1)
+        throw std::runtime_error("--bins: gappa-b200 runs phylogenetic k-means on binned masses only; give --bins B with B >= 1 (gappa recommends 50 or more).");
+    std::string dir = o.out_dir;
+    while (dir.size() > 1 && dir.back() == '/') dir.pop_back();
+    auto out_path = [&](const std::string& infix) { return dir + "/" + o.prefix + infix + o.suffix + ".csv"; };
+    std::vector<std::string> outs;
+    for (int k : ks) outs.push_back(out_path("k_" + std::to_string(k) + "_assignments"));
+    if (o.overview_file) outs.push_back(out_path("overview"));
+    for (const auto& f : outs) if (is_file_path(f)) {
+        if (!o.allow_overwrite)
+            throw std::runtime_error("Output file already exists: " + f + "\nUse --allow-file-overwriting to allow gappa to overwrite the file.");
+        log.msg("Warning: Output file already exists and will be overwritten: " + f);
+    }
+    const auto files = resolve_jplace_paths(o.jplace_paths);
+    log.msg("Found " + std::to_string(files.size()) + " jplace file" + (files.size() > 1 ? "s" : ""));
+    if (files.size() < 2) throw std::runtime_error("Cannot run k-means with fewer than 2 samples.");   // kmeans_phylogenetic.cpp:146-148
+    log.msg("Reading samples.");
+    IngestOptions io;
+    io.point_mass = o.point_mass; io.ignore_multiplicities = o.ignore_multiplicities; io.threads = o.threads;
+    MassSet ms = load_mass_set(files, io);
+    const int32_t n = ms.n_samples();
+    std::vector<int32_t> fixed_init;
+    if (!o.init_centroids.empty()) {
+        std::stringstream ss(o.init_centroids); std::string tok;
+        while (std::getline(ss, tok, ',')) fixed_init.push_back((int32_t)std::stol(tok));
+    }
+    const unsigned long long seed = o.seed >= 0 ? (unsigned long long)o.seed
+                                                : (unsigned long long)std::chrono::system_clock::now().time_since_epoch().count();
+    std::mt19937_64 engine(seed);
+    if (fixed_init.empty()) log.msg("Random seed for k-means++: " + std::to_string(seed));
+
+    krd_config cfg{};
+    cfg.device = o.device; cfg.bins = o.bins;
+    krd_handle* h = nullptr;
+    if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
+    struct Row { int k; double dist, var; };
+    std::vector<Row> overview;
+    mkdirs(dir);
+    try {
+        check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
+        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+        std::vector<double> D;   // pairwise KR matrix: the data-to-data-point distances k-means++ draws from
+        std::vector<int32_t> assign((size_t)n);
+        std::vector<double> dist((size_t)n);
+        for (size_t ki = 0; ki < ks.size(); ++ki) {
+            const int k = ks[ki];
+            log.msg("\nRunning Phylogenetic Kmeans with k=" + std::to_string(k));
+            if (k > n) throw std::runtime_error("Cannot run Kmeans with more clusters (k == " + std::to_string(k) + ") than data points (" + std::to_string(n) + ")");
+            std::vector<int32_t> init;
+            if (!fixed_init.empty()) {
+                if ((int)fixed_init.size() != k) throw std::runtime_error("--init-centroids: needs exactly k sample indices");
+                init = fixed_init;
+            } else {
+                // k-means++ (utils/math/kmeans.hpp:614-659): first centroid uniform, the others with probability
+                // proportional to the squared distance to the nearest centroid chosen so far
+                if (D.empty()) { D.resize((size_t)n * n); check_krd(h, krd_compute(h, 1.0, 1.0, D.data())); }
+                init.push_back((int32_t)std::uniform_int_distribution<size_t>(0, (size_t)n - 1)(engine));
+                std::vector<double> probs((size_t)n);
+                for (int c = 1; c < k; ++c) {
+                    for (int d = 0; d < n; ++d) {
+                        double m = std::numeric_limits<double>::max();
+                        for (int32_t q : init) m = std::min(m, D[(size_t)d * n + q]);
+                        probs[(size_t)d] = m * m;
+                    }
+                    init.push_back((int32_t)std::discrete_distribution<size_t>(probs.begin(), probs.end())(engine));
+                }
+            }
+            int32_t iterations = 0;
+            check_krd(h, krd_kmeans(h, k, 100, init.data(), assign.data(), dist.data(), &iterations));
+            log.msg("Finished after " + std::to_string(iterations) + " iterations");
+            std::ofstream out(outs[ki], std::ios::binary);
+            if (!out) throw std::runtime_error("Cannot open output file '" + outs[ki] + "'.");
+            out << "Sample\tCluster\tDistance\n";
+            for (int d = 0; d < n; ++d) out << sample_label(files[(size_t)d]) << "\t" << assign[(size_t)d] << "\t" << fmt_g(dist[(size_t)d]) << "\n";
+            // print_cluster_info (kmeans.cpp:194-248)
+            double avg_dst = 0.0, avg_var = 0.0;
+            for (int c = 0; c < k; ++c) {
+                double cd = 0.0, cv = 0.0; size_t cnt = 0;
+                for (int d = 0; d < n; ++d) if (assign[(size_t)d] == c) { avg_dst += dist[(size_t)d]; avg_var += dist[(size_t)d] * dist[(size_t)d]; cd += dist[(size_t)d]; cv += dist[(size_t)d] * dist[(size_t)d]; ++cnt; }
+                log.msg("Cluster " + std::to_string(c) + ": " + std::to_string(cnt) + " samples, with a variance of " + fmt_g(cnt ? cv / (double)cnt : 0.0) +
+                        " and average distance " + fmt_g(cd / (double)cnt));
+            }
+            avg_dst /= (double)n; avg_var /= (double)n;
+            log.msg("Total average distance: " + fmt_g(avg_dst));
+            log.msg("Total average variance: " + fmt_g(avg_var));
+            overview.push_back({k, avg_dst, avg_var});
+        }
+    } catch (...) { krd_destroy(h); throw; }
+    krd_destroy(h);
+    if (o.overview_file) {
+        std::ofstream out(outs.back(), std::ios::binary);
+        if (!out) throw std::runtime_error("Cannot open output file '" + outs.back() + "'.");
+        out << "k\tDistance\tVariance\n";
+        for (const auto& r : overview) out << r.k << "\t" << fmt_g(r.dist) << "\t" << fmt_g(r.var) << "\n";
+    }
+    log.msg("Finished");
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv)
@@ -286,7 +438,7 @@ int main(int argc, char** argv)
     Log log;
     if (!o.log_file.empty()) log.file.open(o.log_file);
     try {
-        return o.squash ? run_squash(o, log) : run_krd(o, log);
+        return o.kmeans ? run_kmeans(o, log) : o.squash ? run_squash(o, log) : run_krd(o, log);
     } catch (std::exception const& ex) {
         std::cerr << "Error: " << ex.what() << std::endl;
         if (log.file.is_open()) log.file << "Error: " << ex.what() << std::endl;

@@ -13,6 +13,7 @@ Writes
                            (default / --point-mass / --ignore-multiplicities) + diameter + pendant,
                            reference matrices p = 1, 2, 0.5.
   csv/cluster.newick       `analyze squash`: reference SquashClustering mergers as the Newick text squash.cpp writes
+  csv/k_2_assignments.csv, overview.csv   `analyze phylogenetic-kmeans`: reference MassTreeKmeans result in the files' format
   csv/*.csv                reference MatrixWriter output of the reference p = 1 matrix in the three
                            formats (with/without labels), plus the normalised one; and cfg1's
                            krd_matrix.csv (7847 bytes, test/scripts/analyze-krd-1.sh:7).
@@ -107,7 +108,11 @@ def make_jplace(path, seed, version=3, fields_first=False, use_prox=False, gz=Fa
     # numbers with exponents: rewrite some LWRs in scientific notation (same value text-wise is not
     # required; the reference parses whatever is written)
     text = text.replace("-1234.5", "-1.2345e3", 3)
-    (gzip.open if gz else open)(path, "wt").write(text)
+    if gz:
+        with open(path, "wb") as raw, gzip.GzipFile(filename="", mode="wb", fileobj=raw, mtime=0) as f:   # reproducible bytes
+            f.write(text.encode())
+    else:
+        open(path, "w").write(text)
 
 
 def pack(prefix, out, tree, mass, ex):
@@ -152,6 +157,15 @@ def main():
     mg = np.zeros(len(idx), krd.MERGER_DTYPE)
     mg["index_a"], mg["index_b"], mg["distance_a"], mg["distance_b"] = idx[:, 0], idx[:, 1], dst[:, 0], dst[:, 1]
     open(os.path.join(cd, "cluster.newick"), "w").write(krd.squash_tree_string(labels, mg))
+    # `analyze phylogenetic-kmeans --bins 5 --k 2` started from samples 0 and 3: reference assignments table
+    # (write_assignment_file, src/commands/analyze/kmeans.cpp:163-192) and overview (kmeans.cpp:194-269)
+    a, d, v, it, _ = oracle.ref_kmeans(tree, mass, 2, [0, 3], bins=5)
+    with open(os.path.join(cd, "k_2_assignments.csv"), "w") as f:
+        f.write("Sample\tCluster\tDistance\n")
+        for lab, ai, di in zip(labels, a, d):
+            f.write("%s\t%d\t%g\n" % (lab, ai, di))
+    with open(os.path.join(cd, "overview.csv"), "w") as f:
+        f.write("k\tDistance\tVariance\n%d\t%g\t%g\n" % (2, d.sum() / len(d), (d * d).sum() / len(d)))
     g = np.load(os.path.join(HERE, "cfg1.npz"))
     oracle.ref_write_matrix(os.path.join(cd, "cfg1_krd_matrix.csv"), g["m_p1.0"], "matrix", [str(x) for x in g["names"]])
     print("cfg1 csv bytes", os.path.getsize(os.path.join(cd, "cfg1_krd_matrix.csv")))

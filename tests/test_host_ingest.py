@@ -229,6 +229,26 @@ def test_cli_squash_end_to_end(tmp_path):
 
 
 @pytest.mark.gpu
+def test_cli_phylogenetic_kmeans_end_to_end(tmp_path):
+    base = [host.CLI_PATH, "analyze", "phylogenetic-kmeans", "--jplace-path", JP, "--out-dir", str(tmp_path / "o"), "--bins", "5"]
+    r = subprocess.run(base + ["--k", "2", "--init-centroids", "0,3", "--write-overview-file"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for name in ("k_2_assignments.csv", "overview.csv"):
+        assert (tmp_path / "o" / name).read_text() == open(os.path.join(GOLD, "csv", name)).read()
+    # k-means++ start (seeded): every k of the range list gets its table; clusters are non-empty
+    r = subprocess.run(base + ["--k", "1-3", "--seed", "7", "--file-prefix", "pp_"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for k in (1, 2, 3):
+        rows = (tmp_path / "o" / f"pp_k_{k}_assignments.csv").read_text().splitlines()
+        assert rows[0] == "Sample\tCluster\tDistance" and len(rows) == 6
+        assert sorted({int(x.split("\t")[1]) for x in rows[1:]}) == list(range(k))
+    r = subprocess.run(base + ["--k", "2,x"], capture_output=True, text=True)
+    assert r.returncode != 0 and "Invalid list of values for k" in r.stderr
+    r = subprocess.run(base[:-2] + ["--k", "2"], capture_output=True, text=True)
+    assert r.returncode != 0 and "--bins" in r.stderr
+
+
+@pytest.mark.gpu
 def test_cli_exponent_error_message(tmp_path):
     r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path), "--exponent", "-1"],
                        capture_output=True, text=True)

@@ -256,6 +256,55 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
     return compute_impl(h, p, divisor, rank, world, nullptr, d_packed);
 }
 
+krd_status krd_compute_shard_host(krd_handle* h, double p, double divisor, int32_t rank, int32_t world, double* packed)
+{
+    krd_status st = check_compute(h, p, divisor);
+    if (st != KRD_OK) return st;
+    if (world < 1 || rank < 0 || rank >= world) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad rank/world");
+    if (!packed) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    const size_t bytes = (size_t)krd_shard_doubles(h, world) * 8;
+    if (bytes == 0) return KRD_OK;
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    if (bytes > h->out_tmp_capacity) {
+        cudaFree(h->d_out_tmp); h->d_out_tmp = nullptr; h->out_tmp_capacity = 0;
+        KRD_CUDA(h, cudaMalloc(&h->d_out_tmp, bytes));
+        h->out_tmp_capacity = bytes;
+    }
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        st = compute_impl(h, p, divisor, rank, world, nullptr, h->d_out_tmp);
+        if (st != KRD_OK) return st;
+        KRD_CUDA(h, cudaMemcpyAsync(packed, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (!h->fix_pending) break;
+        krd_stats tmp;
+        krd_get_stats(h, &tmp);
+        if (tmp.gram_fixups >= 0 || attempt == 1) break;
+        h->cfg.p2_mode = 1;      // fix-up list overflowed: this handle stays on the direct p = 2 path
+    }
+    return KRD_OK;
+}
+
+krd_status krd_unpack_shards_host(int32_t n_samples, int32_t world, const double* packed_all, double* out)
+{
+    if (n_samples < 0 || world < 1 || (n_samples > 0 && (!packed_all || !out))) return KRD_ERR_INVALID_ARGUMENT;
+    const int64_t n_tiles = krd_tile_count(n_samples), per_rank = tiles_per_rank(n_tiles, world), N = n_samples;
+    std::vector<int32_t> ti((size_t)n_tiles), tj((size_t)n_tiles);
+    krd_tile_list(n_samples, ti.data(), tj.data());
+    for (int64_t t = 0; t < n_tiles; ++t) {
+        // rank r holds tiles [r*per_rank, (r+1)*per_rank) back to back, ranks concatenated in order: tile t at offset t
+        (void)per_rank;
+        const double* src = packed_all + (size_t)t * (TILE * TILE);
+        const int64_t i0 = (int64_t)ti[(size_t)t] * TILE, j0 = (int64_t)tj[(size_t)t] * TILE;
+        for (int64_t r = 0; r < TILE && i0 + r < N; ++r)
+            for (int64_t c = 0; c < TILE && j0 + c < N; ++c) {
+                const int64_t i = i0 + r, j = j0 + c;
+                if (i < j) { const double v = src[r * TILE + c]; out[i * N + j] = v; out[j * N + i] = v; }
+                else if (i == j) out[i * N + i] = 0.0;
+            }
+    }
+    return KRD_OK;
+}
+
 krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;

@@ -700,11 +700,8 @@ static krd_status build_F_tiled(krd_handle* h)
 {
     const int B1 = h->cfg.bins + 1;
     const size_t smem_fill = (size_t)h->EB * B1 * FTS * sizeof(double), smem_tot = (size_t)h->EB * FTS * sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        KRD_CUDA(h, cudaFuncSetAttribute(k_tile<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAX_ROWS * FTS * 8));
-        configured = true;
-    }
+    static std::atomic<unsigned long long> configured{0};
+    KRD_CUDA(h, allow_dynamic_smem(k_tile<true>, FT_MAX_ROWS * FTS * 8, configured));
     if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero
         KRD_CUDA(h, cudaMemsetAsync(h->d_F + (size_t)h->S * h->ld, 0, (size_t)(h->S_pad - h->S) * h->ld * 8, h->stream));
     dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ld / FT));
@@ -722,11 +719,8 @@ static krd_status build_F_tiled(krd_handle* h)
         k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, h->ld, h->d_M, h->d_D);
     }
     if (use_top) {
-        static bool top_configured = false;
-        if (!top_configured) {
-            KRD_CUDA(h, cudaFuncSetAttribute(k_subtree_top, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            top_configured = true;
-        }
+        static std::atomic<unsigned long long> top_configured{0};
+        KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
         k_subtree_top<<<(unsigned)(h->ld / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
                                                                                  h->ld, h->d_M, h->d_D);
         ++n_launch;

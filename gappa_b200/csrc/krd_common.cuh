@@ -1,6 +1,7 @@
 // Shared internals of libkrd_b200.so (sm_100a only).  See include/krd_b200.h for the C ABI and
 // DESIGN.md for the data layout.  Reference semantics: genesis tree/mass_tree/emd.cpp:60-235.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -124,6 +125,20 @@ krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what);
         cudaError_t _e = (call);                                       \
         if (_e != cudaSuccess) return krd::cuda_fail((h), _e, #call);  \
     } while (0)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE setting: remember it per device (one process may hold
+// handles on several GPUs, e.g. `gappa-b200 --gpus G`), not per process.
+template <typename Kernel>
+inline cudaError_t allow_dynamic_smem(Kernel kernel, int bytes, std::atomic<unsigned long long>& done_mask)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 64 && ((done_mask.load(std::memory_order_acquire) >> dev) & 1ull)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && dev < 64) done_mask.fetch_or(1ull << dev, std::memory_order_release);
+    return e;
+}
 
 // grow-only device buffer: reallocates *p only when `bytes` exceeds its recorded capacity
 krd_status reserve(krd_handle* h, void** p, size_t bytes);

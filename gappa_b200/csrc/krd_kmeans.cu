@@ -180,10 +180,10 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
         else launch_assign<32>(h, k, rpc, part);
         k_km_assign_final<<<(unsigned)((N + 31) / 32), dim3(32, (unsigned)k), 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
     };
-    static bool configured = false;
+    static std::atomic<unsigned long long> configured{0};
     const size_t smem_row = (size_t)N * 8;
     if (smem_row > 200 * 1024) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: more than 25,600 samples are not supported");
-    if (!configured) { KRD_CUDA(h, cudaFuncSetAttribute(k_km_update, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); configured = true; }
+    KRD_CUDA(h, allow_dynamic_smem(k_km_update, 200 * 1024, configured));
 
     int iteration = 0, changed = 0, launches = 2;
     std::vector<int32_t> mem((size_t)N), mem_off((size_t)k + 1);

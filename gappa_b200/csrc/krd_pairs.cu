@@ -529,12 +529,9 @@ static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, d
 template <int MODE>
 static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stream)
 {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_pairs<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    static std::atomic<unsigned long long> configured{0};
+    cudaError_t e = allow_dynamic_smem(k_pairs<MODE>, (int)SMEM_BYTES, configured);
+    if (e != cudaSuccess) return e;
     k_pairs<MODE><<<grid, NT, SMEM_BYTES, stream>>>(P);
     return cudaGetLastError();
 }

@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(_HERE, "libkrd_host.so")
 CLI_PATH = os.path.join(_HERE, "gappa-b200")
 
 EXPORTS = ["krd_host_last_error", "krd_host_load_jplace", "krd_host_free_set", "krd_host_set_sizes",
-           "krd_host_set_copy", "krd_host_set_label", "krd_host_write_matrix", "krd_host_parse_number"]
+           "krd_host_set_copy", "krd_host_set_label", "krd_host_write_matrix", "krd_host_parse_number",
+           "krd_host_add_pendant_work"]
 
 _lib = None
 
@@ -36,6 +37,7 @@ def lib():
         L.krd_host_write_matrix.restype = C.c_int64
         L.krd_host_write_matrix.argtypes = [C.c_char_p, vp, C.c_int32, C.c_char_p, C.POINTER(C.c_char_p), C.c_char_p,
                                             C.c_int32, C.c_int32]
+        L.krd_host_add_pendant_work.argtypes = [vp, C.c_int32, vp]
         L.krd_host_parse_number.restype = C.c_double
         L.krd_host_parse_number.argtypes = [C.c_char_p]
         _lib = L
@@ -82,3 +84,13 @@ def write_matrix(path, matrix, fmt="matrix", labels=None, corner="Sample", gzip=
 
 def parse_number(text):
     return float(lib().krd_host_parse_number(text.encode()))
+
+
+def add_pendant_work(matrix, pendant):
+    """placement::earth_movers_distance(SampleSet, p, with_pendant_length=true) from the mass-tree matrix
+    (placement/function/emd.cpp:107-129): returns matrix + pendant[i] + pendant[j] in every cell."""
+    m = np.array(matrix, np.float64, order="C")
+    pend = np.ascontiguousarray(pendant, np.float64)
+    assert m.ndim == 2 and m.shape[0] == m.shape[1] == len(pend)
+    lib().krd_host_add_pendant_work(m.ctypes.data, m.shape[0], pend.ctypes.data)
+    return m

@@ -86,4 +86,12 @@ double krd_host_parse_number(const char* text)
     try { return js.number().as_double(); } catch (...) { return std::nan(""); }
 }
 
+void krd_host_add_pendant_work(double* m, int32_t n, const double* pendant)
+{
+    // placement::earth_movers_distance( SampleSet, p, with_pendant_length = true ), placement/function/emd.cpp:118-126:
+    // every cell (the diagonal too) gets the pendant work of both of its samples
+    for (int64_t i = 0; i < n; ++i)
+        for (int64_t j = 0; j < n; ++j) m[i * n + j] += pendant[i] + pendant[j];
+}
+
 }  // extern "C"

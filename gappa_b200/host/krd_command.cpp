@@ -11,7 +11,8 @@
 //   gappa-b200 analyze phylogenetic-kmeans --jplace-path ... --k "1-5,8" --bins B [--write-overview-file] [--point-mass]
 //        [--ignore-multiplicities] [--out-dir d] [--file-prefix s] [--file-suffix s]  -> k_<k>_assignments.csv, overview.csv
 //        (gappa src/commands/analyze/kmeans_phylogenetic.cpp:134-199; additive: --seed n, --init-centroids i,j,...)
-//   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d,
+//   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d, --gpus G (analyze krd: tiles
+//             sharded over devices d..d+G-1, one host thread per GPU),
 //             --write-binary f (raw row-major doubles, for full-precision comparisons)
 //
 // Exit code 0 on success; on error prints "Error: <message>" like src/main.cpp:167-173 and exits 1.
@@ -22,6 +23,7 @@
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <thread>
 #include <limits>
 #include <random>
 #include <sstream>
@@ -46,7 +48,7 @@ struct KrdOptions {
     bool normalize = false, point_mass = false, ignore_multiplicities = false;
     std::string out_dir = ".", prefix, suffix, matrix_format = "matrix", log_file, write_binary;
     bool compress = false, omit_labels = false, allow_overwrite = false, verbose = false;
-    int threads = 0, bins = 0, device = 0;
+    int threads = 0, bins = 0, device = 0, gpus = 1;
 };
 
 const char* kUsage =
@@ -62,7 +64,7 @@ const char* kUsage =
     "  --seed INT  --init-centroids LIST (phylogenetic-kmeans, additive) k-means++ seed / explicit start samples.\n"
     "Matrix Output:\n  --out-dir TEXT=.  --file-prefix TEXT  --file-suffix TEXT  --compress\n"
     "  --matrix-format TEXT=matrix       matrix | list | triangular\n  --omit-matrix-labels\n"
-    "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --help\n";
+    "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --gpus INT  --help\n";
 
 [[noreturn]] void usage_error(const std::string& msg)
 {
@@ -127,6 +129,7 @@ KrdOptions parse_args(int argc, char** argv)
         else if (a == "--log-file") o.log_file = value();
         else if (a == "--bins") o.bins = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--device") o.device = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
+        else if (a == "--gpus") o.gpus = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--write-binary") o.write_binary = value();
         else if (a == "--k") o.ks = value();
         else if (a == "--write-overview-file") o.overview_file = true;
@@ -142,6 +145,7 @@ KrdOptions parse_args(int argc, char** argv)
     if (!valid_filefix(o.suffix)) usage_error("--file-suffix: File suffix contains invalid characters (`<>:\"\\/|?*`), non-printable characters, or surrounding whitespace.");
     parse_matrix_format(o.matrix_format);   // validates
     if (o.bins < 0) usage_error("--bins: must be >= 0");
+    if (o.gpus < 1 || o.gpus > 64) usage_error("--gpus: must be in 1..64");
     if (o.threads <= 0) {
         o.threads = (int)std::thread::hardware_concurrency();
         if (o.threads <= 0) o.threads = 1;
@@ -199,21 +203,65 @@ int run_krd(const KrdOptions& o, Log& log)
 
     log.msg("Calculating pairwise KR distances.");
     const int32_t n = ms.n_samples();
-    krd_config cfg{};
-    cfg.device = o.device; cfg.bins = o.bins;
-    krd_handle* h = nullptr;
-    if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
     std::vector<double> matrix((size_t)n * (size_t)n, 0.0);
     krd_stats st{};
-    try {
-        check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
-        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
-        // krd.cpp:144-150: --normalize divides by the DIAMETER of the (averaged) tree
-        const double divisor = o.normalize ? diameter(ms.tree) : 1.0;
-        check_krd(h, krd_compute(h, o.exponent, divisor, matrix.data()));
-        krd_get_stats(h, &st);
-    } catch (...) { krd_destroy(h); throw; }
-    krd_destroy(h);
+    // krd.cpp:144-150: --normalize divides by the DIAMETER of the (averaged) tree
+    const double divisor = o.normalize ? diameter(ms.tree) : 1.0;
+    if (o.gpus <= 1) {
+        krd_config cfg{};
+        cfg.device = o.device; cfg.bins = o.bins;
+        krd_handle* h = nullptr;
+        if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
+        try {
+            check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
+            check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+            check_krd(h, krd_compute(h, o.exponent, divisor, matrix.data()));
+            krd_get_stats(h, &st);
+        } catch (...) { krd_destroy(h); throw; }
+        krd_destroy(h);
+    } else {
+        // --gpus G (additive): one host thread per GPU (devices o.device .. o.device+G-1), every GPU
+        // gets the replicated inputs over its own PCIe link, computes its contiguous share of the tile list and
+        // copies its packed tiles back; the host scatters them into the matrix.  No collective: only the host
+        // needs the result (the NCCL all-gather variant is what bench.py / one-process-per-GPU callers use).
+        const int G = o.gpus;
+        std::vector<std::string> errors((size_t)G);
+        std::vector<krd_stats> stats((size_t)G);
+        std::vector<double> packed;
+        std::vector<std::thread> workers;
+        std::vector<krd_handle*> hs((size_t)G, nullptr);
+        int64_t shard = -1;
+        // phase 1: create + upload on all GPUs concurrently
+        for (int g = 0; g < G; ++g) workers.emplace_back([&, g]() {
+            try {
+                krd_config cfg{};
+                cfg.device = o.device + g; cfg.bins = o.bins;
+                if (krd_create(&cfg, &hs[(size_t)g]) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
+                krd_handle* h = hs[(size_t)g];
+                check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
+                check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+            } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
+        });
+        for (auto& w : workers) w.join();
+        workers.clear();
+        auto cleanup = [&]() { for (auto* h : hs) if (h) krd_destroy(h); };
+        for (const auto& e : errors) if (!e.empty()) { cleanup(); throw std::runtime_error(e); }
+        shard = krd_shard_doubles(hs[0], G);
+        packed.assign((size_t)shard * (size_t)G, 0.0);
+        // phase 2: every GPU computes and returns its share
+        for (int g = 0; g < G; ++g) workers.emplace_back([&, g]() {
+            try {
+                check_krd(hs[(size_t)g], krd_compute_shard_host(hs[(size_t)g], o.exponent, divisor, g, G, packed.data() + (size_t)g * (size_t)shard));
+                krd_get_stats(hs[(size_t)g], &stats[(size_t)g]);
+            } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
+        });
+        for (auto& w : workers) w.join();
+        cleanup();
+        for (const auto& e : errors) if (!e.empty()) throw std::runtime_error(e);
+        if (krd_unpack_shards_host(n, G, packed.data(), matrix.data()) != KRD_OK) throw std::runtime_error("krd_unpack_shards_host failed");
+        st = stats[0];
+        for (const auto& q : stats) { st.ms_pairs = std::max(st.ms_pairs, q.ms_pairs); st.ms_build = std::max(st.ms_build, q.ms_build); }
+    }
     auto t2 = clk::now();
 
     log.msg("Writing distance matrix.");

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -108,6 +108,10 @@ def lib():
     L.krd_compute_shard.argtypes = [vp, dbl, dbl, i32, i32, vp]
     L.krd_unpack_shards.restype = C.c_int
     L.krd_unpack_shards.argtypes = [vp, i32, vp, vp]
+    L.krd_compute_shard_host.restype = C.c_int
+    L.krd_compute_shard_host.argtypes = [vp, dbl, dbl, i32, i32, vp]
+    L.krd_unpack_shards_host.restype = C.c_int
+    L.krd_unpack_shards_host.argtypes = [i32, i32, vp, vp]
     L.krd_kmeans.restype = C.c_int
     L.krd_kmeans.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(C.c_int32)]
     L.krd_squash.restype = C.c_int
@@ -225,6 +229,12 @@ class KrdPlan:
     def unpack_shards(self, d_gathered, d_out, world):
         self._check(self._L.krd_unpack_shards(self._h, world, _ptr(d_gathered), _ptr(d_out)))
 
+    def compute_shard_host(self, rank, world, p=1.0, divisor=1.0):
+        """This rank's packed tiles in a HOST array (krd_compute_shard_host)."""
+        out = np.zeros(self.shard_doubles(world), np.float64)
+        self._check(self._L.krd_compute_shard_host(self._h, float(p), float(divisor), rank, world, _ptr(out)))
+        return out
+
     def squash(self, p=1.0):
         """genesis SquashClustering::run on the resident samples: returns the n-1 mergers as a structured array
         (index_a, index_b, distance_a, distance_b), squash_clustering.hpp:98-119."""
@@ -263,6 +273,16 @@ class KrdPlan:
         ln = np.zeros(s["n_segments"], np.float64)
         self._check(self._L.krd_debug_copy_F(self._h, _ptr(F), _ptr(ln)))
         return F, ln
+
+
+def unpack_shards_host(n_samples, packed_per_rank):
+    """Host-only: the ranks' packed tile buffers (list, rank order) -> symmetric n x n matrix (krd_unpack_shards_host)."""
+    allp = np.ascontiguousarray(np.concatenate(packed_per_rank), np.float64)
+    out = np.zeros((n_samples, n_samples), np.float64)
+    st = lib().krd_unpack_shards_host(n_samples, len(packed_per_rank), _ptr(allp), _ptr(out))
+    if st != 0:
+        raise KrdError(st, "krd_unpack_shards_host failed")
+    return out
 
 
 def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):

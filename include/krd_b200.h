@@ -120,6 +120,14 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
  * full symmetric n x n DEVICE matrix. */
 krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out);
 
+/* The same for a caller without an NCCL communicator (e.g. one host thread per GPU in one process, as
+ * `gappa-b200 --gpus G` does): the rank's packed tiles go to a HOST buffer of krd_shard_doubles() doubles
+ * (D2H over that GPU's own PCIe link), and the concatenation of all ranks' buffers, in rank order, is
+ * scattered into the symmetric n x n HOST matrix on the host (no GPU, no handle needed). */
+krd_status krd_compute_shard_host(krd_handle* h, double p, double divisor, int32_t rank, int32_t world,
+                                  double* packed);
+krd_status krd_unpack_shards_host(int32_t n_samples, int32_t world, const double* packed_all, double* out);
+
 /* Host-only helpers (no GPU needed) describing the sharding, so that callers and tests can reason
  * about it: the upper triangle of 128x128 tiles (off-diagonal tiles in diagonal-major order (i,i+1), (i,i+2), ...
  * with the cheaper diagonal tiles (i,i) spread evenly through the list, so that equal-count shares are

@@ -47,6 +47,12 @@ const char* krd_host_set_label(const krd_host_set* s, int32_t i);
 int64_t krd_host_write_matrix(const char* path, const double* m, int32_t n, const char* format,
                               const char* const* labels, const char* corner, int32_t gzip, int32_t threads);
 
+/* Secondary surface: placement::earth_movers_distance( SampleSet, p, with_pendant_length )
+ * (placement/function/emd.cpp:107-129) = the mass-tree matrix (krd_compute, divisor 1) plus, with
+ * with_pendant_length, pendant[i] + pendant[j] in EVERY cell including the diagonal; `pendant` is the
+ * per-sample pendant work krd_host_set_copy returns (placement/function/operators.cpp:167). In place. */
+void krd_host_add_pendant_work(double* matrix, int32_t n, const double* pendant);
+
 /* The reference's (not correctly rounded) JSON number accumulation, exposed for tests. */
 double krd_host_parse_number(const char* text);
 

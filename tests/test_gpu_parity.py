@@ -304,4 +304,9 @@ def test_sharded_compute_equals_single(gb, world):
     plan.unpack_shards(gathered, out, world)
     torch.cuda.synchronize()
     assert torch.equal(out, single)
+    # host twin (krd_compute_shard_host + krd_unpack_shards_host, what `gappa-b200 --gpus G` runs): same bits
+    from gappa_b200 import krd
+    for p in (1.0, 2.0):
+        host = krd.unpack_shards_host(300, [plan.compute_shard_host(r, world, p=p) for r in range(world)])
+        assert np.array_equal(host, plan.compute(p=p))
     plan.close()

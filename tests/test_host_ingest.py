@@ -196,6 +196,28 @@ def test_genesis_unit_test_documents_live():
         assert np.array_equal(t1["parent"], t2["parent"]) and np.array_equal(t1["bl"], t2["bl"]), f
 
 
+def test_pendant_work_secondary_surface():
+    # placement::earth_movers_distance(SampleSet, p, with_pendant_length) — genesis' own unit-test values
+    # (libs/genesis/test/src/placement/measures.cpp:84-85, 92-97, 104-109): 3.4916666 off the diagonal,
+    # 0.52499998 / 0.76666665 on it
+    z = np.load(os.path.join(GOLD, "test_ab.npz"))
+    m = host.add_pendant_work(z["m_p1.0"], z["pendant"])
+    assert np.float32(m[0, 1]) == np.float32(3.4916666) and m[0, 1] == m[1, 0]
+    assert np.float32(m[0, 0]) == np.float32(0.52499998) and np.float32(m[1, 1]) == np.float32(0.76666665)
+    assert np.array_equal(z["m_p1.0"], z["m_p1.0"].T) and z["m_p1.0"][0, 0] == 0.0   # input untouched
+
+
+@pytest.mark.gpu
+def test_pendant_work_on_gpu_matrix():
+    z = np.load(os.path.join(GOLD, "test_ab.npz"))
+    import gappa_b200
+    tree = dict(parent=z["parent"], child=z["child"], bl=z["bl"], root=int(z["root"]))
+    mass = dict(off=z["off"], edge=z["edge"], pos=z["pos"], mass=z["mass"])
+    m = host.add_pendant_work(gappa_b200.earth_movers_distance(tree, mass, p=1.0), z["pendant"])
+    assert np.float32(m[0, 1]) == np.float32(3.4916666)
+    assert np.float32(m[0, 0]) == np.float32(0.52499998) and np.float32(m[1, 1]) == np.float32(0.76666665)
+
+
 # ---- the CLI end to end on a B200 ------------------------------------------------------------------
 
 @pytest.mark.gpu
@@ -215,6 +237,26 @@ def test_cli_end_to_end(gold, tmp_path, args, csv, key):
     want = gold[key] if key else gold["default_m_p1.0"] / float(gold["default_diameter"])
     assert np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)) <= 1e-10   # north_star tolerance, FP64
     assert "Finished" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_multi_gpu_matches_single(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    for g, d in ((1, "o1"), (2, "o2")):
+        r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path / d), "--gpus", str(g),
+                            "--write-binary", str(tmp_path / f"{d}.bin")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    assert (tmp_path / "o1.bin").read_bytes() == (tmp_path / "o2.bin").read_bytes()
+    assert (tmp_path / "o2" / "krd_matrix.csv").read_bytes() == open(os.path.join(GOLD, "csv", "matrix.csv"), "rb").read()
+
+
+@pytest.mark.gpu
+def test_cli_gpus_beyond_device_count_fails_loudly(tmp_path):
+    r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path / "o"), "--gpus", "64"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "Error:" in r.stderr
 
 
 @pytest.mark.gpu

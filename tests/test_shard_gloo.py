@@ -101,3 +101,14 @@ def test_rank_shares_cover_every_tile_once():
             assert all(spans[r][1] == spans[r + 1][0] for r in range(world - 1))
             per = (len(ti) + world - 1) // world
             assert all(b - a <= per for a, b in spans)
+
+
+@pytest.mark.parametrize("world,n", [(1, 5), (2, 300), (3, 513), (8, 1000)])
+def test_unpack_shards_host_matches_device_contract(world, n):
+    # krd_unpack_shards_host is the host twin of k_unpack (used by `gappa-b200 --gpus G`): no GPU needed
+    import gappa_b200.krd as k
+    rng = np.random.default_rng(n)
+    D = rng.random((n, n)); D = np.triu(D, 1); D = D + D.T
+    packed = [pack_rank(D, n, r, world, k) for r in range(world)]
+    assert all(len(p) == len(packed[0]) for p in packed)
+    assert np.array_equal(k.unpack_shards_host(n, packed), D)

@@ -176,6 +176,7 @@ def main():
     # Weak scaling: the cohort grows with the GPU count so that every GPU keeps the pair count of the 1-GPU
     # workload (pairs ~ samples^2): samples = base * sqrt(world), rounded to whole 128-sample tiles.
     n_samples = args.samples
+    scaling = "strong" if (args.samples is not None and world > 1) else "weak"   # --samples pins the cohort: total work fixed
     if n_samples is None and world > 1:
         base = workloads.WORKLOADS[args.workload]["samples"]
         n_samples = int(round(base * np.sqrt(world) / 128.0)) * 128
@@ -285,14 +286,15 @@ def main():
         executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((st["n_tiles"] - T) + 0.625 * T) * share
         line = {
             "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": spec["name"], "samples": N, "edges": spec["edges"], "placements_per_sample": spec["placements"],
                        "bins": bins, "p": p, "segments": int(S), "pairs": int(pairs), "masses": int(st["n_masses"]),
                        "l2": "inputs larger than L2 (F %.0f MB + split workspace)" % (st["f_bytes"] / 1e6),
                        "parallelism": (f"upper-triangular tiles/{world}, F replicated, NCCL all-gather of result tiles; "
-                                       f"weak scaling: samples = {workloads.WORKLOADS[args.workload]['samples']}*sqrt({world}) "
-                                       "rounded to 128") if world > 1 else "1 gpu"},
+                                       + (f"weak scaling: samples = {workloads.WORKLOADS[args.workload]['samples']}*sqrt({world}) "
+                                          "rounded to 128" if scaling == "weak" else "strong scaling: cohort fixed by --samples"))
+                                      if world > 1 else "1 gpu"},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(N * N * 8)},
             "gpu_launches": int(st["launches"]) * args.steps,

@@ -10,16 +10,52 @@ namespace krd {
 // FP64 sqrt and pow written for the FP64 pipe's issue rate (the library versions spend > 100
 // instructions and a divergent slow path on the exact zeros that |F_i - F_j| is full of).
 //
-// sqrt: MUFU.RSQ64H seed (2^-22) + two Heron steps y += (x - y*y) * (r/2): error 2^-44, then rounding level.
-__device__ __forceinline__ double kr_sqrt(double x)   // x >= 0
+// sqrt(|d|): MUFU.RSQ64H seed r = (1 + q)/sqrt(x), |q| <= 2^-22, then ONE third-order step:
+//   y = x r,  e = 1 - y r = -2q - q^2,  sqrt(x) = y / (1 + q) = y (1 + e/2 + 3/8 e^2 + O(e^3)) = y + (y e)(1/2 + 3/8 e)
+// -> 5 FP64 instructions (DMUL, DFMA, DFMA, DMUL, DFMA), error 2^-64 before the final rounding.
+// x = 0 (and subnormal x, which the seed flushes): the seed is +inf; its high word is replaced by 0 (integer compare +
+// select on the integer pipe), which makes r vanishingly small and the result exactly 0 — no FP64 compare, no NaN.
+// |.| is a bit mask for the seed and an operand modifier for the multiply.
+__device__ __forceinline__ double kr_rsqrt_seed_abs(double d)   // ~ 1/sqrt(|d|), 0-ish for |d| < 2^-1022
 {
+    const int xh = __double2hiint(d) & 0x7fffffff;
     double r;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));   // MUFU.RSQ64H: ~2^-22, no FP32 round trip; x = 0 -> +inf
-    double y = x * r;
-    const double hr = 0.5 * r;
-    y = fma(fma(-y, y, x), hr, y);
-    y = fma(fma(-y, y, x), hr, y);
-    return x > 1e-300 ? y : 0.0;                              // zero (and flushed subnormals): 0 * inf = NaN is replaced
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(__hiloint2double(xh, __double2loint(d))));   // MUFU.RSQ64H (reads the high word)
+    return __hiloint2double(xh < 0x00100000 ? 0 : __double2hiint(r), __double2loint(r));
+}
+
+__device__ __forceinline__ double kr_sqrt_abs(double d)
+{
+    const double r = kr_rsqrt_seed_abs(d);
+    const double y = fabs(d) * r;
+    const double e = fma(-y, r, 1.0);
+    const double t = fma(0.375, e, 0.5);
+    return fma(y * e, t, y);
+}
+
+// One row of the register tile for p = 1/2, written stage by stage over the NC columns so that the NC independent
+// dependency chains are interleaved in program order (ptxas otherwise pairs the chains two at a time and the FP64
+// latency shows: 44 % of the stall samples were fixed-latency waits).
+template <int NC>
+__device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__ b, double l, double* __restrict__ acc)
+{
+    double d[NC], r[NC], e[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = a - b[c];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) r[c] = kr_rsqrt_seed_abs(d[c]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fabs(d[c]) * r[c];          // y
+#pragma unroll
+    for (int c = 0; c < NC; ++c) e[c] = fma(-d[c], r[c], 1.0);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) r[c] = fma(0.375, e[c], 0.5);      // t
+#pragma unroll
+    for (int c = 0; c < NC; ++c) e[c] = d[c] * e[c];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fma(e[c], r[c], d[c]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) acc[c] = fma(l, d[c], acc[c]);
 }
 
 // pow(x, p) = exp2(p * log2 x), x >= 0, p > 0.  Table-driven, all in FP64, relative error < 1e-14:
@@ -73,7 +109,7 @@ __device__ __forceinline__ double pair_op(double a, double b, double l, double p
 {
     if (MODE == MODE_P1) return fma(l, fabs(a - b), acc);
     if (MODE == MODE_P2) { double d = a - b; return fma(d, d, acc); }   // operands pre-scaled by sqrt(len)
-    if (MODE == MODE_PHALF) return fma(l, kr_sqrt(fabs(a - b)), acc);
+    if (MODE == MODE_PHALF) return fma(l, kr_sqrt_abs(a - b), acc);
     if (MODE == MODE_INT) return fma(l, kr_powi(fabs(a - b), (int)p), acc);
     if (MODE == MODE_P3) { const double d = fabs(a - b); return fma(l * d, d * d, acc); }
     if (MODE == MODE_P4) { const double d = a - b, d2 = d * d; return fma(l * d2, d2, acc); }

@@ -17,6 +17,7 @@
 // kernel adds the partials of a tile in fixed order, applies the outer root / divisor and mirrors.
 // FP64 CUDA cores only: per (pair, segment) p = 1 costs DADD + DFMA, the floor for this operator.
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 
 #include "krd_common.cuh"
@@ -85,15 +86,26 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
 
 // per-CTA (start, end, first item, last item) of the last pair launch in %globaltimer ns — tuning aid, read by krd_debug_cta_times
 __device__ unsigned long long g_cta_time[4 * 1024];
+__device__ unsigned long long g_item_time[2 * 4096];   // (start, end) per work item as seen by warp 0 — tuning aid
 
 // One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
 // (diagonal tiles: blocks that lie entirely below the diagonal).
+#ifndef KRD_P12_UNROLL
+#define KRD_P12_UNROLL 4
+#endif
+#ifndef KRD_P34_UNROLL
+#define KRD_P34_UNROLL 2
+#endif
+// unroll factor of the segment loop: the short operators (p = 1, 2) are unrolled 4x; the long ones keep ONE segment
+// (64 independent operators, fixed accumulator registers) as the loop body so that it stays inside the instruction cache
+constexpr int mode_unroll(int mode) { return (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC) ? 1 : (mode == MODE_P3 || mode == MODE_P4) ? KRD_P34_UNROLL : KRD_P12_UNROLL; }
+
 template <int MODE, int QMIN>
 __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const double* __restrict__ pb,
                                            const double* __restrict__ sL, double p, const double* __restrict__ tab,
                                            double (&acc)[8][8])
 {
-#pragma unroll 4
+#pragma unroll (mode_unroll(MODE))
     for (int kk = 0; kk < KC; ++kk) {
         double a[8], b[8];
         const double l = sL[kk];
@@ -113,10 +125,15 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
 #pragma unroll
             for (int q = 2 * QMIN; q < 8; ++q) b[q] *= l;
         }
+        if (MODE == MODE_PHALF) {
 #pragma unroll
-        for (int r = 0; r < 8; ++r)
+            for (int r = 0; r < 8; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+        } else {
 #pragma unroll
-            for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
+        }
     }
 }
 
@@ -162,7 +179,10 @@ __device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa,
     }
 }
 
-constexpr bool mode_is_rolled(int mode) { return mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC; }
+#ifndef KRD_ROTATING_BODY
+#define KRD_ROTATING_BODY 0     // 1: the two-row rotating body also for p = 1/2 (A/B measurements)
+#endif
+constexpr bool mode_is_rolled(int mode) { return (KRD_ROTATING_BODY && mode == MODE_PHALF) || mode == MODE_INT || mode == MODE_GENERIC; }
 
 // ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
 // Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
@@ -269,6 +289,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
         const int qmin = (diag && MODE != MODE_P2G && !mode_is_rolled(MODE)) ? (rg >> 1) : 0;
+        if (threadIdx.x == 0 && item < 4096) { unsigned long long tt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tt)); g_item_time[2 * item] = tt; }
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -299,6 +320,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             if (lane == 0) mbar_arrive(&empty[s]);
         }
 
+        if (threadIdx.x == 0 && item < 4096) { unsigned long long tt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tt)); g_item_time[2 * item + 1] = tt; }
         // partial tile -> workspace; row = row0 + r, col = 32*q + 2*tx + {0,1}
         double* wout = P.ws + (size_t)item * (size_t)(TILE * TILE);
         if (MODE == MODE_P2G) {
@@ -553,12 +575,19 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
 
     const int mode = mode_for_exponent(p, h->cfg.p2_mode != 1);   // p = 2: auto = Gram on the tensor cores + direct fix-ups
     const bool full_diag = (mode == MODE_P2G) || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
-    const double diag_cost = full_diag ? 1.0 : DIAG_COST_SKIP;
+    // cost of a diagonal-tile chunk relative to a full one: 5/8 of the math, but the warps of a diagonal tile carry unequal
+    // shares (the top row groups skip nothing).  p = 1, 2 are FP64-pipe-bound, so the lighter warps free the pipe for the
+    // others (measured 0.705); the long operators are bound by each warp's own dependency chains, so the tile takes almost
+    // as long as a full one (measured: p = 1/2 0.925, p = 3, 4 0.8; profiles/cta_balance.py).  Diagonal tiles also run FOUR
+    // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
+    // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.925 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 
     const int n_chunks = (int)(h->S_pad / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
-    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 2 + (full_diag ? 1 : 0);
+    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 4096 + (int64_t)(diag_cost * 2048.0);
     if (key != h->sched_key) {
         std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
         make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
@@ -673,6 +702,11 @@ krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j)
 }
 
 /* tuning aid (not part of the product surface): per-CTA start/end (ns) and item range of the last pair launch */
+int krd_debug_item_times(unsigned long long* out, int n_items)
+{
+    return (int)cudaMemcpyFromSymbol(out, krd::g_item_time, sizeof(unsigned long long) * 2 * (size_t)std::min(n_items, 4096));
+}
+
 int krd_debug_cta_times(unsigned long long* out, int n_ctas)
 {
     return (int)cudaMemcpyFromSymbol(out, krd::g_cta_time, sizeof(unsigned long long) * 4 * (size_t)std::min(n_ctas, 1024));

@@ -31,6 +31,16 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double seed, int iters, doubl
                     x[i] = x[i] + fabs(d);
                 } else if (MODE == 5) {
                     x[i] = fma(a, b, x[i]);
+                } else if (MODE == 6) {       // MUFU.RSQ64H: the FP64 reciprocal-square-root seed
+                    asm volatile("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(x[i]) : "d"(x[i]));
+                } else if (MODE == 7) {       // MUFU.RSQ: the FP32 seed
+                    float f = __int_as_float(__double2hiint(x[i]));
+                    asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"(f));
+                    x[i] = __hiloint2double(__float_as_int(f), __double2loint(x[i]));
+                } else if (MODE == 8) {       // F2F.F32.F64 + F2F.F64.F32 round trip
+                    float f;
+                    asm volatile("cvt.rn.f32.f64 %0, %1;" : "=f"(f) : "d"(x[i]));
+                    asm volatile("cvt.f64.f32 %0, %1;" : "=d"(x[i]) : "f"(f));
                 } else {
                     double d = x[i] - y[(i + k) % ILP];
                     x[i] = fma(a, fabs(d), x[i]);
@@ -85,12 +95,16 @@ extern "C" double krd_measure_fp64_peak(int device, int mode, double ms_target)
         else if (mode == 3) k_fp64_peak<3><<<grid, block>>>(1.000001, iters, sink);
         else if (mode == 4) k_fp64_peak<4><<<grid, block>>>(1.000001, iters, sink);
         else if (mode == 5) k_fp64_peak<5><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 6) k_fp64_peak<6><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 7) k_fp64_peak<7><<<grid, block>>>(1.000001, iters, sink);
+        else if (mode == 8) k_fp64_peak<8><<<grid, block>>>(1.000001, iters, sink);
         else k_dmma_peak<<<grid, block>>>(1.000001, iters, sink);
     };
     auto flops = [&](int iters) -> double {
         const double threads = (double)grid * block;
         if (mode == 0 || mode == 5) return threads * iters * (double)INNER * ILP * 2.0;
-        if (mode == 3) return threads * iters * (double)INNER * ILP * 1.0;            // DADD only, 1 flop each
+        if (mode == 3 || mode == 6 || mode == 7) return threads * iters * (double)INNER * ILP * 1.0;   // 1 op each
+        if (mode == 8) return threads * iters * (double)INNER * ILP * 2.0;            // two conversions
         if (mode == 4) return threads * iters * (double)INNER * ILP * 2.0;            // DADD + DADD
         if (mode == 1) return threads * iters * (double)INNER * ILP * 3.0;        // DADD (1) + DFMA (2)
         return (threads / 32.0) * iters * (double)(INNER / 4) * ILP * (8 * 8 * 4 * 2.0);

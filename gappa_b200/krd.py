@@ -78,11 +78,12 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("KRD_B200_LIB", LIB_PATH)   # tuning variants built with `make EXTRA=... LIB=...` (csrc/Makefile)
+    if not os.path.exists(path):
         raise ImportError(
-            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(nvcc, sm_100a). gappa_b200 has no CPU fallback.")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
     L.krd_create.restype = C.c_int
     L.krd_create.argtypes = [C.POINTER(KrdConfig), C.POINTER(vp)]

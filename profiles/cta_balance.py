@@ -25,3 +25,5 @@ print("fastest 8 CTAs (cta, dur, items):", [(int(c), round(float(dur[c])), int(n
 print("slowest 8 CTAs (cta, dur, items):", [(int(c), round(float(dur[c])), int(nitems[c])) for c in order[-8:]])
 for k in sorted(set(nitems.tolist())):
     print("items=%d: n=%d mean dur %.0f" % (k, (nitems == k).sum(), dur[nitems == k].mean()))
+if len(sys.argv) > 2:   # full per-CTA dump (duration in us by CTA index = position along the tile list)
+    print("dur by cta:", " ".join(str(int(round(x))) for x in dur))

@@ -104,6 +104,34 @@ __device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uni
     return r;
 }
 
+// One row of the register tile for integer p (square-and-multiply), stage by stage over the NC columns; the bit loop is
+// warp-uniform and its body is NC (or 2 NC) independent DMULs.
+template <int NC>
+__device__ __forceinline__ void kr_row_powi(double a, const double* __restrict__ b, double l, int n, double* __restrict__ acc)
+{
+    double base[NC], res[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) base[c] = fabs(a - b[c]);
+    if (n & 1) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) res[c] = base[c];
+    } else {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) res[c] = 1.0;
+    }
+#pragma unroll 1
+    for (int e = n >> 1; e; e >>= 1) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) base[c] *= base[c];
+        if (e & 1) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) res[c] *= base[c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) acc[c] = fma(l, res[c], acc[c]);
+}
+
 template <int MODE>
 __device__ __forceinline__ double pair_op(double a, double b, double l, double p, const double* __restrict__ tab, double acc)
 {

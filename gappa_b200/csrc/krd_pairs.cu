@@ -128,6 +128,10 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
         if (MODE == MODE_PHALF) {
 #pragma unroll
             for (int r = 0; r < 8; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+        } else if (MODE == MODE_INT) {
+            const int n = (int)p;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) kr_row_powi<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, n, &acc[r][2 * QMIN]);
         } else {
 #pragma unroll
             for (int r = 0; r < 8; ++r)
@@ -182,7 +186,7 @@ __device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa,
 #ifndef KRD_ROTATING_BODY
 #define KRD_ROTATING_BODY 0     // 1: the two-row rotating body also for p = 1/2 (A/B measurements)
 #endif
-constexpr bool mode_is_rolled(int mode) { return (KRD_ROTATING_BODY && mode == MODE_PHALF) || mode == MODE_INT || mode == MODE_GENERIC; }
+constexpr bool mode_is_rolled(int mode) { return (KRD_ROTATING_BODY && (mode == MODE_PHALF || mode == MODE_INT)) || mode == MODE_GENERIC; }
 
 // ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
 // Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
@@ -581,7 +585,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     // as long as a full one (measured: p = 1/2 0.925, p = 3, 4 0.8; profiles/cta_balance.py).  Diagonal tiles also run FOUR
     // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
     // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
-    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.925 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF || mode == MODE_INT) ? 0.925 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
     if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 

@@ -351,7 +351,6 @@ krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const in
 {
     krd_status st = check_compute(h, 1.0, 1.0);
     if (st != KRD_OK) return st;
-    if (h->cfg.bins < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means needs binned masses (krd_config.bins >= 1): without bins the reference centres the centroid masses on the branches (kmeans.cpp:75-78), which the dense layout does not represent");
     if (k > h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "Cannot run Kmeans with more clusters (k) than data points.");   // kmeans.hpp:538-544
     if (k < 1 || k > 32) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: k must be in 1..32");
     if (max_iterations < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: max_iterations must be >= 1");

@@ -123,6 +123,119 @@ k_km_update(double* __restrict__ F, int64_t ld, int64_t S_pad, int N, int k, con
     }
 }
 
+// ---- exact mode (bins = 0): branch-centred centroids -------------------------------------------------------------
+// gappa leaves MassTreeKmeans::accumulate_centroid_masses at 1 when --bins is 0 (kmeans_phylogenetic.cpp:160-167), so a
+// centroid carries ONE mass per branch, at the mass centre of everything its members have there
+// (mass_tree_center_masses_on_branches_averaged, functions.cpp:181-220; the initial centroids too: pre_loop_hook,
+// kmeans.cpp:67-84).  Its cumulative function on edge e is D (mass strictly below e) plus m_e for x < c_e: a centroid is
+// three numbers per edge (D, m_e, c_e), and a segment [lo, hi] of e contributes
+//   (clamp(c_e) - lo) |x - (D + m_e)| + (hi - clamp(c_e)) |x - D|.
+// D comes from the members' F at the edge's last (distal) segment, m_e and c_e from per-sample per-edge sums of mass and
+// position x mass taken once from the mass entries.
+__global__ void k_km_seg_geom(const int32_t* __restrict__ seg_off, const double* __restrict__ len, int E, double* __restrict__ seg_lo,
+                              int32_t* __restrict__ seg_edge)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    double lo = 0.0;
+    for (int s = seg_off[e]; s < seg_off[e + 1]; ++s) { seg_lo[s] = lo; seg_edge[s] = e; lo += len[s]; }
+}
+
+// Q[e][i] = sum of sample i's masses on edge e, P[e][i] = sum of position * mass (entries are in (sample, edge, pos) order:
+// the first entry of every run adds its run up sequentially)
+__global__ void k_km_moments(const uint32_t* __restrict__ sid, const int32_t* __restrict__ edge, const double* __restrict__ pos,
+                             const double* __restrict__ mass, int64_t M, int64_t ld, double* __restrict__ Q, double* __restrict__ P)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= M) return;
+    const uint32_t s = sid[g]; const int32_t e = edge[g];
+    if (g > 0 && sid[g - 1] == s && edge[g - 1] == e) return;
+    double q = 0.0, p = 0.0;
+    for (int64_t j = g; j < M && sid[j] == s && edge[j] == e; ++j) { q += mass[j]; p += pos[j] * mass[j]; }
+    Q[(int64_t)e * ld + s] = q; P[(int64_t)e * ld + s] = p;
+}
+
+// cent[e][c] = (D, m, centre) of centroid c on edge e from its members (fixed order: lane-strided partial sums + shuffle tree)
+__global__ void __launch_bounds__(128)
+k_km_update_exact(const double* __restrict__ F, const double* __restrict__ Q, const double* __restrict__ P, const int32_t* __restrict__ seg_off,
+                  int64_t ld, int E, int k, const int32_t* __restrict__ mem_off, const int32_t* __restrict__ mem, const double* __restrict__ ctot,
+                  double* __restrict__ cent)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int e = blockIdx.x; e < E; e += gridDim.x) {
+        const int64_t last = (int64_t)(seg_off[e + 1] - 1) * ld, row = (int64_t)e * ld;
+        for (int c = warp; c < k; c += 4) {
+            double sD = 0.0, sQ = 0.0, sP = 0.0;
+            for (int q = mem_off[c] + lane; q < mem_off[c + 1]; q += 32) { const int m = mem[q]; sD += F[last + m]; sQ += Q[row + m]; sP += P[row + m]; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                sD += __shfl_down_sync(0xffffffffu, sD, o); sQ += __shfl_down_sync(0xffffffffu, sQ, o); sP += __shfl_down_sync(0xffffffffu, sP, o);
+            }
+            if (lane == 0) {
+                const double t = ctot[c] == 0.0 ? 1.0 : ctot[c];
+                double* o3 = cent + ((int64_t)e * k + c) * 3;
+                o3[0] = sD / t; o3[1] = sQ / t; o3[2] = sQ > 0.0 ? sP / sQ : 0.0;
+            }
+        }
+    }
+}
+
+constexpr int KME_ROWS = 16;
+template <int KMAX>
+__global__ void __launch_bounds__(128)
+k_km_assign_part_exact(const double* __restrict__ F, const double* __restrict__ len, const double* __restrict__ seg_lo,
+                       const int32_t* __restrict__ seg_edge, const double* __restrict__ cent, int64_t ld, int64_t S, int64_t rows_per_chunk,
+                       int N, int k, double* __restrict__ part)
+{
+    __shared__ double sv1[KME_ROWS][KMAX], sv2[KME_ROWS][KMAX], sw1[KME_ROWS][KMAX], sw2[KME_ROWS][KMAX];
+    const int64_t d = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S, s0 + rows_per_chunk);
+    double acc[KMAX];
+#pragma unroll
+    for (int c = 0; c < KMAX; ++c) acc[c] = 0.0;
+    for (int64_t r0 = s0; r0 < s1; r0 += KME_ROWS) {
+        const int nr = (int)min((int64_t)KME_ROWS, s1 - r0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < KME_ROWS * KMAX; i += 128) {
+            const int r = i / KMAX, c = i % KMAX;
+            double v1 = 0.0, v2 = 0.0, w1 = 0.0, w2 = 0.0;
+            if (r < nr && c < k) {
+                const int64_t s = r0 + r;
+                const double* c3 = cent + ((int64_t)seg_edge[s] * k + c) * 3;
+                const double lo = seg_lo[s], l = len[s];
+                const double cc = fmin(fmax(c3[2], lo), lo + l);
+                w1 = fmin(cc - lo, l); w2 = l - w1;
+                v2 = c3[0]; v1 = v2 + c3[1];
+            }
+            sv1[r][c] = v1; sv2[r][c] = v2; sw1[r][c] = w1; sw2[r][c] = w2;
+        }
+        __syncthreads();
+        for (int r = 0; r < nr; r += 4) {
+            double x[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) x[u] = F[(r0 + min(r + u, nr - 1)) * ld + d];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r + u < nr) {
+#pragma unroll
+                    for (int c = 0; c < KMAX; ++c)
+                        if (c < k) acc[c] = fma(sw1[r + u][c], fabs(x[u] - sv1[r + u][c]), fma(sw2[r + u][c], fabs(x[u] - sv2[r + u][c]), acc[c]));
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < KMAX; ++c)
+        if (c < k) part[((int64_t)blockIdx.y * k + c) * ld + d] = acc[c];
+}
+
+template <int KMAX>
+static void launch_assign_exact(krd_handle* h, int k, int64_t rpc, const double* seg_lo, const int32_t* seg_edge, const double* cent, double* part)
+{
+    k_km_assign_part_exact<KMAX><<<dim3((unsigned)((h->N + 127) / 128), KM_CHUNKS), 128, 0, h->stream>>>(
+        h->d_F, h->d_len, seg_lo, seg_edge, cent, h->ld, h->S, rpc, h->N, k, part);
+}
+
 template <int KMAX>
 static void launch_assign(krd_handle* h, int k, int64_t rpc, double* part)
 {
@@ -133,7 +246,8 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
                       double* distances, int32_t* iterations_out)
 {
     const int N = h->N;
-    if (h->ld < N + k) {     // room for the centroid columns
+    const bool exact = h->cfg.bins == 0;   // branch-centred centroids (three numbers per edge) instead of centroid columns
+    if (!exact && h->ld < N + k) {     // room for the centroid columns
         h->extra_cols = std::max(h->extra_cols, k);
         krd_status st = prepare_masses(h);
         if (st != KRD_OK) return st;
@@ -149,7 +263,10 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
     auto al = [](size_t x) { return (x + 255) / 256 * 256; };
     const size_t b_part = (size_t)KM_CHUNKS * k * h->ld * 8, b_n8 = (size_t)N * 8, b_n4 = (size_t)N * 4, b_k = (size_t)(k + 1) * 8;
     const size_t b_root = std::max<size_t>(root_seg.size(), 1) * 4;
-    if ((st = reserve(h, &h->d_kmeans, al(b_part) + 2 * al(b_n8) + 2 * al(b_n4) + 3 * al(b_k) + al(b_root) + 256)) != KRD_OK) return st;
+    const size_t b_seg8 = exact ? (size_t)h->S_pad * 8 : 0, b_seg4 = exact ? (size_t)h->S_pad * 4 : 0;
+    const size_t b_mom = exact ? (size_t)std::max(h->E, 1) * h->ld * 8 : 0, b_cent = exact ? (size_t)std::max(h->E, 1) * k * 3 * 8 : 0;
+    if ((st = reserve(h, &h->d_kmeans, al(b_part) + 2 * al(b_n8) + 2 * al(b_n4) + 3 * al(b_k) + al(b_root) + 256 +
+                                       al(b_seg8) + al(b_seg4) + 2 * al(b_mom) + al(b_cent))) != KRD_OK) return st;
     char* q = static_cast<char*>(h->d_kmeans);
     double* part = (double*)q; q += al(b_part);
     double* d_dist = (double*)q; q += al(b_n8);
@@ -160,21 +277,38 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
     double* d_ctot = (double*)q; q += al(b_k);
     int32_t* d_init = (int32_t*)q; q += al(b_k);
     int32_t* d_root = (int32_t*)q; q += al(b_root);
-    int* d_changed = (int*)q;
+    int* d_changed = (int*)q; q += 256;
+    double* seg_lo = (double*)q; q += al(b_seg8);
+    int32_t* seg_edge = (int32_t*)q; q += al(b_seg4);
+    double* d_Q = (double*)q; q += al(b_mom);
+    double* d_P = (double*)q; q += al(b_mom);
+    double* d_cent = (double*)q;
 
     KRD_CUDA(h, cudaMemcpyAsync(d_root, root_seg.data(), root_seg.size() * 4, cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaMemcpyAsync(d_init, init_centroids, (size_t)k * 4, cudaMemcpyHostToDevice, h->stream));
     std::vector<int32_t> a((size_t)N, 0);   // kmeans.hpp:303-305: assignments start at 0 when only centroids are given
     KRD_CUDA(h, cudaMemcpyAsync(d_assign, a.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
     k_km_totals<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, d_root, (int)root_seg.size(), N, d_total);
-    k_km_copy_cols<<<(unsigned)((h->S_pad * k + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, d_init, N, k);
+    if (exact) {
+        KRD_CUDA(h, cudaMemsetAsync(d_Q, 0, 2 * al(b_mom), h->stream));   // Q and P are adjacent
+        k_km_seg_geom<<<(unsigned)((h->E + 127) / 128), 128, 0, h->stream>>>(h->d_seg_off, h->d_len, h->E, seg_lo, seg_edge);
+        if (h->M > 0) k_km_moments<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, h->d_mass, h->M, h->ld, d_Q, d_P);
+    } else {
+        k_km_copy_cols<<<(unsigned)((h->S_pad * k + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, d_init, N, k);
+    }
     std::vector<double> total((size_t)N);
     KRD_CUDA(h, cudaMemcpyAsync(total.data(), d_total, b_n8, cudaMemcpyDeviceToHost, h->stream));
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
 
     const int64_t rpc = (h->S_pad + KM_CHUNKS - 1) / KM_CHUNKS;
     auto assign_pass = [&](int reassign) {
-        if (k <= 4) launch_assign<4>(h, k, rpc, part);
+        if (exact) {
+            if (k <= 4) launch_assign_exact<4>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
+            else if (k <= 8) launch_assign_exact<8>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
+            else if (k <= 16) launch_assign_exact<16>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
+            else launch_assign_exact<32>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
+        }
+        else if (k <= 4) launch_assign<4>(h, k, rpc, part);
         else if (k <= 8) launch_assign<8>(h, k, rpc, part);
         else if (k <= 16) launch_assign<16>(h, k, rpc, part);
         else launch_assign<32>(h, k, rpc, part);
@@ -182,8 +316,10 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
     };
     static std::atomic<unsigned long long> configured{0};
     const size_t smem_row = (size_t)N * 8;
-    if (smem_row > 200 * 1024) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: more than 25,600 samples are not supported");
-    KRD_CUDA(h, allow_dynamic_smem(k_km_update, 200 * 1024, configured));
+    if (!exact) {
+        if (smem_row > 200 * 1024) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means on binned masses: more than 25,600 samples are not supported");
+        KRD_CUDA(h, allow_dynamic_smem(k_km_update, 200 * 1024, configured));
+    }
 
     int iteration = 0, changed = 0, launches = 2;
     std::vector<int32_t> mem((size_t)N), mem_off((size_t)k + 1);
@@ -191,6 +327,24 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
     // update_centroids from the host copy of the assignments: member lists in sample order + the members'
     // total mass per centroid (host: N integers), then one pass over F.  A centroid without members becomes
     // all-zero (mass_tree_normalize_masses returns early on an empty tree, functions.cpp:126-132).
+    auto push_members = [&]() -> krd_status {
+        KRD_CUDA(h, cudaMemcpyAsync(d_mem, mem.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(d_mem_off, mem_off.data(), (size_t)(k + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(d_ctot, ctot.data(), (size_t)k * 8, cudaMemcpyHostToDevice, h->stream));
+        if (exact)
+            k_km_update_exact<<<(unsigned)std::min(std::max(h->E, 1), 16 * h->num_sms), 128, 0, h->stream>>>(h->d_F, d_Q, d_P, h->d_seg_off, h->ld, h->E, k,
+                                                                                                           d_mem_off, d_mem, d_ctot, d_cent);
+        else
+            k_km_update<<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, smem_row, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
+        KRD_CUDA(h, cudaGetLastError());
+        return KRD_OK;
+    };
+    if (exact) {   // pre_loop_hook: the initial centroids are the start samples with their masses centred on the branches
+        for (int c = 0; c < k; ++c) { mem[(size_t)c] = init_centroids[c]; mem_off[(size_t)c] = c; ctot[(size_t)c] = total[(size_t)init_centroids[c]]; }
+        mem_off[(size_t)k] = k;
+        if ((st = push_members()) != KRD_OK) return st;
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
     auto update = [&]() -> krd_status {
         std::fill(mem_off.begin(), mem_off.end(), 0);
         for (int d = 0; d < N; ++d) mem_off[(size_t)a[(size_t)d] + 1]++;
@@ -198,10 +352,7 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
         std::vector<int32_t> fill(mem_off.begin(), mem_off.end() - 1);
         std::fill(ctot.begin(), ctot.end(), 0.0);
         for (int d = 0; d < N; ++d) { mem[(size_t)fill[(size_t)a[(size_t)d]]++] = d; ctot[(size_t)a[(size_t)d]] += total[(size_t)d]; }
-        KRD_CUDA(h, cudaMemcpyAsync(d_mem, mem.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
-        KRD_CUDA(h, cudaMemcpyAsync(d_mem_off, mem_off.data(), (size_t)(k + 1) * 4, cudaMemcpyHostToDevice, h->stream));
-        KRD_CUDA(h, cudaMemcpyAsync(d_ctot, ctot.data(), (size_t)k * 8, cudaMemcpyHostToDevice, h->stream));
-        k_km_update<<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, smem_row, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
+        { krd_status ps = push_members(); if (ps != KRD_OK) return ps; }
         KRD_CUDA(h, cudaStreamSynchronize(h->stream));   // the host vectors are reused
         launches += 1;
         return KRD_OK;

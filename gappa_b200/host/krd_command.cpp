@@ -60,7 +60,7 @@ const char* kUsage =
     "  --point-mass                      Treat every pquery as a point mass on its highest-weight placement.\n"
     "  --ignore-multiplicities           Set the multiplicity of each pquery to 1.0.\n"
     "  --bins INT=0                      (additive) binify masses into this many bins per edge first.\n"
-    "  --k TEXT  --write-overview-file   (phylogenetic-kmeans) values of k, e.g. 1-5,8; needs --bins >= 1.\n"
+    "  --k TEXT  --write-overview-file   (phylogenetic-kmeans) values of k, e.g. 1-5,8.\n"
     "  --seed INT  --init-centroids LIST (phylogenetic-kmeans, additive) k-means++ seed / explicit start samples.\n"
     "Matrix Output:\n  --out-dir TEXT=.  --file-prefix TEXT  --file-suffix TEXT  --compress\n"
     "  --matrix-format TEXT=matrix       matrix | list | triangular\n  --omit-matrix-labels\n"
@@ -379,8 +379,6 @@ std::string fmt_g(double v) { char b[64]; std::snprintf(b, sizeof b, "%g", v); r
 int run_kmeans(const KrdOptions& o, Log& log)
 {
     const std::vector<int> ks = parse_k_values(o.ks);
-    if (o.bins < 1)
-        throw std::runtime_error("--bins: gappa-b200 runs phylogenetic k-means on binned masses only; give --bins B with B >= 1 (gappa recommends 50 or more).");
     std::string dir = o.out_dir;
     while (dir.size() > 1 && dir.back() == '/') dir.pop_back();
     auto out_path = [&](const std::string& infix) { return dir + "/" + o.prefix + infix + o.suffix + ".csv"; };

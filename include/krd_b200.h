@@ -153,9 +153,12 @@ krd_status krd_squash(krd_handle* h, double p, krd_merger* out);
 
 /* Phylogenetic k-means (`gappa analyze phylogenetic-kmeans`, src/commands/analyze/kmeans_phylogenetic.cpp:134-175)
  * = genesis::tree::MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) on the Lloyd loop of
- * utils/math/kmeans.hpp:118-168, run on the resident dense matrix: centroids are extra columns of F (the
- * re-normalised sum of their members' columns), the assignment step is the p = 1 KR reduction of every
- * sample against the k centroids, first minimum wins.  Empty centroids are treated as in kmeans.hpp:426-500.
+ * utils/math/kmeans.hpp:118-168, run on the resident dense matrix.  The assignment step is the p = 1 KR reduction of
+ * every sample against the k centroids, first minimum wins; empty centroids are treated as in kmeans.hpp:426-500.
+ * krd_config.bins >= 1 (gappa --bins B: accumulate_centroid_masses = B): centroids are extra columns of F, the
+ * re-normalised sum of their members' columns.  bins == 0 (gappa's default: accumulate_centroid_masses stays 1):
+ * centroids carry one mass per branch at the members' mass centre (functions.cpp:181-220), kept as (mass below, mass,
+ * centre) per edge.
  * `init_centroids` (HOST, k sample indices) are the initial centroids, i.e. the state after the reference's
  * initialisation (kmeans.hpp:254-306: random samples or k-means++, both pick data points); all assignments
  * start at 0.  Outputs (HOST): assignments[n], distances[n] = KR distance of every sample to its centroid

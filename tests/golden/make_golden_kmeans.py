@@ -2,9 +2,9 @@
 Run in the build container only:   python tests/golden/make_golden_kmeans.py
 Writes kmeans.npz: synthetic 60 samples x 99 edges x 120 placements; reference assignments / distances /
 variances / iteration counts for several (bins, k, initial centroids, max_iterations), among them a start with
-duplicate centroids (forces the empty-centroid treatment, utils/math/kmeans.hpp:426-500).  bins >= 1 only: with
---bins 0 gappa leaves accumulate_centroid_masses at 1 and the centroids get ONE mass per branch at the mass centre
-(kmeans.cpp:75-78, functions.cpp:181-220), which is outside the dense layout."""
+duplicate centroids (forces the empty-centroid treatment, utils/math/kmeans.hpp:426-500), and bins = 0 cases: there
+gappa leaves accumulate_centroid_masses at 1 and the centroids get ONE mass per branch at the mass centre
+(kmeans.cpp:75-78, functions.cpp:181-220)."""
 import os
 import sys
 
@@ -26,6 +26,10 @@ for bins, k, max_it in ((5, 3, 100), (5, 7, 100), (1, 4, 100), (20, 10, 100), (5
     cases.append((bins, k, max_it, init))
 cases.append((5, 4, 100, np.array([7, 7, 30, 7], np.int32)))      # duplicates: centroids 1 and 3 start empty
 cases.append((12, 3, 100, np.array([11, 11, 11], np.int32)))
+# bins = 0 (gappa's default): accumulate_centroid_masses stays 1 -> centroids with one mass per branch at the mass centre
+cases.append((0, 3, 100, rng.choice(60, 3, replace=False).astype(np.int32)))
+cases.append((0, 6, 100, rng.choice(60, 6, replace=False).astype(np.int32)))
+cases.append((0, 4, 100, np.array([20, 20, 5, 20], np.int32)))
 names = []
 for i, (bins, k, max_it, init) in enumerate(cases):
     a, d, v, it, sec = oracle.ref_kmeans(tree, mass, k, init, bins=bins, max_iterations=max_it)

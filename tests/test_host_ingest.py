@@ -286,8 +286,10 @@ def test_cli_phylogenetic_kmeans_end_to_end(tmp_path):
         assert sorted({int(x.split("\t")[1]) for x in rows[1:]}) == list(range(k))
     r = subprocess.run(base + ["--k", "2,x"], capture_output=True, text=True)
     assert r.returncode != 0 and "Invalid list of values for k" in r.stderr
-    r = subprocess.run(base[:-2] + ["--k", "2"], capture_output=True, text=True)
-    assert r.returncode != 0 and "--bins" in r.stderr
+    # gappa's default --bins 0 (branch-centred centroids): runs, every sample gets a cluster
+    r = subprocess.run(base[:-2] + ["--k", "2", "--seed", "3", "--file-prefix", "b0_"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert len((tmp_path / "o" / "b0_k_2_assignments.csv").read_text().splitlines()) == 6
 
 
 @pytest.mark.gpu

@@ -32,7 +32,7 @@ def test_fixture_is_consistent():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", [f"c{i}" for i in range(8)])
+@pytest.mark.parametrize("case", [f"c{i}" for i in range(11)])
 def test_kmeans_matches_reference(case):
     z = np.load(GOLD)
     bins, k, max_it = (int(x) for x in z[f"{case}_cfg"])
@@ -54,7 +54,7 @@ def test_kmeans_matches_reference(case):
     # largest within-cluster distance)
     for q in range(k):
         idx = np.flatnonzero(a == q)
-        if len(idx) > 1:
+        if len(idx) > 1 and bins > 0:     # bins = 0: the centroid is not a mean of its members (branch-centred masses)
             assert d[idx].max() <= m[np.ix_(idx, idx)].max() * (1 + 1e-12)
     plan.close()
 
@@ -70,8 +70,4 @@ def test_kmeans_argument_errors():
         plan.kmeans(33, np.arange(33))
     with pytest.raises(krd.KrdError, match="not a sample index"):
         plan.kmeans(2, [0, n])
-    plan.close()
-    plan = _plan(z, 0)
-    with pytest.raises(krd.KrdError, match="needs binned masses"):
-        plan.kmeans(2, [0, 1])
     plan.close()

@@ -127,7 +127,11 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
         }
         if (MODE == MODE_PHALF) {
 #pragma unroll
+#ifdef KRD_EXPERIMENT_HALFROWS   // register-pressure experiment only (computes half the rows: results are wrong)
+            for (int r = 0; r < 4; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+#else
             for (int r = 0; r < 8; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+#endif
         } else if (MODE == MODE_INT) {
             const int n = (int)p;
 #pragma unroll
@@ -370,12 +374,15 @@ struct EpiParams {
 // ratio are recomputed directly by k_gram_fixup, which keeps the Gram path inside the 1e-10 bar.
 constexpr double GRAM_CANCEL_RATIO = 1e-3;
 
+constexpr int EPI_SPLIT = 8;   // CTAs per tile (row bands of 16): a small matrix has few tiles (36 at cfg2), one CTA per tile leaves SMs idle
 __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
 {
-    const Tile tile = P.tiles[blockIdx.x];
-    const int i0 = P.tile_item_off[blockIdx.x], i1 = P.tile_item_off[blockIdx.x + 1];
+    const int t = blockIdx.x / EPI_SPLIT, band = blockIdx.x % EPI_SPLIT;
+    const Tile tile = P.tiles[t];
+    const int i0 = P.tile_item_off[t], i1 = P.tile_item_off[t + 1];
     const double inv_p = 1.0 / P.p;
-    for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
+    constexpr int BAND = TILE * TILE / EPI_SPLIT;
+    for (int idx = band * BAND + threadIdx.x; idx < (band + 1) * BAND; idx += blockDim.x) {
         double v = 0.0;
         for (int s = i0; s < i1; ++s) v += P.ws[(size_t)s * (size_t)(TILE * TILE) + idx];
         const int r = idx / TILE, c = idx % TILE;
@@ -385,12 +392,12 @@ __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
             v = fmax(nn - 2.0 * v, 0.0);
             if (i < j && j < P.N && v < GRAM_CANCEL_RATIO * nn) {
                 const int pos = atomicAdd(&P.fix[0].x, 1);
-                if (pos < P.fix_cap) P.fix[1 + pos] = make_int4((int)i, (int)j, (int)blockIdx.x, idx);
+                if (pos < P.fix_cap) P.fix[1 + pos] = make_int4((int)i, (int)j, t, idx);
             }
         }
         if (P.p > 1.0) v = (P.p == 2.0) ? sqrt(v) : pow(v, inv_p);
         v = v / P.divisor;
-        if (P.packed) P.packed[(size_t)blockIdx.x * (TILE * TILE) + idx] = (i < j) ? v : 0.0;
+        if (P.packed) P.packed[(size_t)t * (TILE * TILE) + idx] = (i < j) ? v : 0.0;
         if (P.out && i < P.N && j < P.N) {
             if (i < j) { P.out[i * P.N + j] = v; P.out[j * P.N + i] = v; }
             else if (i == j) P.out[i * P.N + i] = 0.0;
@@ -648,7 +655,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         KRD_CUDA(h, cudaMemsetAsync(h->d_fix, 0, sizeof(int4), h->stream));
         Q.norm = h->d_norm; Q.fix = static_cast<int4*>(h->d_fix); Q.fix_cap = FIX_CAP;
     }
-    k_epilogue<<<(unsigned)n_tiles, 256, 0, h->stream>>>(Q);
+    k_epilogue<<<(unsigned)n_tiles * EPI_SPLIT, 256, 0, h->stream>>>(Q);
     if (mode == MODE_P2G) {
         k_gram_fixup<<<2 * h->num_sms, 256, 0, h->stream>>>(static_cast<const int4*>(h->d_fix), FIX_CAP, h->d_F, h->d_len, h->ld, h->S_pad,
                                                             h->N, divisor, d_out_matrix, d_out_packed);

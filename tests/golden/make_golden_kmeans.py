@@ -30,6 +30,7 @@ cases.append((12, 3, 100, np.array([11, 11, 11], np.int32)))
 cases.append((0, 3, 100, rng.choice(60, 3, replace=False).astype(np.int32)))
 cases.append((0, 6, 100, rng.choice(60, 6, replace=False).astype(np.int32)))
 cases.append((0, 4, 100, np.array([20, 20, 5, 20], np.int32)))
+cases.append((50, 4, 100, rng.choice(60, 4, replace=False).astype(np.int32)))   # gappa's recommended bin count (general F builder)
 names = []
 for i, (bins, k, max_it, init) in enumerate(cases):
     a, d, v, it, sec = oracle.ref_kmeans(tree, mass, k, init, bins=bins, max_iterations=max_it)

@@ -32,7 +32,7 @@ def test_fixture_is_consistent():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", [f"c{i}" for i in range(11)])
+@pytest.mark.parametrize("case", [f"c{i}" for i in range(12)])
 def test_kmeans_matches_reference(case):
     z = np.load(GOLD)
     bins, k, max_it = (int(x) for x in z[f"{case}_cfg"])

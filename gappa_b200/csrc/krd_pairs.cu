@@ -30,6 +30,21 @@ constexpr int LAG = 2;         // a stage is refilled LAG chunks after it was co
 constexpr int NT = 256;        // threads per CTA (8 warps; all compute, the TMA-issue role rotates)
 constexpr int STAGE_DOUBLES = 2 * KC * TILE + 2 * KC;  // A rows, B rows, len, centre (Gram mode)
 constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * ST * sizeof(uint64_t);
+// Long inner operators (p = 1/2, integer p >= 5, general p) keep only HALF of the thread's 8 x 8 accumulators in
+// registers: every chunk is walked twice (rows 0-3, rows 4-7) and the idle half waits in shared memory.  With all 64
+// accumulators resident the compiler has ~45 doubles left for the operators' temporaries, interleaves 4-5 dependency
+// chains and the FP64 latency shows (computing only four rows ran 1.41x faster per operator, profiles/r1o_long_ops.txt).
+// These modes need a fraction of the operand bandwidth, so the ring shrinks to 4 stages and leaves room for the spill.
+#ifndef KRD_HALVED
+#define KRD_HALVED 1
+#endif
+constexpr bool mode_is_halved(int mode) { return KRD_HALVED && (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC); }
+constexpr int stages_for(int mode) { return mode_is_halved(mode) ? 4 : ST; }
+constexpr size_t SPILL_BYTES = (size_t)32 * NT * sizeof(double);
+constexpr size_t smem_bytes_for(int mode)
+{
+    return (size_t)stages_for(mode) * STAGE_DOUBLES * sizeof(double) + 2 * stages_for(mode) * sizeof(uint64_t) + (mode_is_halved(mode) ? SPILL_BYTES : 0);
+}
 constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
 constexpr double DIAG_COST_SKIP = 0.705;  // measured (profiles/cta_balance.py) cost of a diagonal-tile chunk relative to a full one (5/8 of the math, same pipeline overheads)
 
@@ -145,6 +160,43 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
     }
 }
 
+// Four rows (4 * half .. 4 * half + 3 of the thread's eight) of one chunk, for the halved modes.
+template <int MODE, int QMIN>
+__device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, const double* __restrict__ pb,
+                                                 const double* __restrict__ sL, double p, const double* __restrict__ tab,
+                                                 int half, double (&acc)[4][8])
+{
+    constexpr int NC = 8 - 2 * QMIN;
+#pragma unroll 1
+    for (int kk = 0; kk < KC; ++kk) {
+        double a[4], b[8];
+        const double l = sL[kk];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 4 * half + 2 * q);
+            a[2 * q] = va.x; a[2 * q + 1] = va.y;
+        }
+#pragma unroll
+        for (int q = QMIN; q < 4; ++q) {
+            const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
+            b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
+        }
+        if (MODE == MODE_PHALF) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) kr_row_sqrt<NC>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+        } else if (MODE == MODE_INT) {
+            const int n = (int)p;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) kr_row_powi<NC>(a[r], b + 2 * QMIN, l, n, &acc[r][2 * QMIN]);
+        } else {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
+        }
+    }
+}
+
 // Exponents whose inner operator is long (sqrt: ~12, pow: ~40 instructions per pair and segment): a fully
 // unrolled 8x8 body would be tens of thousands of instructions and thrash the instruction cache.  The
 // body is therefore two rows (16 independent operators = enough ILP for the FP64 pipe) in a rolled loop,
@@ -190,7 +242,7 @@ __device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa,
 #ifndef KRD_ROTATING_BODY
 #define KRD_ROTATING_BODY 0     // 1: the two-row rotating body also for p = 1/2 (A/B measurements)
 #endif
-constexpr bool mode_is_rolled(int mode) { return (KRD_ROTATING_BODY && (mode == MODE_PHALF || mode == MODE_INT)) || mode == MODE_GENERIC; }
+constexpr bool mode_is_rolled(int mode) { return !mode_is_halved(mode) && ((KRD_ROTATING_BODY && (mode == MODE_PHALF || mode == MODE_INT)) || mode == MODE_GENERIC); }
 
 // ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
 // Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
@@ -230,9 +282,12 @@ template <int MODE>
 __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int STM = stages_for(MODE);   // ring depth of this mode
     double* stage_base = reinterpret_cast<double*>(smem_raw);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)ST * STAGE_DOUBLES * sizeof(double));
-    uint64_t* empty = full + ST;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STM * STAGE_DOUBLES * sizeof(double));
+    uint64_t* empty = full + STM;
+    // halved modes: the thread's idle half of the accumulators, [32][NT] (conflict-free: consecutive threads, consecutive words)
+    double* spill = reinterpret_cast<double*>(smem_raw + (size_t)STM * STAGE_DOUBLES * sizeof(double) + 2 * STM * sizeof(uint64_t)) + threadIdx.x;
 
     __shared__ double s_tab[MODE == MODE_GENERIC ? POW_TAB : 1];
     if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB; k += NT) s_tab[k] = g_pow_tab[k];   // visible after the barrier below
@@ -252,7 +307,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     }
 
     if (tid == 0) {
-        for (int s = 0; s < ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NT / 32); }
+        for (int s = 0; s < STM; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NT / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -267,8 +322,8 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     auto produce_one = [&]() {   // advance the flattened sequence by one chunk; issue it if it is ours
         if (p_item >= it1) return;
         if ((p_flat & 7) == warp) {
-            const int s = p_flat % ST;
-            if (p_flat >= ST) mbar_wait(&empty[s], (uint32_t)(((p_flat / ST) - 1) & 1));
+            const int s = p_flat % STM;
+            if (p_flat >= STM) mbar_wait(&empty[s], (uint32_t)(((p_flat / STM) - 1) & 1));
             const Tile t = P.tiles[p_w.tile];
             const bool dg = (t.i == t.j);
             double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
@@ -288,31 +343,56 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             if (++p_item < it1) { p_w = P.items[p_item]; p_chunk = p_w.c0; }
         }
     };
-    for (int c = 0; c < ST - LAG; ++c) produce_one();
+    for (int c = 0; c < STM - LAG; ++c) produce_one();
 
     double acc[8][8];
+    double h4[4][8];   // halved modes: the four accumulator rows that are in registers
     int flat = 0;
     for (int item = it0; item < it1; ++item) {
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G && !mode_is_rolled(MODE)) ? (rg >> 1) : 0;
+        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && !mode_is_rolled(MODE)) ? (rg >> 1) : 0;
         if (threadIdx.x == 0 && item < 4096) { unsigned long long tt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tt)); g_item_time[2 * item] = tt; }
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
             for (int c = 0; c < 8; ++c) acc[r][c] = 0.0;
+        int act = 0;
+        if (mode_is_halved(MODE)) {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) { spill[q * NT] = 0.0; h4[q >> 3][q & 7] = 0.0; }
+        }
 
         for (int c = w.c0; c < w.c1; ++c, ++flat) {
             produce_one();   // (owner warp) refills the stage consumed LAG chunks ago
-            const int s = flat % ST;
-            mbar_wait(&full[s], (uint32_t)((flat / ST) & 1));
+            const int s = flat % STM;
+            mbar_wait(&full[s], (uint32_t)((flat / STM) & 1));
             const double* sA = stage_base + (size_t)s * STAGE_DOUBLES;
             const double* sB = diag ? sA : sA + KC * TILE;
             const double* sL = sA + 2 * KC * TILE;
             const double* pa = sA + row0;
             const double* pb = sB + 2 * tx;
-            if (MODE == MODE_P2G) {
+            if (mode_is_halved(MODE)) {
+                // rows [4 act, 4 act + 4) are in registers (acc[0..3]), the other four in `spill`; one exchange per chunk
+#pragma unroll 1
+                for (int pass = 0; pass < 2; ++pass) {
+                    if (pass == 1) {
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+#pragma unroll
+                            for (int cc = 0; cc < 8; ++cc) { const double t = spill[(r * 8 + cc) * NT]; spill[(r * 8 + cc) * NT] = h4[r][cc]; h4[r][cc] = t; }
+                        act ^= 1;
+                    }
+                    if (MODE == MODE_GENERIC) { chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); continue; }   // one code variant
+                    switch (qmin) {
+                        case 0: chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); break;
+                        case 1: chunk_math_rows4<MODE, 1>(pa, pb, sL, P.p, s_tab, act, h4); break;
+                        case 2: chunk_math_rows4<MODE, 2>(pa, pb, sL, P.p, s_tab, act, h4); break;
+                        default: chunk_math_rows4<MODE, 3>(pa, pb, sL, P.p, s_tab, act, h4); break;
+                    }
+                }
+            } else if (MODE == MODE_P2G) {
                 chunk_gram(sA, sB, sL, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
             } else if (mode_is_rolled(MODE)) {
                 chunk_math_rolled<MODE>(pa, pb, sL, P.p, s_tab, acc);
@@ -340,6 +420,17 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                 for (int ni = 0; ni < 8; ++ni)
                     *reinterpret_cast<double2*>(wout + (wr + 8 * mi + (lane >> 2)) * TILE + wc + 8 * ni + 2 * (lane & 3)) =
                         make_double2(acc[2 * mi][ni], acc[2 * mi + 1][ni]);
+            continue;
+        }
+        if (mode_is_halved(MODE)) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    *reinterpret_cast<double2*>(wout + (row0 + 4 * act + r) * TILE + 32 * q + 2 * tx) = make_double2(h4[r][2 * q], h4[r][2 * q + 1]);
+                    *reinterpret_cast<double2*>(wout + (row0 + 4 * (act ^ 1) + r) * TILE + 32 * q + 2 * tx) =
+                        make_double2(spill[(r * 8 + 2 * q) * NT], spill[(r * 8 + 2 * q + 1) * NT]);
+                }
             continue;
         }
 #pragma unroll
@@ -563,9 +654,9 @@ template <int MODE>
 static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stream)
 {
     static std::atomic<unsigned long long> configured{0};
-    cudaError_t e = allow_dynamic_smem(k_pairs<MODE>, (int)SMEM_BYTES, configured);
+    cudaError_t e = allow_dynamic_smem(k_pairs<MODE>, (int)smem_bytes_for(MODE), configured);
     if (e != cudaSuccess) return e;
-    k_pairs<MODE><<<grid, NT, SMEM_BYTES, stream>>>(P);
+    k_pairs<MODE><<<grid, NT, smem_bytes_for(MODE), stream>>>(P);
     return cudaGetLastError();
 }
 
@@ -585,14 +676,14 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
 
     const int mode = mode_for_exponent(p, h->cfg.p2_mode != 1);   // p = 2: auto = Gram on the tensor cores + direct fix-ups
-    const bool full_diag = (mode == MODE_P2G) || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
+    const bool full_diag = (mode == MODE_P2G) || mode == MODE_GENERIC || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
     // cost of a diagonal-tile chunk relative to a full one: 5/8 of the math, but the warps of a diagonal tile carry unequal
     // shares (the top row groups skip nothing).  p = 1, 2 are FP64-pipe-bound, so the lighter warps free the pipe for the
     // others (measured 0.705); the long operators are bound by each warp's own dependency chains, so the tile takes almost
-    // as long as a full one (measured: p = 1/2 0.925, p = 3, 4 0.8; profiles/cta_balance.py).  Diagonal tiles also run FOUR
+    // as long as a full one (measured: p = 3, 4 0.8; halved modes p = 1/2 0.72, integer p 0.85; profiles/cta_balance.py).  Diagonal tiles also run FOUR
     // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
     // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
-    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF || mode == MODE_INT) ? 0.925 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_INT) ? 0.85 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
     if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 

@@ -104,29 +104,37 @@ __device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uni
     return r;
 }
 
-// One row of the register tile for integer p (square-and-multiply), stage by stage over the NC columns; the bit loop is
-// warp-uniform and its body is NC (or 2 NC) independent DMULs.
+// One row of the register tile for integer p = 5 .. 16 (square-and-multiply), stage by stage over the NC columns; the
+// branches on the bits of p are warp-uniform.
 template <int NC>
 __device__ __forceinline__ void kr_row_powi(double a, const double* __restrict__ b, double l, int n, double* __restrict__ acc)
 {
-    double base[NC], res[NC];
+    // n = 5 .. 16: x^4 is always needed; result = x^4 [* x^8 or x^16 instead] * (x^2 if bit 1) * (x if bit 0)
+    double x1[NC], x2[NC], res[NC];
 #pragma unroll
-    for (int c = 0; c < NC; ++c) base[c] = fabs(a - b[c]);
+    for (int c = 0; c < NC; ++c) x1[c] = fabs(a - b[c]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) x2[c] = x1[c] * x1[c];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) res[c] = x2[c] * x2[c];                       // x^4
+    if (n >= 8) {                                                               // warp-uniform branches
+#pragma unroll
+        for (int c = 0; c < NC; ++c) res[c] *= res[c];                          // x^8
+        if (n >= 16) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) res[c] *= res[c];                      // x^16
+        } else if (n & 4) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) res[c] *= x2[c] * x2[c];               // x^12
+        }
+    }
+    if (n & 2) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) res[c] *= x2[c];
+    }
     if (n & 1) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) res[c] = base[c];
-    } else {
-#pragma unroll
-        for (int c = 0; c < NC; ++c) res[c] = 1.0;
-    }
-#pragma unroll 1
-    for (int e = n >> 1; e; e >>= 1) {
-#pragma unroll
-        for (int c = 0; c < NC; ++c) base[c] *= base[c];
-        if (e & 1) {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) res[c] *= base[c];
-        }
+        for (int c = 0; c < NC; ++c) res[c] *= x1[c];
     }
 #pragma unroll
     for (int c = 0; c < NC; ++c) acc[c] = fma(l, res[c], acc[c]);

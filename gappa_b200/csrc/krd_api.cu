@@ -87,6 +87,7 @@ void krd_destroy(krd_handle* h)
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    pipe_destroy(h);
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
@@ -94,7 +95,8 @@ void krd_destroy(krd_handle* h)
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
-    cudaFree(h->d_ws); cudaFree(h->d_sched); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
+    cudaFree(h->d_flags);
+    cudaFree(h->d_ws); for (auto& kv : h->scheds) cudaFree(kv.second.d); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     delete h;
 }
@@ -119,7 +121,7 @@ krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_no
     h->parent.assign(parent_node, parent_node + n_edges);
     h->child.assign(child_node, child_node + n_edges);
     h->bl.assign(branch_length, branch_length + n_edges);
-    h->have_tree = false; h->F_valid = false; h->have_masses = false;
+    h->have_tree = false; h->F_valid = false; h->have_masses = false; h->piped = false; ++h->tree_version;
     krd_status st = build_tree(h);
     if (st == KRD_OK) h->have_tree = true;
     return st;
@@ -135,6 +137,8 @@ krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sampl
     if (M > 0 && (!edge || !pos || !mass)) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
     KRD_CUDA(h, cudaSetDevice(h->device));
     free_masses(h);
+    if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass);
+    if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = M;
     const size_t Mx = (size_t)std::max<int64_t>(M, 1);
     if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
@@ -161,6 +165,7 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
     if (st != KRD_OK) return st;
     KRD_CUDA(h, cudaSetDevice(h->device));
     free_masses(h);
+    if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = sample_off[n_samples];
     if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
     KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
@@ -185,6 +190,10 @@ static krd_status check_compute(krd_handle* h, double p, double divisor)
 static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed)
 {
     KRD_CUDA(h, cudaSetDevice(h->device));
+    if (h->piped) {
+        if (world != 1 || d_packed) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }   // sharding works on the ordinary tile order
+        else return pipe_compute(h, p, divisor, d_out);
+    }
     h->stats.launches = 0;
     cudaEventRecord(h->ev[0], h->stream);
     if (!h->F_valid) {
@@ -343,6 +352,7 @@ krd_status krd_squash(krd_handle* h, double p, krd_merger* out)
     if (h->N < 2) return fail(h, KRD_ERR_TOO_FEW_SAMPLES, "Squash clustering needs at least 2 samples.");
     if (!out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
     KRD_CUDA(h, cudaSetDevice(h->device));
+    if ((st = pipe_flatten(h)) != KRD_OK) return st;
     return run_squash(h, p, out);
 }
 
@@ -358,6 +368,7 @@ krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const in
     for (int c = 0; c < k; ++c)
         if (init_centroids[c] < 0 || init_centroids[c] >= h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: initial centroid is not a sample index");
     KRD_CUDA(h, cudaSetDevice(h->device));
+    if ((st = pipe_flatten(h)) != KRD_OK) return st;
     return run_kmeans(h, k, max_iterations, init_centroids, assignments, distances, iterations);
 }
 
@@ -373,6 +384,7 @@ krd_status krd_debug_copy_F(krd_handle* h, double* out_F, double* out_len)
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
     KRD_CUDA(h, cudaSetDevice(h->device));
+    if (h->piped && !h->F_valid) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }
     if (!h->F_valid) { krd_status st = build_F(h); if (st != KRD_OK) return st; }
     if (out_F) KRD_CUDA(h, cudaMemcpyAsync(out_F, h->d_F, (size_t)h->S * h->ld * 8, cudaMemcpyDeviceToHost, h->stream));
     if (out_len) KRD_CUDA(h, cudaMemcpyAsync(out_len, h->d_len, (size_t)h->S * 8, cudaMemcpyDeviceToHost, h->stream));

@@ -300,6 +300,28 @@ static krd_status sort_edge_pos(krd_handle* h, uint32_t* perm /*M*/, uint32_t* s
 
 static krd_status prepare_tiled(krd_handle* h);
 
+// Segment table of binned mode without any mass data (the parent of a pipelined ingest needs len / seg_off for the pair
+// kernel while its children hold the masses): same kernels as prepare_masses.
+krd_status prepare_len_binned(krd_handle* h)
+{
+    const int E = h->E, B = h->cfg.bins;
+    if (B <= 0) return fail(h, KRD_ERR_STATE, "prepare_len_binned needs bins > 0");
+    if ((int64_t)E * (B + 1) > 0x7FFFFFF0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "too many segments");
+    h->S = (int64_t)E * (B + 1);
+    h->S_pad = ((h->S + KC - 1) / KC) * KC;
+    if (h->S_pad == 0) h->S_pad = KC;
+    krd_status rs;
+    if ((rs = reserve(h, (void**)&h->d_seg_off, (size_t)(E + 1) * 4)) != KRD_OK) return rs;
+    if ((rs = reserve(h, (void**)&h->d_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
+    if ((rs = reserve(h, (void**)&h->d_sqrt_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
+    KRD_CUDA(h, cudaMemsetAsync(h->d_len, 0, (size_t)h->S_pad * 8, h->stream));
+    k_len_binned<<<nblk((int64_t)E * (B + 1) + 1), 256, 0, h->stream>>>(h->d_bl, E, B, h->d_len, h->d_seg_off);
+    k_sqrt<<<nblk(h->S_pad), 256, 0, h->stream>>>(h->d_len, h->S_pad, h->d_sqrt_len);
+    KRD_CUDA(h, cudaGetLastError());
+    return KRD_OK;
+}
+
+
 krd_status prepare_masses(krd_handle* h)
 {
     const int64_t M = h->M;
@@ -308,16 +330,18 @@ krd_status prepare_masses(krd_handle* h)
     if (M >= (int64_t)0xFFFFFFF0u) return fail(h, KRD_ERR_INVALID_ARGUMENT, "more than 2^32 masses are not supported");
 
     // --- canonical order check (edge asc, pos asc per sample = MassTree iteration order) ---
-    DevBuf flags;
+    // (the flag word lives in the handle: a scoped cudaMalloc/cudaFree here would synchronise the whole device on every
+    //  call, including the copy stream of a pipelined ingest)
+    { krd_status rs = reserve(h, &h->d_flags, 16); if (rs != KRD_OK) return rs; }
+    int* const d_flags = static_cast<int*>(h->d_flags);
     { krd_status rs = reserve(h, (void**)&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
-    KRD_CUDA(h, flags.alloc(sizeof(int)));
-    KRD_CUDA(h, cudaMemsetAsync(flags.p, 0, sizeof(int), h->stream));
+    KRD_CUDA(h, cudaMemsetAsync(d_flags, 0, sizeof(int), h->stream));
     if (M > 0) {
         k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
-        k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, M, E, flags.as<int>());
+        k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, M, E, d_flags);
     }
     int hflags = 0;
-    KRD_CUDA(h, cudaMemcpyAsync(&hflags, flags.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaMemcpyAsync(&hflags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
     if (hflags & 2) return fail(h, KRD_ERR_INVALID_ARGUMENT, "mass entry refers to an edge outside the tree");
     if (hflags & 1) {
@@ -404,7 +428,8 @@ krd_status prepare_masses(krd_handle* h)
     KRD_CUDA(h, cudaGetLastError());
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
 
-    h->ld = ((N + h->extra_cols + TILE - 1) / TILE) * TILE;
+    if (!h->ld_fixed) { h->ld = ((N + h->extra_cols + TILE - 1) / TILE) * TILE; h->ncols = h->ld; }
+    else h->ncols = ((N + TILE - 1) / TILE) * TILE;     // child of a pipelined ingest: own columns inside the parent's F
     h->stats.n_segments = h->S;
     h->stats.ld_samples = h->ld;
     h->stats.f_bytes = (int64_t)h->S_pad * h->ld * 8;
@@ -702,9 +727,9 @@ static krd_status build_F_tiled(krd_handle* h)
     const size_t smem_fill = (size_t)h->EB * B1 * FTS * sizeof(double), smem_tot = (size_t)h->EB * FTS * sizeof(double);
     static std::atomic<unsigned long long> configured{0};
     KRD_CUDA(h, allow_dynamic_smem(k_tile<true>, FT_MAX_ROWS * FTS * 8, configured));
-    if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero
-        KRD_CUDA(h, cudaMemsetAsync(h->d_F + (size_t)h->S * h->ld, 0, (size_t)(h->S_pad - h->S) * h->ld * 8, h->stream));
-    dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ld / FT));
+    if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero (own columns only)
+        KRD_CUDA(h, cudaMemset2DAsync(h->d_F + (size_t)h->S * h->ld, (size_t)h->ld * 8, 0, (size_t)h->ncols * 8, (size_t)(h->S_pad - h->S), h->stream));
+    dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ncols / FT));
     k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
                                                       nullptr, h->d_M, nullptr);
     const int L = (int)h->lvl_off.size() - 1;
@@ -715,13 +740,13 @@ static krd_status build_F_tiled(krd_handle* h)
     int n_launch = 2;
     for (int l = 1; l < l_end; ++l, ++n_launch) {   // level 0 = leaf edges: nothing below them
         const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
-        dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ld / 128));
+        dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ncols / 128));
         k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, h->ld, h->d_M, h->d_D);
     }
     if (use_top) {
         static std::atomic<unsigned long long> top_configured{0};
         KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
-        k_subtree_top<<<(unsigned)(h->ld / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
+        k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
                                                                                  h->ld, h->d_M, h->d_D);
         ++n_launch;
     }
@@ -736,7 +761,9 @@ krd_status build_F(krd_handle* h)
 {
     h->norms_valid = false;
     const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
-    if (need > h->F_capacity) {
+    if (h->ld_fixed) {   // child of a pipelined ingest: d_F points into the parent's matrix
+        if (!h->d_F || !h->tiled) return fail(h, KRD_ERR_STATE, "pipelined child without a tiled builder");
+    } else if (need > h->F_capacity) {
         cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
         KRD_CUDA(h, cudaMalloc(&h->d_F, need));
         h->F_capacity = need;

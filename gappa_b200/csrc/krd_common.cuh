@@ -71,6 +71,8 @@ struct krd_handle {
     int64_t S = 0, S_pad = 0;
     int32_t ld = 0;              // column stride of F: N (+ extra_cols) rounded up to TILE
     int32_t extra_cols = 0;      // columns reserved after the samples (squash clustering: one per merged cluster)
+    int32_t ncols = 0;           // columns this handle's F builder writes (= ld, except for the children of a pipelined ingest)
+    bool     ld_fixed = false;   // child of a pipelined ingest: ld (the parent's), d_F (inside the parent's F) are set by the parent
     int32_t* d_seg_off = nullptr;  // E+1
     double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
     double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
@@ -93,6 +95,7 @@ struct krd_handle {
     int64_t* d_tile_ptr = nullptr; // n_eblocks x N (+1): first tile-major entry of (edge block b, sample i)
     double*  d_M = nullptr;        // E x ld: subtree mass at the proximal end of every edge
     void*    d_scratch[3] = {nullptr, nullptr, nullptr};   // K0 scratch, grow-only
+    void*    d_flags = nullptr;    // K0: canonical-order / range check flags
     double*  d_D = nullptr;        // E x ld: mass strictly below every edge (sum of its child edges' M)
 
     // ---- pair kernel workspace ----
@@ -100,8 +103,23 @@ struct krd_handle {
     size_t  ws_capacity = 0;
     krd::Tile* d_tiles = nullptr;
     std::vector<krd::Tile> h_tiles;
-    void* d_sched = nullptr;      // work items + per-CTA offsets + per-tile offsets of the pair kernel
+    void* d_sched = nullptr;      // work items + per-CTA offsets + per-tile offsets of the pair kernel (current schedule)
     int64_t sched_key = -1, sched_items = 0, sched_cta_bytes = 0;
+    struct Sched { void* d; int64_t items, cta_bytes; };
+    std::unordered_map<int64_t, Sched> scheds;   // schedules by key (tile range, chunks, CTAs, diagonal cost); d_sched points into one
+    int64_t force_t0 = -1, force_t1 = -1;        // pipelined ingest: explicit tile range of the next run_pairs
+    bool custom_tiles = false;                   // tile list set by the pipelined ingest (phase-major), not krd_tile_list
+
+    // ---- pipelined ingest (krd_config.pipeline, krd_pipe.cu): sample-range children whose uploads overlap the pair kernel ----
+    std::vector<krd_handle*> kids;
+    std::vector<int32_t> kid_first;              // first sample of every child (+ N at the end)
+    std::vector<int64_t> phase_off;              // tile ranges of the phases in h_tiles
+    std::vector<std::vector<int64_t>> kid_off;   // rebased host offsets of every child
+    std::vector<cudaEvent_t> kid_ev;             // upload of child q complete (copy stream)
+    cudaStream_t copy_stream = nullptr;
+    int32_t kids_ready = 0;                      // children whose masses are prepared
+    int64_t tree_version = 0, kids_tree_version = -1;
+    bool piped = false;
     int64_t n_tiles_alloc = 0;
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     double* d_out_tmp_sq = nullptr;   // squash clustering: initial N*N distances
@@ -152,6 +170,15 @@ krd_status build_F(krd_handle* h);                    // K1
 krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
                      double* d_out_matrix, double* d_out_packed);
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
+
+// krd_pipe.cu — pipelined ingest (krd_config.pipeline)
+bool pipe_wanted(const krd_handle* h, int32_t n_samples);
+krd_status pipe_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge, const double* pos, const double* mass);
+krd_status pipe_compute(krd_handle* h, double p, double divisor, double* d_out);   // all phases, or everything at once when the children are resident
+krd_status pipe_flatten(krd_handle* h);     // finish the uploads and turn the handle into an ordinary one (squash, k-means, sharding, introspection)
+void pipe_destroy(krd_handle* h);
+krd_status prepare_len_binned(krd_handle* h);   // krd_build.cu: segment lengths / offsets of binned mode (no mass data needed)
+krd_status set_custom_tiles(krd_handle* h, const std::vector<krd::Tile>& tiles);   // krd_pairs.cu
 
 // krd_squash.cu
 krd_status run_squash(krd_handle* h, double p, krd_merger* out);

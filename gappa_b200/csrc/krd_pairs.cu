@@ -603,6 +603,7 @@ static krd_status ensure_tiles(krd_handle* h)
     const int T = (h->N + TILE - 1) / TILE;   // (ld may be wider than N: squash clustering appends cluster columns)
     const int64_t n_tiles = (int64_t)T * (T + 1) / 2;
     if (h->n_tiles_alloc == n_tiles && h->d_tiles) return KRD_OK;
+    if (h->custom_tiles) return fail(h, KRD_ERR_STATE, "pipelined tile list is out of date");
     h->h_tiles.resize((size_t)n_tiles);
     {
         std::vector<int32_t> ti((size_t)n_tiles), tj((size_t)n_tiles);
@@ -615,7 +616,34 @@ static krd_status ensure_tiles(krd_handle* h)
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
     h->n_tiles_alloc = n_tiles;
     h->stats.n_tiles = n_tiles;
-    h->sched_key = -1;
+    h->custom_tiles = false;
+    for (auto& kv : h->scheds) cudaFree(kv.second.d);
+    h->scheds.clear();
+    h->d_sched = nullptr; h->sched_key = -1;
+    return KRD_OK;
+}
+
+static void drop_schedules(krd_handle* h)
+{
+    for (auto& kv : h->scheds) cudaFree(kv.second.d);
+    h->scheds.clear();
+    h->d_sched = nullptr; h->sched_key = -1;
+}
+
+// Tile list in an order of the caller's choice (the pipelined ingest orders it by phase); run_pairs then works on the
+// range [force_t0, force_t1) of it.
+krd_status set_custom_tiles(krd_handle* h, const std::vector<Tile>& tiles)
+{
+    const int64_t n_tiles = (int64_t)tiles.size();
+    h->h_tiles = tiles;
+    cudaFree(h->d_tiles); h->d_tiles = nullptr;
+    KRD_CUDA(h, cudaMalloc(&h->d_tiles, (size_t)std::max<int64_t>(n_tiles, 1) * sizeof(Tile)));
+    KRD_CUDA(h, cudaMemcpyAsync(h->d_tiles, h->h_tiles.data(), (size_t)n_tiles * sizeof(Tile), cudaMemcpyHostToDevice, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->n_tiles_alloc = n_tiles;
+    h->stats.n_tiles = n_tiles;
+    h->custom_tiles = true;
+    drop_schedules(h);
     return KRD_OK;
 }
 
@@ -672,6 +700,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     const int64_t per_rank = tiles_per_rank(n_tiles_all, world);
     int64_t t0 = 0, t1 = 0;
     krd_rank_tiles(n_tiles_all, rank, world, &t0, &t1);
+    if (h->force_t0 >= 0) { t0 = h->force_t0; t1 = h->force_t1; }   // pipelined ingest: one phase of the phase-major list
     const int n_tiles = (int)(t1 - t0);
     if (d_out_packed && n_tiles < per_rank)   // ragged tail: keep the all-gather payload defined
         KRD_CUDA(h, cudaMemsetAsync(d_out_packed + (size_t)n_tiles * TILE * TILE, 0, (size_t)(per_rank - n_tiles) * TILE * TILE * 8, h->stream));
@@ -694,17 +723,22 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
     const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 4096 + (int64_t)(diag_cost * 2048.0);
     if (key != h->sched_key) {
-        std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
-        make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
-        cudaFree(h->d_sched); h->d_sched = nullptr;
-        const size_t b_items = items.size() * sizeof(WorkItem), b_cta = cta_off.size() * 4, b_tile = tile_off.size() * 4;
-        KRD_CUDA(h, cudaMalloc(&h->d_sched, b_items + b_cta + b_tile));
-        char* base = static_cast<char*>(h->d_sched);
-        KRD_CUDA(h, cudaMemcpyAsync(base, items.data(), b_items, cudaMemcpyHostToDevice, h->stream));
-        KRD_CUDA(h, cudaMemcpyAsync(base + b_items, cta_off.data(), b_cta, cudaMemcpyHostToDevice, h->stream));
-        KRD_CUDA(h, cudaMemcpyAsync(base + b_items + b_cta, tile_off.data(), b_tile, cudaMemcpyHostToDevice, h->stream));
-        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
-        h->sched_items = (int64_t)items.size(); h->sched_cta_bytes = (int64_t)b_cta; h->sched_key = key;
+        auto it = h->scheds.find(key);
+        if (it == h->scheds.end()) {
+            if (h->scheds.size() >= 64) drop_schedules(h);
+            std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
+            make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
+            const size_t b_items = items.size() * sizeof(WorkItem), b_cta = cta_off.size() * 4, b_tile = tile_off.size() * 4;
+            void* d = nullptr;
+            KRD_CUDA(h, cudaMalloc(&d, b_items + b_cta + b_tile));
+            char* base = static_cast<char*>(d);
+            KRD_CUDA(h, cudaMemcpyAsync(base, items.data(), b_items, cudaMemcpyHostToDevice, h->stream));
+            KRD_CUDA(h, cudaMemcpyAsync(base + b_items, cta_off.data(), b_cta, cudaMemcpyHostToDevice, h->stream));
+            KRD_CUDA(h, cudaMemcpyAsync(base + b_items + b_cta, tile_off.data(), b_tile, cudaMemcpyHostToDevice, h->stream));
+            KRD_CUDA(h, cudaStreamSynchronize(h->stream));   // the host vectors die here
+            it = h->scheds.emplace(key, krd_handle::Sched{d, (int64_t)items.size(), (int64_t)b_cta}).first;
+        }
+        h->d_sched = it->second.d; h->sched_items = it->second.items; h->sched_cta_bytes = it->second.cta_bytes; h->sched_key = key;
     }
     const size_t b_items = (size_t)h->sched_items * sizeof(WorkItem);
     const WorkItem* d_items = reinterpret_cast<const WorkItem*>(h->d_sched);

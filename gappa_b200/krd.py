@@ -34,7 +34,7 @@ EXPORTS = [
 
 class KrdConfig(C.Structure):
     _fields_ = [("device", C.c_int), ("bins", C.c_int), ("split", C.c_int), ("builder", C.c_int),
-                ("p2_mode", C.c_int), ("reserved", C.c_int * 3)]
+                ("p2_mode", C.c_int), ("pipeline", C.c_int), ("reserved", C.c_int * 2)]
 
 
 class KrdStats(C.Structure):
@@ -153,10 +153,10 @@ def _ptr(a):
 class KrdPlan:
     """One handle of the C ABI: tree + masses resident in HBM, distance matrices on demand."""
 
-    def __init__(self, device=0, bins=0, split=0, builder=0, p2_mode=0):
+    def __init__(self, device=0, bins=0, split=0, builder=0, p2_mode=0, pipeline=0):
         self._L = lib()
         self._h = C.c_void_p()
-        cfg = KrdConfig(device=device, bins=bins, split=split, builder=builder, p2_mode=p2_mode)
+        cfg = KrdConfig(device=device, bins=bins, split=split, builder=builder, p2_mode=p2_mode, pipeline=pipeline)
         st = self._L.krd_create(C.byref(cfg), C.byref(self._h))
         if st != KRD_OK:
             raise KrdError(st, self._L.krd_last_error(None).decode())
@@ -198,6 +198,7 @@ class KrdPlan:
             pos = np.ascontiguousarray(pos, np.float64)
             mass = np.ascontiguousarray(mass, np.float64)
         n = len(off) - 1
+        self._keep_host = [off, edge, pos, mass]   # krd_config.pipeline: the arrays are read until the next compute returns
         self._check(self._L.krd_set_masses(self._h, n, _ptr(off), _ptr(edge), _ptr(pos), _ptr(mass)))
         self.n_samples = n
 

@@ -57,7 +57,16 @@ typedef struct krd_config {
     int p2_mode;       /* exponent 2: 0 = auto (= 2), 1 = direct (a-b)^2 on the FP64 CUDA cores,
                           2 = Gram contraction |a|^2+|b|^2-2ab on the FP64 tensor cores (DMMA m8n8k4) with
                           direct recomputation of the cells where the subtraction cancels */
-    int reserved[3];   /* must be 0 */
+    int pipeline;      /* 1 = pipelined ingest for krd_set_masses + krd_compute[_device] from HOST arrays (binned mode,
+                          1 <= bins <= 31, >= 512 samples; ignored otherwise): the samples are uploaded in four
+                          sample-range blocks and block q's F columns and the pair tiles that need only blocks <= q are
+                          computed while block q+1 is still crossing PCIe.  krd_set_masses returns once the first block
+                          is resident; the rest of the ingest completes inside the first krd_compute*, so (a) the input
+                          arrays must stay valid until that call returns, (b) input errors of the later blocks are
+                          reported by it.  Results agree with the ordinary path to rounding (different partial-sum
+                          splits).  Sharded compute is not available on such a handle; krd_squash / krd_kmeans /
+                          introspection first turn it into an ordinary one. */
+    int reserved[2];   /* must be 0 */
 } krd_config;
 
 typedef struct krd_stats {

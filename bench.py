@@ -50,7 +50,7 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
@@ -275,8 +275,8 @@ def main():
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step = timed(step_device, args.steps, max(args.warmup, 3))
     st = plan.stats()
-    clocks = sampler.stop() if sampler else None
     ms_e2e = timed(step_e2e, max(2, min(args.steps, 5)), 1)
+    clocks = sampler.stop() if sampler else None          # sampled over both timed regions (value and e2e)
 
     if rank == 0:
         # roofline of the dominant kernel (k_pairs): FP64 pipe

@@ -275,8 +275,14 @@ def main():
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step = timed(step_device, args.steps, max(args.warmup, 3))
     st = plan.stats()
-    ms_e2e = timed(step_e2e, max(2, min(args.steps, 5)), 1)
-    clocks = sampler.stop() if sampler else None          # sampled over both timed regions (value and e2e)
+    # clocks: nvidia-smi samples every 20 ms; the timed region is tens of ms, so the same step keeps running (untimed) until
+    # the sampler has seen ~0.4 s of this load.  It is stopped before the e2e region: polling the driver that often delays
+    # the host-side submissions the e2e path depends on (measured +0.9 ms per step).
+    for _ in range(int(min(2000, max(1, 400.0 / max(ms_step, 0.05))))):    # (same count on every rank: ms_step is the max over ranks)
+        step_device()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    ms_e2e = timed(step_e2e, max(2, min(args.steps, 5)), 3)
 
     if rank == 0:
         # roofline of the dominant kernel (k_pairs): FP64 pipe
@@ -303,7 +309,7 @@ def main():
                                           "rounded to 128" if scaling == "weak" else "strong scaling: cohort fixed by --samples"))
                                       if world > 1 else "1 gpu"},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "ingest": "pipelined (krd_config.pipeline=1): 4 sample blocks, upload overlapped with K0/K1/pair phases" if world == 1
+                    "ingest": "pipelined (krd_config.pipeline=1): up to 8 sample blocks, upload overlapped with K0/K1/pair phases" if world == 1
                               else "sharded upload + NVLink all-gather of the entries",
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(N * N * 8)},
             "gpu_launches": int(st["launches"]) * args.steps,

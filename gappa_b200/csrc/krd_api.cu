@@ -27,6 +27,7 @@ krd_status reserve(krd_handle* h, void** p, size_t bytes)
     if (bytes == 0) bytes = 16;
     auto it = h->caps.find(p);
     if (*p && it != h->caps.end() && it->second >= bytes) return KRD_OK;
+    if (h->capturing) return fail(h, KRD_ERR_STATE, "buffer growth inside a captured phase");   // (the phase is re-issued launch by launch)
     if (*p) { cudaFree(*p); *p = nullptr; }
     h->caps[p] = 0;
     KRD_CUDA(h, cudaMalloc(p, bytes));
@@ -168,7 +169,8 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
     if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = sample_off[n_samples];
     if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
-    KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    if (h->d_off_from) launch_rebase_off(h->d_off_from, n_samples + 1, h->d_off, h->stream);
+    else KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     h->d_edge = const_cast<int32_t*>(d_edge); h->d_pos = const_cast<double*>(d_pos); h->d_mass = const_cast<double*>(d_mass);
     st = prepare_masses(h);
     if (st != KRD_OK) return st;
@@ -192,7 +194,11 @@ static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank
     KRD_CUDA(h, cudaSetDevice(h->device));
     if (h->piped) {
         if (world != 1 || d_packed) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }   // sharding works on the ordinary tile order
-        else return pipe_compute(h, p, divisor, d_out);
+        else {
+            krd_status ps = pipe_compute(h, p, divisor, d_out);
+            if (ps != KRD_OK || h->piped) return ps;
+            // (a late child was not in MassTree order: the handle has been flattened, continue the ordinary way)
+        }
     }
     h->stats.launches = 0;
     cudaEventRecord(h->ev[0], h->stream);

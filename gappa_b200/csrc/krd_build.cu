@@ -149,6 +149,29 @@ __global__ void k_check_canonical(const uint32_t* __restrict__ sid, const int32_
     }
 }
 
+// Deferred check (children of a pipelined ingest, whose entries are the parent's OWN device copy): an edge id outside
+// the tree is recorded (flags |= 2) and replaced by 0 so that everything downstream stays inside its buffers; the host
+// reads the flags once, when the whole pipeline has been issued, and fails the call then.
+__global__ void k_clamp_edges(int32_t* __restrict__ edge, int64_t M, int E, int* __restrict__ flags)
+{
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const int e = edge[m];
+    if (e < 0 || e >= E) { atomicOr(flags, 2); edge[m] = 0; }
+}
+
+// Sample offsets of a pipelined child = the parent's (already on the device), rebased to the child's first entry.  (A host
+// copy here would queue behind the cohort's bulk upload on the copy engine: measured 0.3 ms per child at cfg2.)
+__global__ void k_rebase_off(const int64_t* __restrict__ src, int n, int64_t* __restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i] - src[0];
+}
+void launch_rebase_off(const int64_t* d_src, int n, int64_t* d_dst, cudaStream_t stream)
+{
+    k_rebase_off<<<(n + 255) / 256, 256, 0, stream>>>(d_src, n, d_dst);
+}
+
 __global__ void k_iota(uint32_t* a, int64_t M)
 {
     int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -257,6 +280,18 @@ __global__ void k_sqrt(const double* __restrict__ a, int64_t n, double* __restri
 
 static inline unsigned nblk(int64_t n, int bs = 256) { return (unsigned)((n + bs - 1) / bs); }
 
+// Zero fill by a KERNEL (rows x width 8-byte words, row pitch in words).  cudaMemset*Async may run on a copy engine, where
+// it queues behind the bulk upload of a pipelined ingest (measured: +0.25 ms per child at cfg2).
+__global__ void k_zero_words(unsigned long long* __restrict__ p, int64_t pitch, int64_t width, int64_t rows)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < width * rows) p[(g / width) * pitch + g % width] = 0ull;
+}
+static inline void zero_words(void* p, int64_t pitch, int64_t width, int64_t rows, cudaStream_t st)
+{
+    if (width * rows > 0) k_zero_words<<<nblk(width * rows), 256, 0, st>>>(static_cast<unsigned long long*>(p), pitch, width, rows);
+}
+
 struct DevBuf {  // scoped device scratch
     void* p = nullptr;
     cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
@@ -314,7 +349,7 @@ krd_status prepare_len_binned(krd_handle* h)
     if ((rs = reserve(h, (void**)&h->d_seg_off, (size_t)(E + 1) * 4)) != KRD_OK) return rs;
     if ((rs = reserve(h, (void**)&h->d_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
     if ((rs = reserve(h, (void**)&h->d_sqrt_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
-    KRD_CUDA(h, cudaMemsetAsync(h->d_len, 0, (size_t)h->S_pad * 8, h->stream));
+    zero_words(h->d_len, h->S_pad, h->S_pad, 1, h->stream);
     k_len_binned<<<nblk((int64_t)E * (B + 1) + 1), 256, 0, h->stream>>>(h->d_bl, E, B, h->d_len, h->d_seg_off);
     k_sqrt<<<nblk(h->S_pad), 256, 0, h->stream>>>(h->d_len, h->S_pad, h->d_sqrt_len);
     KRD_CUDA(h, cudaGetLastError());
@@ -335,14 +370,17 @@ krd_status prepare_masses(krd_handle* h)
     { krd_status rs = reserve(h, &h->d_flags, 16); if (rs != KRD_OK) return rs; }
     int* const d_flags = static_cast<int*>(h->d_flags);
     { krd_status rs = reserve(h, (void**)&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
-    KRD_CUDA(h, cudaMemsetAsync(d_flags, 0, sizeof(int), h->stream));
+    zero_words(d_flags, 1, 1, 1, h->stream);   // (16 bytes reserved)
     if (M > 0) {
         k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
+        if (h->defer_check) k_clamp_edges<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, M, E, d_flags);
         k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, M, E, d_flags);
     }
     int hflags = 0;
-    KRD_CUDA(h, cudaMemcpyAsync(&hflags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (!h->defer_check) {   // (deferred: no host round trip here; krd_pipe.cu reads d_flags after the last phase is issued)
+        KRD_CUDA(h, cudaMemcpyAsync(&hflags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
     if (hflags & 2) return fail(h, KRD_ERR_INVALID_ARGUMENT, "mass entry refers to an edge outside the tree");
     if (hflags & 1) {
         // sort by (sample, edge, pos), stable: three LSD passes, then gather into owned buffers
@@ -375,7 +413,7 @@ krd_status prepare_masses(krd_handle* h)
         krd_status rs = reserve(h, (void**)&h->d_len, (size_t)h->S_pad * 8);
         if (rs != KRD_OK) return rs;
         if ((rs = reserve(h, (void**)&h->d_sqrt_len, (size_t)h->S_pad * 8)) != KRD_OK) return rs;
-        KRD_CUDA(h, cudaMemsetAsync(h->d_len, 0, (size_t)h->S_pad * 8, h->stream));
+        zero_words(h->d_len, h->S_pad, h->S_pad, 1, h->stream);
         return KRD_OK;
     };
 
@@ -426,7 +464,7 @@ krd_status prepare_masses(krd_handle* h)
     }
     k_sqrt<<<nblk(h->S_pad), 256, 0, h->stream>>>(h->d_len, h->S_pad, h->d_sqrt_len);
     KRD_CUDA(h, cudaGetLastError());
-    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (!h->ld_fixed) KRD_CUDA(h, cudaStreamSynchronize(h->stream));   // (a child of a pipelined ingest keeps the stream running)
 
     if (!h->ld_fixed) { h->ld = ((N + h->extra_cols + TILE - 1) / TILE) * TILE; h->ncols = h->ld; }
     else h->ncols = ((N + TILE - 1) / TILE) * TILE;     // child of a pipelined ingest: own columns inside the parent's F
@@ -521,9 +559,13 @@ __global__ void k_block_ptr(const int64_t* __restrict__ off, const int32_t* __re
     blk_ptr[g] = lo;
 }
 
-__global__ void k_slice_len(const int64_t* __restrict__ blk_ptr, int64_t n, int N, int64_t* __restrict__ len)
+// `guard` (deferred check only, else nullptr): a non-zero flag word means the entries are not in canonical order or were
+// clamped — the block pointers are then meaningless, so every slice is made empty (k_tile sees no entries) and
+// k_tile_order does nothing; the host discards the results when it reads the flags.
+__global__ void k_slice_len(const int64_t* __restrict__ blk_ptr, int64_t n, int N, int64_t* __restrict__ len, const int* __restrict__ guard)
 {
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (guard && *guard) { if (g <= n) len[g] = 0; return; }
     if (g < n) len[g] = blk_ptr[g + N] - blk_ptr[g];
     else if (g == n) len[g] = 0;
 }
@@ -534,10 +576,10 @@ __global__ void k_slice_len(const int64_t* __restrict__ blk_ptr, int64_t n, int 
 __global__ void k_tile_order(const uint32_t* __restrict__ sid, const int32_t* __restrict__ edge, const int32_t* __restrict__ slot,
                              const double* __restrict__ mass, const int64_t* __restrict__ blk_ptr,
                              const int64_t* __restrict__ tile_ptr, int64_t M, int N, int EB, int B1,
-                             uint16_t* __restrict__ cell, double* __restrict__ tmass)
+                             uint16_t* __restrict__ cell, double* __restrict__ tmass, const int* __restrict__ guard)
 {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= M) return;
+    if (m >= M || (guard && *guard)) return;
     const int i = (int)sid[m], e = edge[m], b = e / EB;
     const int64_t g = (int64_t)b * N + i;
     const int64_t dst = tile_ptr[g] + (m - blk_ptr[g]);
@@ -701,21 +743,22 @@ static krd_status prepare_tiled(krd_handle* h)
     if ((st = reserve(h, (void**)&h->d_tile_ptr, (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
-    KRD_CUDA(h, cudaMemsetAsync(h->d_D, 0, (size_t)h->E * h->ld * 8, h->stream));   // leaf edges: nothing below
+    zero_words(h->d_D, h->ld, h->ncols, h->E, h->stream);   // leaf edges: nothing below (own columns)
     // scratch lives in the handle (grow-only): no cudaMalloc/cudaFree, no host sync on this path
     if ((st = reserve(h, &h->d_scratch[0], (size_t)(n_slices + h->N) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_scratch[1], (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
     int64_t* blk = static_cast<int64_t*>(h->d_scratch[0]);
     int64_t* len = static_cast<int64_t*>(h->d_scratch[1]);
     k_block_ptr<<<nblk(n_slices + h->N), 256, 0, h->stream>>>(h->d_off, h->d_edge, h->N, h->n_eblocks, h->EB, blk);
-    k_slice_len<<<nblk(n_slices + 1), 256, 0, h->stream>>>(blk, n_slices, h->N, len);
+    const int* guard = h->defer_check ? static_cast<const int*>(h->d_flags) : nullptr;
+    k_slice_len<<<nblk(n_slices + 1), 256, 0, h->stream>>>(blk, n_slices, h->N, len, guard);
     size_t bytes = 0;
     KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(nullptr, bytes, len, h->d_tile_ptr, n_slices + 1, h->stream));
     if ((st = reserve(h, &h->d_scratch[2], bytes)) != KRD_OK) return st;
     KRD_CUDA(h, cub::DeviceScan::ExclusiveSum(h->d_scratch[2], bytes, len, h->d_tile_ptr, n_slices + 1, h->stream));
     if (h->M > 0)
         k_tile_order<<<nblk(h->M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_slot, h->d_mass, blk, h->d_tile_ptr,
-                                                        h->M, h->N, h->EB, B1, h->d_cell, h->d_tmass);
+                                                        h->M, h->N, h->EB, B1, h->d_cell, h->d_tmass, guard);
     KRD_CUDA(h, cudaGetLastError());
     h->tiled = true;
     return KRD_OK;
@@ -728,7 +771,7 @@ static krd_status build_F_tiled(krd_handle* h)
     static std::atomic<unsigned long long> configured{0};
     KRD_CUDA(h, allow_dynamic_smem(k_tile<true>, FT_MAX_ROWS * FTS * 8, configured));
     if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero (own columns only)
-        KRD_CUDA(h, cudaMemset2DAsync(h->d_F + (size_t)h->S * h->ld, (size_t)h->ld * 8, 0, (size_t)h->ncols * 8, (size_t)(h->S_pad - h->S), h->stream));
+        zero_words(h->d_F + (size_t)h->S * h->ld, h->ld, h->ncols, h->S_pad - h->S, h->stream);
     dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ncols / FT));
     k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
                                                       nullptr, h->d_M, nullptr);

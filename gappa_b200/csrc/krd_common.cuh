@@ -117,9 +117,15 @@ struct krd_handle {
     std::vector<std::vector<int64_t>> kid_off;   // rebased host offsets of every child
     std::vector<cudaEvent_t> kid_ev;             // upload of child q complete (copy stream)
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t cap_stream = nullptr;           // capture-only stream of the phase graphs (never executes anything)
     int32_t kids_ready = 0;                      // children whose masses are prepared
     int64_t tree_version = 0, kids_tree_version = -1;
     bool piped = false;
+    const int64_t* d_off_from = nullptr;         // child: its sample offsets are this device array (the parent's), rebased
+    bool defer_check = false;                    // child q >= 1: K0 leaves its check flags on the device (no host round trip)
+    bool graph_ok = false;                       // a phase has run launch by launch once (buffers, schedules exist)
+    std::vector<cudaGraphExec_t> phase_exec;     // executable graph of every phase, updated in place call after call
+    bool capturing = false;                      // inside a stream capture (a phase of the pipelined ingest): no timing events
     int64_t n_tiles_alloc = 0;
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     double* d_out_tmp_sq = nullptr;   // squash clustering: initial N*N distances
@@ -162,6 +168,7 @@ inline cudaError_t allow_dynamic_smem(Kernel kernel, int bytes, std::atomic<unsi
 krd_status reserve(krd_handle* h, void** p, size_t bytes);
 
 // krd_build.cu
+void launch_rebase_off(const int64_t* d_src, int n, int64_t* d_dst, cudaStream_t stream);
 krd_status build_tree(krd_handle* h);                 // host preprocessing + upload
 krd_status prepare_masses(krd_handle* h);             // canonical order, slots, segment table
 krd_status build_F(krd_handle* h);                    // K1

@@ -462,20 +462,23 @@ struct EpiParams {
     const double* norm; // Gram mode: |a_i - c|^2 per sample, else nullptr
     int4* fix;          // Gram mode: pairs whose Gram difference cancelled too much; fix[0].x = count, entries from fix[1]
     int fix_cap;
+    int split;          // CTAs per tile (row bands of 128 / split rows ... 16384 / split cells)
 };
 
 // |a-b|^2 = |a|^2 + |b|^2 - 2ab loses  eps * (|a|^2+|b|^2) / |a-b|^2  relative accuracy.  Cells below this
 // ratio are recomputed directly by k_gram_fixup, which keeps the Gram path inside the 1e-10 bar.
 constexpr double GRAM_CANCEL_RATIO = 1e-3;
 
-constexpr int EPI_SPLIT = 8;   // CTAs per tile (row bands of 16): a small matrix has few tiles (36 at cfg2), one CTA per tile leaves SMs idle
+// CTAs per tile: 8 (row bands of 16) when there are many tiles; a launch over a few tiles (a phase of the pipelined ingest:
+// 1-8 tiles, each with up to 148 partials) is split further so that the partial sums are spread over all SMs.
+constexpr int EPI_SPLIT_MIN = 8, EPI_SPLIT_MAX = 64;
 __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
 {
-    const int t = blockIdx.x / EPI_SPLIT, band = blockIdx.x % EPI_SPLIT;
+    const int t = blockIdx.x / P.split, band = blockIdx.x % P.split;
     const Tile tile = P.tiles[t];
     const int i0 = P.tile_item_off[t], i1 = P.tile_item_off[t + 1];
     const double inv_p = 1.0 / P.p;
-    constexpr int BAND = TILE * TILE / EPI_SPLIT;
+    const int BAND = TILE * TILE / P.split;
     for (int idx = band * BAND + threadIdx.x; idx < (band + 1) * BAND; idx += blockDim.x) {
         double v = 0.0;
         for (int s = i0; s < i1; ++s) v += P.ws[(size_t)s * (size_t)(TILE * TILE) + idx];
@@ -725,6 +728,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     if (key != h->sched_key) {
         auto it = h->scheds.find(key);
         if (it == h->scheds.end()) {
+            if (h->capturing) return fail(h, KRD_ERR_STATE, "schedule not cached inside a captured phase");   // (re-issued launch by launch)
             if (h->scheds.size() >= 64) drop_schedules(h);
             std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
             make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
@@ -747,6 +751,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
 
     const size_t ws_need = (size_t)h->sched_items * TILE * TILE * sizeof(double);
     if (ws_need > h->ws_capacity) {
+        if (h->capturing) return fail(h, KRD_ERR_STATE, "workspace growth inside a captured phase");
         cudaFree(h->d_ws); h->d_ws = nullptr; h->ws_capacity = 0;
         KRD_CUDA(h, cudaMalloc(&h->d_ws, ws_need));
         h->ws_capacity = ws_need;
@@ -771,7 +776,7 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
             break;
     }
     if (e != cudaSuccess) return cuda_fail(h, e, "k_pairs launch");
-    cudaEventRecord(h->ev[2], h->stream);
+    if (!h->capturing) cudaEventRecord(h->ev[2], h->stream);
 
     EpiParams Q;
     Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.tile_item_off = d_tile_off; Q.n_tiles = n_tiles; Q.N = h->N;
@@ -783,7 +788,9 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
         KRD_CUDA(h, cudaMemsetAsync(h->d_fix, 0, sizeof(int4), h->stream));
         Q.norm = h->d_norm; Q.fix = static_cast<int4*>(h->d_fix); Q.fix_cap = FIX_CAP;
     }
-    k_epilogue<<<(unsigned)n_tiles * EPI_SPLIT, 256, 0, h->stream>>>(Q);
+    Q.split = EPI_SPLIT_MIN;
+    while (Q.split < EPI_SPLIT_MAX && (int64_t)n_tiles * Q.split < 4 * (int64_t)h->num_sms) Q.split *= 2;
+    k_epilogue<<<(unsigned)n_tiles * Q.split, 256, 0, h->stream>>>(Q);
     if (mode == MODE_P2G) {
         k_gram_fixup<<<2 * h->num_sms, 256, 0, h->stream>>>(static_cast<const int4*>(h->d_fix), FIX_CAP, h->d_F, h->d_len, h->ld, h->S_pad,
                                                             h->N, divisor, d_out_matrix, d_out_packed);

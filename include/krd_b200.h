@@ -58,7 +58,7 @@ typedef struct krd_config {
                           2 = Gram contraction |a|^2+|b|^2-2ab on the FP64 tensor cores (DMMA m8n8k4) with
                           direct recomputation of the cells where the subtraction cancels */
     int pipeline;      /* 1 = pipelined ingest for krd_set_masses + krd_compute[_device] from HOST arrays (binned mode,
-                          1 <= bins <= 31, >= 512 samples; ignored otherwise): the samples are uploaded in four
+                          1 <= bins <= 31, >= 512 samples; ignored otherwise): the samples are uploaded in up to eight
                           sample-range blocks and block q's F columns and the pair tiles that need only blocks <= q are
                           computed while block q+1 is still crossing PCIe.  krd_set_masses returns once the first block
                           is resident; the rest of the ingest completes inside the first krd_compute*, so (a) the input

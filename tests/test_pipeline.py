@@ -27,7 +27,7 @@ def _close(a, b, tol=1e-12):
     return np.max(np.abs(a[off] - b[off]) / np.maximum(b[off], 1e-300)) <= tol and np.array_equal(np.diag(a), np.diag(b))
 
 
-@pytest.mark.parametrize("n,bins", [(600, 3), (1000, 4), (512, 1), (777, 7)])
+@pytest.mark.parametrize("n,bins", [(600, 3), (1000, 4), (512, 1), (777, 7), (1300, 2)])
 def test_pipelined_equals_ordinary(n, bins):
     tree, mass = _data(n)
     ref = _plan(tree, mass, bins)
@@ -100,4 +100,27 @@ def test_error_in_a_late_block_surfaces_at_compute():
     pip.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
     ref = _plan(tree, mass, 2)
     assert _close(pip.compute(p=1.0), ref.compute(p=1.0))
+    pip.close(); ref.close()
+
+
+def test_unsorted_late_block_falls_back_to_the_sorting_path():
+    """Children after the first are checked without a host round trip (flags read once at the end): entries that are
+    not in MassTree order in a late block make the call start over on the ordinary path, which sorts them."""
+    import gappa_b200
+    tree, mass = _data(700)
+    off = mass["off"]
+    edge, pos, m = mass["edge"].copy(), mass["pos"].copy(), mass["mass"].copy()
+    for i in (650, 699):                       # reverse the entries of two samples of the last block
+        a, b = off[i], off[i + 1]
+        edge[a:b] = edge[a:b][::-1]; pos[a:b] = pos[a:b][::-1]; m[a:b] = m[a:b][::-1]
+    ref = _plan(tree, mass, 2)
+    want = ref.compute(p=1.0)
+    pip = gappa_b200.KrdPlan(bins=2, pipeline=1)
+    pip.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    for p in (1.0, 2.0):
+        pip.set_masses(off, edge, pos, m)
+        got = pip.compute(p=p)
+        assert _close(got, ref.compute(p=p), 1e-11), p
+    pip.set_masses(off, mass["edge"], mass["pos"], mass["mass"])     # and a clean cohort afterwards: phased again
+    assert _close(pip.compute(p=1.0), want)
     pip.close(); ref.close()

@@ -198,7 +198,7 @@ def main():
     h_edge = torch.from_numpy(masses["edge"]).pin_memory()
     h_pos = torch.from_numpy(masses["pos"]).pin_memory()
     h_mass = torch.from_numpy(masses["mass"]).pin_memory()
-    h_out = torch.empty((N, N), dtype=torch.float64).pin_memory()
+    h_out = torch.empty((N, N) if rank == 0 else (1, 1), dtype=torch.float64).pin_memory()   # only rank 0 receives the matrix
     h2d_bytes = sum(t.numel() * t.element_size() for t in (h_off, h_edge, h_pos, h_mass))
 
     plan = gappa_b200.KrdPlan(device=local, bins=bins)

@@ -333,6 +333,17 @@ def main():
                          "ms_kernel": st["ms_pairs"], "ms_build_F": st["ms_build"], "ms_epilogue": st["ms_epilogue"],
                          "ctas": st["pair_ctas"], "split": st["split"]},
         }
+        # second kernel group of the step: the F builder (K1) is HBM-bound; algorithmic bytes per build:
+        # F written once + the tile-major entries read twice (10 B each) + ~5 passes over the E x ld subtree matrices
+        try:
+            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]); hbm_src = "MEASURED_PEAKS.json hbm_gbs"
+        except (OSError, KeyError, ValueError):
+            hbm_peak, hbm_src = 6550.0, "fallback (B200_PROFILING.md copy bandwidth)"
+        k1_bytes = float(st["f_bytes"]) + 20.0 * st["n_masses"] + 40.0 * spec["edges"] * st["ld_samples"]
+        k1_gbs = k1_bytes / (st["ms_build"] * 1e-3) / 1e9 if st["ms_build"] > 0 else 0.0
+        line["roofline_build_F"] = {"bound": "hbm", "kernel": "K1 (k_tile<TOTALS>, k_subtree_level/top, k_tile<FILL>)", "achieved": k1_gbs,
+                                    "peak": hbm_peak, "unit": "GB/s", "frac": k1_gbs / hbm_peak, "bytes": k1_bytes,
+                                    "ms": st["ms_build"], "peak_source": hbm_src, "share_of_step": st["ms_build"] / ms_step}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_rate(tree, masses, p, bins, args.cpu_seconds)
         print(json.dumps(line))

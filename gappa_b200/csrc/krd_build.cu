@@ -592,7 +592,7 @@ constexpr int FTS = FT + 1;   // shared-memory row stride (doubles): odd, so tha
 template <bool FILL>
 __global__ void __launch_bounds__(256)
 k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, const int64_t* __restrict__ tile_ptr,
-       int N, int64_t ld, int E, int EB, int B1, const double* __restrict__ Dsub, double* __restrict__ Msub,
+       int N, int64_t ld, int64_t ldm, int E, int EB, int B1, const double* __restrict__ Dsub, double* __restrict__ Msub,
        double* __restrict__ F)
 {
     extern __shared__ double tile[];   // [rows][FTS]
@@ -646,11 +646,11 @@ k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, cons
         // thread = (edge group, sample): running sum down each edge, started from the mass below it
         // (emd.cpp:141 current_mass = node_masses[secondary]; :149-166 distal -> proximal)
         const int il = tid & (FT - 1), eg = tid / FT;
-        const double* dcol = Dsub + (int64_t)e0 * ld + i0 + il;
+        const double* dcol = Dsub + (int64_t)e0 * ldm + i0 + il;
         for (int el = eg; el < ne; el += 2 * (256 / FT)) {
             const int el2 = el + 256 / FT;
-            double acc = dcol[(int64_t)el * ld];
-            double acc2 = (el2 < ne) ? dcol[(int64_t)el2 * ld] : 0.0;
+            double acc = dcol[(int64_t)el * ldm];
+            double acc2 = (el2 < ne) ? dcol[(int64_t)el2 * ldm] : 0.0;
             double* t = tile + (size_t)el * B1 * FTS + il;
             for (int s = B1 - 1; s >= 0; --s) { acc += t[s * FTS]; t[s * FTS] = acc; }
             if (el2 < ne) {
@@ -660,10 +660,11 @@ k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, cons
         }
         __syncthreads();
     }
-    double* dst = (FILL ? F : Msub) + (int64_t)base * ld + i0;
+    const int64_t ldo = FILL ? ld : ldm;       // F has the (parent's) sample stride, M/D the handle's own column count
+    double* dst = (FILL ? F : Msub) + (int64_t)base * ldo + i0;
     for (int k = tid; k < rows * FT; k += 256) {
         const int r = k / FT, cc = k % FT;
-        dst[(int64_t)r * ld + cc] = tile[r * FTS + cc];
+        dst[(int64_t)r * ldo + cc] = tile[r * FTS + cc];
     }
 }
 
@@ -741,9 +742,9 @@ static krd_status prepare_tiled(krd_handle* h)
     if ((st = reserve(h, (void**)&h->d_cell, (size_t)std::max<int64_t>(h->M, 1) * 2)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_tmass, (size_t)std::max<int64_t>(h->M, 1) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_tile_ptr, (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
-    if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
-    if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ld * 8)) != KRD_OK) return st;
-    zero_words(h->d_D, h->ld, h->ncols, h->E, h->stream);   // leaf edges: nothing below (own columns)
+    if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;   // E x ncols (stride ncols)
+    if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;
+    zero_words(h->d_D, h->ncols, h->ncols, h->E, h->stream);   // leaf edges: nothing below
     // scratch lives in the handle (grow-only): no cudaMalloc/cudaFree, no host sync on this path
     if ((st = reserve(h, &h->d_scratch[0], (size_t)(n_slices + h->N) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_scratch[1], (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
@@ -773,7 +774,8 @@ static krd_status build_F_tiled(krd_handle* h)
     if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero (own columns only)
         zero_words(h->d_F + (size_t)h->S * h->ld, h->ld, h->ncols, h->S_pad - h->S, h->stream);
     dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ncols / FT));
-    k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
+    const int64_t ldm = h->ncols;   // stride of M / D: the handle's own columns (a pipelined child owns a slice of the parent's F)
+    k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
                                                       nullptr, h->d_M, nullptr);
     const int L = (int)h->lvl_off.size() - 1;
     const size_t smem_top = (size_t)2 * h->top_edges * TOP_COLS * 8 +
@@ -784,16 +786,16 @@ static krd_status build_F_tiled(krd_handle* h)
     for (int l = 1; l < l_end; ++l, ++n_launch) {   // level 0 = leaf edges: nothing below them
         const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
         dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ncols / 128));
-        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, h->ld, h->d_M, h->d_D);
+        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, ldm, h->d_M, h->d_D);
     }
     if (use_top) {
         static std::atomic<unsigned long long> top_configured{0};
         KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
         k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
-                                                                                 h->ld, h->d_M, h->d_D);
+                                                                                 ldm, h->d_M, h->d_D);
         ++n_launch;
     }
-    k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, h->E, h->EB, B1,
+    k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
                                                      h->d_D, nullptr, h->d_F);
     KRD_CUDA(h, cudaGetLastError());
     h->build_launches = n_launch;   // totals + level passes + top-of-tree + fill

@@ -93,10 +93,10 @@ struct krd_handle {
     uint16_t* d_cell = nullptr;    // M, tile-major order: (row << 6 | sample-in-tile) of every mass entry
     double*  d_tmass = nullptr;    // M, tile-major order: the masses
     int64_t* d_tile_ptr = nullptr; // n_eblocks x N (+1): first tile-major entry of (edge block b, sample i)
-    double*  d_M = nullptr;        // E x ld: subtree mass at the proximal end of every edge
+    double*  d_M = nullptr;        // E x ncols: subtree mass at the proximal end of every edge
     void*    d_scratch[3] = {nullptr, nullptr, nullptr};   // K0 scratch, grow-only
     void*    d_flags = nullptr;    // K0: canonical-order / range check flags
-    double*  d_D = nullptr;        // E x ld: mass strictly below every edge (sum of its child edges' M)
+    double*  d_D = nullptr;        // E x ncols: mass strictly below every edge (sum of its child edges' M)
 
     // ---- pair kernel workspace ----
     double* d_ws = nullptr;

@@ -63,7 +63,8 @@ typedef struct krd_config {
                           computed while block q+1 is still crossing PCIe.  krd_set_masses returns once the first block
                           is resident; the rest of the ingest completes inside the first krd_compute*, so (a) the input
                           arrays must stay valid until that call returns, (b) input errors of the later blocks are
-                          reported by it.  Results agree with the ordinary path to rounding (different partial-sum
+                          reported by it (their checks are read back once, after the last phase; a later block whose
+                          entries are not in MassTree order makes the call start over on the ordinary, sorting path).  Results agree with the ordinary path to rounding (different partial-sum
                           splits).  Sharded compute is not available on such a handle; krd_squash / krd_kmeans /
                           introspection first turn it into an ordinary one. */
     int reserved[2];   /* must be 0 */

@@ -24,13 +24,46 @@ __device__ __forceinline__ double kr_rsqrt_seed_abs(double d)   // ~ 1/sqrt(|d|)
     return __hiloint2double(xh < 0x00100000 ? 0 : __double2hiint(r), __double2loint(r));
 }
 
+// Shorter forms: the reference's std::pow is correctly rounded, the bar is 1e-10, so ONE second-order step is enough.
+// With r = (1 + q)/sqrt(x), |q| <= 2^-22, both forms below return sqrt(x) (1 - 3/2 q^2 - ...): relative error <= 8.6e-14.
+//   KRD_SQRT_SHORT = 2 (default)  y = x r,  e = 1 - y r,  s = y + (y e)/2        4 FP64 (DMUL, DFMA, DMUL, DFMA)
+//   KRD_SQRT_SHORT = 1            y = x r,  s = y + (x - y^2) h,  h = r/2        3 FP64 + the integer work for h
+//   KRD_SQRT_SHORT = 0            the 5-instruction third-order step above (error 2^-64)
+// Measured at the cfg2 shape (pair kernel, p = 1/2): 12.9 ms / 14.1 ms / 14.8 ms.  Per operator the kernel issues
+// DADD + sqrt + DFMA on the FP64 pipe (2 issue cycles each) plus MUFU, LOP3, ISETP, SEL and a MOV for the seed: form 2 is
+// FP64-pipe-bound at 12 cycles, form 1 needs h as a second register pair (VIADD, SEL, MOV) and becomes issue-bound at ~15.
+#ifndef KRD_SQRT_SHORT
+#define KRD_SQRT_SHORT 2
+#endif
+__device__ __forceinline__ void kr_rsqrt_seed_abs2(double d, double& r, double& h)   // r ~ 1/sqrt(|d|), h = r/2; both 0-ish for |d| < 2^-1022
+{
+    const int xh = __double2hiint(d) & 0x7fffffff;
+    double s;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(s) : "d"(__hiloint2double(xh, __double2loint(d))));   // MUFU.RSQ64H
+    const int sh = __double2hiint(s), sl = __double2loint(s);
+    const bool tiny = xh < 0x00100000;
+    r = __hiloint2double(tiny ? 0 : sh, sl);
+    h = __hiloint2double(tiny ? 0 : sh - 0x00100000, sl);
+}
+
 __device__ __forceinline__ double kr_sqrt_abs(double d)
 {
+#if KRD_SQRT_SHORT == 2
+    const double r = kr_rsqrt_seed_abs(d);
+    const double y = fabs(d) * r;
+    return fma(y * fma(-y, r, 1.0), 0.5, y);
+#elif KRD_SQRT_SHORT
+    double r, h;
+    kr_rsqrt_seed_abs2(d, r, h);
+    const double y = fabs(d) * r;
+    return fma(fma(-y, y, fabs(d)), h, y);
+#else
     const double r = kr_rsqrt_seed_abs(d);
     const double y = fabs(d) * r;
     const double e = fma(-y, r, 1.0);
     const double t = fma(0.375, e, 0.5);
     return fma(y * e, t, y);
+#endif
 }
 
 // One row of the register tile for p = 1/2, written stage by stage over the NC columns so that the NC independent
@@ -42,6 +75,27 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
     double d[NC], r[NC], e[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) d[c] = a - b[c];
+#if KRD_SQRT_SHORT == 2   // second-order step in the e form: y = x r, e = 1 - y r, s = y + (y e)/2 -> 4 FP64, no h
+#pragma unroll
+    for (int c = 0; c < NC; ++c) r[c] = kr_rsqrt_seed_abs(d[c]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fabs(d[c]) * r[c];          // y
+#pragma unroll
+    for (int c = 0; c < NC; ++c) e[c] = fma(-d[c], r[c], 1.0);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) e[c] = d[c] * e[c];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fma(e[c], 0.5, d[c]);
+#elif KRD_SQRT_SHORT
+#pragma unroll
+    for (int c = 0; c < NC; ++c) kr_rsqrt_seed_abs2(d[c], r[c], e[c]);   // e = h = r/2
+#pragma unroll
+    for (int c = 0; c < NC; ++c) r[c] = fabs(d[c]) * r[c];               // y
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fma(-r[c], r[c], fabs(d[c]));    // x - y^2
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fma(d[c], e[c], r[c]);           // sqrt
+#else
 #pragma unroll
     for (int c = 0; c < NC; ++c) r[c] = kr_rsqrt_seed_abs(d[c]);
 #pragma unroll
@@ -54,6 +108,7 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
     for (int c = 0; c < NC; ++c) e[c] = d[c] * e[c];
 #pragma unroll
     for (int c = 0; c < NC; ++c) d[c] = fma(e[c], r[c], d[c]);
+#endif
 #pragma unroll
     for (int c = 0; c < NC; ++c) acc[c] = fma(l, d[c], acc[c]);
 }

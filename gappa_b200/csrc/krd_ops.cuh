@@ -121,12 +121,14 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
 constexpr int POW_TAB = 128 + 128 + 32;
 static __device__ double g_pow_tab[POW_TAB];   // one copy per translation unit
 
-__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)
+__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)   // x >= 0 (no sign bit)
 {
-    const long long ix = __double_as_longlong(x);
-    const int e = (int)(ix >> 52) - 1023;
-    const int j = (int)(ix >> 45) & 127;
-    const double m = __longlong_as_double((ix & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);
+    // exponent / table index / mantissa from the HIGH word with 32-bit integer operations (64-bit shifts cost three
+    // instructions each); every clamp and the x = 0 case are integer compares — an FP64 compare occupies the FP64 pipe
+    const int hi = __double2hiint(x), lo = __double2loint(x);
+    const int e = (hi >> 20) - 1023;
+    const int j = (hi >> 13) & 127;
+    const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, lo);
     const double r = fma(m, tab[j], -1.0);
     double q = fma(r, 0.28853900817779268, -0.36067376022224085);     // 1/(5 ln2), -1/(4 ln2)  (degree 5: the r^6 term is < 9e-16)
     q = fma(r, q, 0.48089834696298783);                                //  1/(3 ln2)
@@ -135,21 +137,25 @@ __device__ __forceinline__ double kr_pow(double x, double p, const double* __res
     // e as a double without an I2F conversion: 2^52 + 2^31 + e is exact in the low mantissa bits
     const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;
     const double L = fma(r, q, tab[128 + j]) + ed;
-    double t = fmin(fmax(p * L, -1021.0), 1023.0);
+    const double t = p * L;
     const double MAGIC = 6755399441055744.0;                           // 1.5 * 2^52: rounds t*32 to an integer in the low bits
     double kd = fma(t, 32.0, MAGIC);
-    const int k = __double2loint(kd);
+    int k = __double2loint(kd);
     kd -= MAGIC;
-    const double g = fma(kd, -0.03125, t);
+    const double g = fma(kd, -0.03125, t);                             // |g| <= 1/64, from the UNclamped k
     double w = fma(g, 9.6181291076284772e-3, 5.5504108664821580e-2);   // ln2^4/24, ln2^3/6  (degree 4: truncation 1.25e-12 relative, the bar is 1e-10)
     w = fma(g, w, 2.4022650695910071e-1);                              // ln2^2/2
     w = fma(g, w, 6.9314718055994531e-1);                              // ln2
+    // the scale 2^(k/32) is built in the exponent field: keep it a normal number (results beyond under/overflow anyway;
+    // |32 t| < 2^31 is assumed, i.e. p < 6e4 at the smallest normal x)
+    k = min(max(k, -1021 * 32), 1023 * 32);
     const double s0 = tab[256 + (k & 31)];
-    const double sc = __hiloint2double(__double2hiint(s0) + ((k >> 5) << 20), __double2loint(s0));
-    const double val = fma(sc, g * w, sc);
-    return x > 0.0 ? val : 0.0;
+    // x = 0 or subnormal -> exactly 0 (|F_i - F_j| is full of zeros): a MASK, not a select — a select on so common a
+    // condition was compiled into a divergent branch
+    const int keep = ~((hi - 0x00100000) >> 31);
+    const double sc = __hiloint2double((__double2hiint(s0) + ((k >> 5) << 20)) & keep, __double2loint(s0) & keep);
+    return fma(sc, g * w, sc);
 }
-
 __device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uniform
 {
     double r = (n & 1) ? x : 1.0, base = x;

@@ -184,6 +184,8 @@ static krd_status check_compute(krd_handle* h, double p, double divisor)
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     if (!(p > 0.0))  // also rejects NaN; genesis emd.cpp:186-190
         return fail(h, KRD_ERR_INVALID_EXPONENT, "Invalid exponent value p for earth mover's distance calculation. Has to be > 0.0.");
+    if (p > 30000.0)   // the general-p operator builds 2^(p log2 x) from the integer part of 32 p log2 x: |.| < 2^31 needs p < 6e4
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "exponents above 30000 are not supported");
     if (!h->have_tree || !h->have_masses) return fail(h, KRD_ERR_STATE, "krd_set_tree and krd_set_masses must be called first");
     if (divisor == 0.0 || divisor != divisor) return fail(h, KRD_ERR_INVALID_ARGUMENT, "divisor must be a non-zero number");
     return KRD_OK;

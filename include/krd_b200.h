@@ -114,7 +114,9 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
 
 /* earth_movers_distance(trees, p) [/ divisor].  Builds F (level-synchronous subtree scan), runs
  * the all-pairs kernel, writes the n x n matrix.  `out` is a HOST pointer; returns after the
- * matrix is complete in host memory. divisor = 1.0 for no normalisation. */
+ * matrix is complete in host memory. divisor = 1.0 for no normalisation.  p <= 0 (or NaN) fails with
+ * KRD_ERR_INVALID_EXPONENT and genesis' message (emd.cpp:186-190); p > 30000 fails with KRD_ERR_INVALID_ARGUMENT
+ * (the general-p operator's exp2 argument must fit 31 bits — the one deviation from "any p > 0"). */
 krd_status krd_compute(krd_handle* h, double p, double divisor, double* out);
 
 /* Same with a DEVICE output pointer (n*n doubles); asynchronous on the handle's stream. */

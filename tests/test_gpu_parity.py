@@ -325,3 +325,24 @@ def test_sharded_compute_equals_single(gb, world):
         host = krd.unpack_shards_host(300, [plan.compute_shard_host(r, world, p=p) for r in range(world)])
         assert np.array_equal(host, plan.compute(p=p))
     plan.close()
+
+
+@pytest.mark.gpu
+def test_absurd_exponent_is_rejected_not_garbled():
+    """The general-p operator needs 32 p log2(x) inside 31 bits; beyond p = 30000 the call fails loudly."""
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(99, seed=3)
+    masses = synth.sample_masses(tree, 12, 50, seed=3)
+    plan = gappa_b200.KrdPlan(bins=0)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
+    with pytest.raises(gappa_b200.KrdError, match="30000"):
+        plan.compute(p=1e5)
+    import oracle
+    for p in (250.5, 37.25):             # large but legal
+        got = plan.compute(p=p)
+        want = oracle.port_matrix(tree, masses, p=p, bins=0)
+        assert np.all(np.isfinite(got))
+        assert rel_err(got, want) <= 1e-10, p
+    plan.close()

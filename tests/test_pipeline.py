@@ -124,3 +124,24 @@ def test_unsorted_late_block_falls_back_to_the_sorting_path():
     pip.set_masses(off, mass["edge"], mass["pos"], mass["mass"])     # and a clean cohort afterwards: phased again
     assert _close(pip.compute(p=1.0), want)
     pip.close(); ref.close()
+
+
+def test_pipelined_blocks_without_masses():
+    """Ragged cohorts: a whole late block (and a few scattered samples) without a single mass entry."""
+    import gappa_b200
+    tree, mass = _data(900)
+    off = mass["off"].copy()
+    keep = np.ones(len(mass["edge"]), bool)
+    for i in list(range(640, 768)) + [3, 130, 899]:          # block 5 entirely, plus singles in the first and last block
+        keep[off[i]:off[i + 1]] = False
+    counts = np.diff(mass["off"]); counts[[*range(640, 768), 3, 130, 899]] = 0
+    off2 = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    sub = dict(off=off2, edge=mass["edge"][keep], pos=mass["pos"][keep], mass=mass["mass"][keep])
+    ref = _plan(tree, sub, 3)
+    pip = _plan(tree, sub, 3, pipeline=1)
+    for p in (1.0, 0.5):
+        want, got = ref.compute(p=p), pip.compute(p=p)
+        assert _close(got, want, 1e-12 if p >= 1 else 1e-8), p
+        assert np.all(got[640:768, 640:768] == 0.0)          # empty samples are at distance 0 from each other
+        pip.set_masses(sub["off"], sub["edge"], sub["pos"], sub["mass"])
+    ref.close(); pip.close()

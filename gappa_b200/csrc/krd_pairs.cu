@@ -118,11 +118,60 @@ __device__ unsigned long long g_item_time[2 * 4096];   // (start, end) per work 
 // (64 independent operators, fixed accumulator registers) as the loop body so that it stays inside the instruction cache
 constexpr int mode_unroll(int mode) { return (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC) ? 1 : (mode == MODE_P3 || mode == MODE_P4) ? KRD_P34_UNROLL : KRD_P12_UNROLL; }
 
+// Integer exponents 5..16 with the exponent as a template parameter: one segment = 64 independent, fully static operator
+// chains that the compiler interleaves freely (the run-time ladder kr_row_powi had to stop at every warp-uniform branch:
+// p = 5 ran at 64 % of its FP64 issue bound, p = 3 with a static body at 90 %).  Only the body of the exponent in use
+// (and its diagonal-tile variants) is hot, so the instruction cache sees one ~7 KB loop, not twelve.
+#ifndef KRD_INT_STATIC
+#define KRD_INT_STATIC 1
+#endif
+template <int QMIN, int N>
+__device__ __forceinline__ void chunk_math_int(const double* __restrict__ pa, const double* __restrict__ pb,
+                                            const double* __restrict__ sL, double (&acc)[8][8])
+{
+#pragma unroll 1
+    for (int kk = 0; kk < KC; ++kk) {
+        double a[8], b[8];
+        const double l = sL[kk];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
+            a[2 * q] = va.x; a[2 * q + 1] = va.y;
+        }
+#pragma unroll
+        for (int q = QMIN; q < 4; ++q) {
+            const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
+            b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = fma(l, kr_pow_n<N>(fabs(a[r] - b[cc])), acc[r][cc]);
+    }
+}
+
 template <int MODE, int QMIN>
 __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const double* __restrict__ pb,
                                            const double* __restrict__ sL, double p, const double* __restrict__ tab,
                                            double (&acc)[8][8])
 {
+    if (MODE == MODE_INT && KRD_INT_STATIC) {
+        switch ((int)p) {   // warp-uniform
+            case 5: chunk_math_int<QMIN, 5>(pa, pb, sL, acc); return;
+            case 6: chunk_math_int<QMIN, 6>(pa, pb, sL, acc); return;
+            case 7: chunk_math_int<QMIN, 7>(pa, pb, sL, acc); return;
+            case 8: chunk_math_int<QMIN, 8>(pa, pb, sL, acc); return;
+            case 9: chunk_math_int<QMIN, 9>(pa, pb, sL, acc); return;
+            case 10: chunk_math_int<QMIN, 10>(pa, pb, sL, acc); return;
+            case 11: chunk_math_int<QMIN, 11>(pa, pb, sL, acc); return;
+            case 12: chunk_math_int<QMIN, 12>(pa, pb, sL, acc); return;
+            case 13: chunk_math_int<QMIN, 13>(pa, pb, sL, acc); return;
+            case 14: chunk_math_int<QMIN, 14>(pa, pb, sL, acc); return;
+            case 15: chunk_math_int<QMIN, 15>(pa, pb, sL, acc); return;
+            case 16: chunk_math_int<QMIN, 16>(pa, pb, sL, acc); return;
+            default: break;   // (mode_for_exponent sends nothing else here)
+        }
+    }
 #pragma unroll (mode_unroll(MODE))
     for (int kk = 0; kk < KC; ++kk) {
         double a[8], b[8];
@@ -718,7 +767,12 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     // as long as a full one (measured: p = 3, 4 0.8; halved modes p = 1/2 0.72, integer p 0.85; profiles/cta_balance.py).  Diagonal tiles also run FOUR
     // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
     // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
-    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_INT) ? 0.85 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    if (mode == MODE_INT) {   // static bodies (chunk_math_int): 0.80 measured for 3 multiplications (p = 5), 0.85-0.875 for 6 (p = 15)
+        int mults = 0;
+        for (int n = (int)p; n > 1; n = (n & 1) ? n - 1 : n / 2) ++mults;
+        diag_cost = 0.725 + 0.025 * mults;
+    }
     if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 

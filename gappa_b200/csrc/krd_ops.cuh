@@ -113,30 +113,44 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
     for (int c = 0; c < NC; ++c) acc[c] = fma(l, d[c], acc[c]);
 }
 
-// pow(x, p) = exp2(p * log2 x), x >= 0, p > 0.  Table-driven, all in FP64, relative error < 1.3e-12 + 1e-15 p:
-//   log2: x = 2^e * m, m in [1,2); j = top 7 mantissa bits, c_j = interval midpoint, r = m/c_j - 1 (|r| <= 2^-8),
-//         log2 x = e + log2 c_j + r (A1 + r (A2 + ... r A5))            (truncation 9e-16)
+// pow(x, p) = exp2(p * log2 x), x >= 0, p > 0.  Table-driven, all in FP64, relative error < 1.3e-12 + 4e-14 p:
+//   log2: x = 2^e * m, m in [1,2); j = top 6 mantissa bits, c_j = interval midpoint, r = m/c_j - 1 (|r| <= 2^-7),
+//         log2 x = e + log2 c_j + r (A1 + r (A2 + ... r A5))            (truncation 6e-14)
 //   exp2: t = k/32 + g, |g| <= 1/64; 2^t = 2^(k>>5) * 2^((k&31)/32) * (1 + g (C1 + ... g C4))   (truncation 1.25e-12)
-// tab = [invc 128][logc 128][2^(i/32) 32] in shared memory (make_pow_tables() below).
-constexpr int POW_TAB = 128 + 128 + 32;
+// tab = [invc 64][logc 64][2^(i/32) 32] in shared memory (make_pow_tables() below), entry stride TS.
+#ifndef KRD_POW_I2F
+#define KRD_POW_I2F 0
+#endif
+constexpr int POW_LOGN = 64, POW_EXPN = 32;
+constexpr int POW_TAB = 2 * POW_LOGN + POW_EXPN;
+// Table stride of the pair kernel: every entry is stored 16 times, lane L reads copy L & 15, so that the bank pair of a
+// lookup is fixed by the lane and not by the (data-dependent) index — with one copy the three lookups per operator ran
+// into 4-6-way bank conflicts and the kernel was bound by the shared-memory pipe (48.9 ms; 40.1 ms with every lane
+// reading entry 0).  64 log entries instead of 128 keep the replicated tables at 20 KB (degree 5 still truncates < 6e-14).
+constexpr int POW_TS_PAIR = 16;
 static __device__ double g_pow_tab[POW_TAB];   // one copy per translation unit
 
-__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)   // x >= 0 (no sign bit)
+template <int TS>
+__device__ __forceinline__ double kr_pow(double x, double p, const double* __restrict__ tab)   // x >= 0 (no sign bit); tab stride TS
 {
     // exponent / table index / mantissa from the HIGH word with 32-bit integer operations (64-bit shifts cost three
     // instructions each); every clamp and the x = 0 case are integer compares — an FP64 compare occupies the FP64 pipe
     const int hi = __double2hiint(x), lo = __double2loint(x);
     const int e = (hi >> 20) - 1023;
-    const int j = (hi >> 13) & 127;
+    const int j = (hi >> 14) & (POW_LOGN - 1);
     const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, lo);
-    const double r = fma(m, tab[j], -1.0);
-    double q = fma(r, 0.28853900817779268, -0.36067376022224085);     // 1/(5 ln2), -1/(4 ln2)  (degree 5: the r^6 term is < 9e-16)
+    const double r = fma(m, tab[j * TS], -1.0);
+    double q = fma(r, 0.28853900817779268, -0.36067376022224085);     // 1/(5 ln2), -1/(4 ln2)  (degree 5: the r^6 term is < 6e-14)
     q = fma(r, q, 0.48089834696298783);                                //  1/(3 ln2)
     q = fma(r, q, -0.72134752044448170);                               // -1/(2 ln2)
     q = fma(r, q, 1.4426950408889634);                                 //  1/ln2
     // e as a double without an I2F conversion: 2^52 + 2^31 + e is exact in the low mantissa bits
+#if KRD_POW_I2F
+    const double ed = (double)e;                                       // I2F.F64.S32 on the conversion unit (A/B switch)
+#else
     const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;
-    const double L = fma(r, q, tab[128 + j]) + ed;
+#endif
+    const double L = fma(r, q, tab[(POW_LOGN + j) * TS]) + ed;
     const double t = p * L;
     const double MAGIC = 6755399441055744.0;                           // 1.5 * 2^52: rounds t*32 to an integer in the low bits
     double kd = fma(t, 32.0, MAGIC);
@@ -149,7 +163,7 @@ __device__ __forceinline__ double kr_pow(double x, double p, const double* __res
     // the scale 2^(k/32) is built in the exponent field: keep it a normal number (results beyond under/overflow anyway;
     // |32 t| < 2^31 is assumed, i.e. p < 6e4 at the smallest normal x)
     k = min(max(k, -1021 * 32), 1023 * 32);
-    const double s0 = tab[256 + (k & 31)];
+    const double s0 = tab[(2 * POW_LOGN + (k & (POW_EXPN - 1))) * TS];
     // x = 0 or subnormal -> exactly 0 (|F_i - F_j| is full of zeros): a MASK, not a select — a select on so common a
     // condition was compiled into a divergent branch
     const int keep = ~((hi - 0x00100000) >> 31);
@@ -208,7 +222,7 @@ __device__ __forceinline__ double kr_pow_n(double x)
     else return kr_pow_n<N - 1>(x) * x;
 }
 
-template <int MODE>
+template <int MODE, int TS = 1>
 __device__ __forceinline__ double pair_op(double a, double b, double l, double p, const double* __restrict__ tab, double acc)
 {
     if (MODE == MODE_P1) return fma(l, fabs(a - b), acc);
@@ -217,20 +231,20 @@ __device__ __forceinline__ double pair_op(double a, double b, double l, double p
     if (MODE == MODE_INT) return fma(l, kr_powi(fabs(a - b), (int)p), acc);
     if (MODE == MODE_P3) { const double d = fabs(a - b); return fma(l * d, d * d, acc); }
     if (MODE == MODE_P4) { const double d = a - b, d2 = d * d; return fma(l * d2, d2, acc); }
-    return fma(l, kr_pow(fabs(a - b), p, tab), acc);
+    return fma(l, kr_pow<TS>(fabs(a - b), p, tab), acc);
 }
 
 // Host: fill this translation unit's copy of the tables (cheap; done before every GENERIC launch).
 static inline cudaError_t make_pow_tables()
 {
     double tab[POW_TAB];
-    for (int j = 0; j < 128; ++j) {
-        const long double c = 1.0L + ((long double)j + 0.5L) / 128.0L;
+    for (int j = 0; j < POW_LOGN; ++j) {
+        const long double c = 1.0L + ((long double)j + 0.5L) / (long double)POW_LOGN;
         const double invc = (double)(1.0L / c);
         tab[j] = invc;
-        tab[128 + j] = (double)(-log2l((long double)invc));   // consistent with the ROUNDED 1/c
+        tab[POW_LOGN + j] = (double)(-log2l((long double)invc));   // consistent with the ROUNDED 1/c
     }
-    for (int i = 0; i < 32; ++i) tab[256 + i] = (double)exp2l((long double)i / 32.0L);
+    for (int i = 0; i < POW_EXPN; ++i) tab[2 * POW_LOGN + i] = (double)exp2l((long double)i / (long double)POW_EXPN);
     return cudaMemcpyToSymbol(g_pow_tab, tab, sizeof tab);
 }
 

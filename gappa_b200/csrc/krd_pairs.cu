@@ -207,7 +207,7 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
 #pragma unroll
             for (int r = 0; r < 8; ++r)
 #pragma unroll
-                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
+                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE, POW_TS_PAIR>(a[r], b[cc], l, p, tab, acc[r][cc]);
         }
     }
 }
@@ -244,7 +244,7 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
 #pragma unroll
             for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE>(a[r], b[cc], l, p, tab, acc[r][cc]);
+                for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = pair_op<MODE, POW_TS_PAIR>(a[r], b[cc], l, p, tab, acc[r][cc]);
         }
     }
 }
@@ -273,8 +273,8 @@ __device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa,
         for (int it = 0; it < 4; ++it) {
 #pragma unroll
             for (int cc = 0; cc < 8; ++cc) {
-                acc[0][cc] = pair_op<MODE>(a[0], b[cc], l, p, tab, acc[0][cc]);
-                acc[1][cc] = pair_op<MODE>(a[1], b[cc], l, p, tab, acc[1][cc]);
+                acc[0][cc] = pair_op<MODE, POW_TS_PAIR>(a[0], b[cc], l, p, tab, acc[0][cc]);
+                acc[1][cc] = pair_op<MODE, POW_TS_PAIR>(a[1], b[cc], l, p, tab, acc[1][cc]);
             }
             const double a0 = a[0], a1 = a[1];
 #pragma unroll
@@ -341,8 +341,10 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     // halved modes: the thread's idle half of the accumulators, [32][NT] (conflict-free: consecutive threads, consecutive words)
     double* spill = reinterpret_cast<double*>(smem_raw + (size_t)STM * STAGE_DOUBLES * sizeof(double) + 2 * STM * sizeof(uint64_t)) + threadIdx.x;
 
-    __shared__ double s_tab[MODE == MODE_GENERIC ? POW_TAB : 1];
-    if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB; k += NT) s_tab[k] = g_pow_tab[k];   // visible after the barrier below
+    // general p: the pow tables, every entry POW_TS_PAIR times (lane L reads copy L & 15: conflict-free for any index)
+    __shared__ double s_tab_all[MODE == MODE_GENERIC ? POW_TAB * POW_TS_PAIR : 1];
+    if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB * POW_TS_PAIR; k += NT) s_tab_all[k] = g_pow_tab[k / POW_TS_PAIR];   // visible after the barrier below
+    const double* const s_tab = s_tab_all + (MODE == MODE_GENERIC ? (threadIdx.x & (POW_TS_PAIR - 1)) : 0);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tx = lane & 15;

@@ -1,5 +1,6 @@
 // C ABI of libkrd_b200.so — see include/krd_b200.h.  No exception leaves this file.
 #include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <new>
 
@@ -22,6 +23,23 @@ krd_status cuda_fail(krd_handle* h, cudaError_t e, const char* what)
     return fail(h, KRD_ERR_CUDA, m);
 }
 
+// cudaMalloc of one of the large buffers with a message that says what did not fit (a bare "out of memory" is useless
+// to someone who ran a cohort the CPU path can hold); the CUDA error state is cleared.
+krd_status alloc_sized(krd_handle* h, void** p, size_t bytes, const char* what)
+{
+    const cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
+    if (e == cudaSuccess) return KRD_OK;
+    *p = nullptr;
+    cudaGetLastError();
+    size_t free_b = 0, total_b = 0;
+    cudaMemGetInfo(&free_b, &total_b);
+    cudaGetLastError();
+    char msg[320];
+    std::snprintf(msg, sizeof msg, "%s needs %.2f GB of device memory, %.2f GB of %.2f GB are free (%s)", what, bytes / 1e9,
+                  free_b / 1e9, total_b / 1e9, cudaGetErrorString(e));
+    return fail(h, KRD_ERR_CUDA, msg);
+}
+
 krd_status reserve(krd_handle* h, void** p, size_t bytes)
 {
     if (bytes == 0) bytes = 16;
@@ -33,6 +51,13 @@ krd_status reserve(krd_handle* h, void** p, size_t bytes)
     KRD_CUDA(h, cudaMalloc(p, bytes));
     h->caps[p] = bytes;
     return KRD_OK;
+}
+
+// A pipelined krd_set_masses may still be uploading blocks on the copy stream: before the state is dropped and the
+// buffers are written again (or the caller's arrays look free), wait for it.
+static void pipe_quiesce(krd_handle* h)
+{
+    if (h->piped && h->copy_stream) cudaStreamSynchronize(h->copy_stream);
 }
 
 static void free_masses(krd_handle* h)   // buffers are kept for reuse; only the state is dropped
@@ -122,6 +147,7 @@ krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_no
     h->parent.assign(parent_node, parent_node + n_edges);
     h->child.assign(child_node, child_node + n_edges);
     h->bl.assign(branch_length, branch_length + n_edges);
+    pipe_quiesce(h);
     h->have_tree = false; h->F_valid = false; h->have_masses = false; h->piped = false; ++h->tree_version;
     krd_status st = build_tree(h);
     if (st == KRD_OK) h->have_tree = true;
@@ -137,6 +163,7 @@ krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sampl
     const int64_t M = sample_off[n_samples];
     if (M > 0 && (!edge || !pos || !mass)) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
     KRD_CUDA(h, cudaSetDevice(h->device));
+    pipe_quiesce(h);
     free_masses(h);
     if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass);
     if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
@@ -165,6 +192,7 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
     krd_status st = set_masses_common(h, n_samples, sample_off);
     if (st != KRD_OK) return st;
     KRD_CUDA(h, cudaSetDevice(h->device));
+    pipe_quiesce(h);
     free_masses(h);
     if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = sample_off[n_samples];
@@ -184,8 +212,6 @@ static krd_status check_compute(krd_handle* h, double p, double divisor)
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     if (!(p > 0.0))  // also rejects NaN; genesis emd.cpp:186-190
         return fail(h, KRD_ERR_INVALID_EXPONENT, "Invalid exponent value p for earth mover's distance calculation. Has to be > 0.0.");
-    if (p > 30000.0)   // the general-p operator builds 2^(p log2 x) from the integer part of 32 p log2 x: |.| < 2^31 needs p < 6e4
-        return fail(h, KRD_ERR_INVALID_ARGUMENT, "exponents above 30000 are not supported");
     if (!h->have_tree || !h->have_masses) return fail(h, KRD_ERR_STATE, "krd_set_tree and krd_set_masses must be called first");
     if (divisor == 0.0 || divisor != divisor) return fail(h, KRD_ERR_INVALID_ARGUMENT, "divisor must be a non-zero number");
     return KRD_OK;
@@ -234,26 +260,13 @@ krd_status krd_compute(krd_handle* h, double p, double divisor, double* out)
     const size_t bytes = (size_t)h->N * h->N * 8;
     if (bytes > h->out_tmp_capacity) {
         cudaFree(h->d_out_tmp); h->d_out_tmp = nullptr; h->out_tmp_capacity = 0;
-        KRD_CUDA(h, cudaMalloc(&h->d_out_tmp, bytes));
+        if ((st = alloc_sized(h, (void**)&h->d_out_tmp, bytes, "the n x n distance matrix")) != KRD_OK) return st;
         h->out_tmp_capacity = bytes;
     }
     st = compute_impl(h, p, divisor, 0, 1, h->d_out_tmp, nullptr);
     if (st != KRD_OK) return st;
     KRD_CUDA(h, cudaMemcpyAsync(out, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
     KRD_CUDA(h, cudaStreamSynchronize(h->stream));
-    if (h->fix_pending) {   // Gram path: if the fix-up list overflowed, redo the matrix on the direct path
-        krd_stats tmp;
-        krd_get_stats(h, &tmp);
-        if (tmp.gram_fixups < 0) {
-            const int saved = h->cfg.p2_mode;
-            h->cfg.p2_mode = 1;
-            st = compute_impl(h, p, divisor, 0, 1, h->d_out_tmp, nullptr);
-            h->cfg.p2_mode = saved;
-            if (st != KRD_OK) return st;
-            KRD_CUDA(h, cudaMemcpyAsync(out, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
-            KRD_CUDA(h, cudaStreamSynchronize(h->stream));
-        }
-    }
     return KRD_OK;
 }
 
@@ -287,17 +300,10 @@ krd_status krd_compute_shard_host(krd_handle* h, double p, double divisor, int32
         KRD_CUDA(h, cudaMalloc(&h->d_out_tmp, bytes));
         h->out_tmp_capacity = bytes;
     }
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        st = compute_impl(h, p, divisor, rank, world, nullptr, h->d_out_tmp);
-        if (st != KRD_OK) return st;
-        KRD_CUDA(h, cudaMemcpyAsync(packed, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
-        KRD_CUDA(h, cudaStreamSynchronize(h->stream));
-        if (!h->fix_pending) break;
-        krd_stats tmp;
-        krd_get_stats(h, &tmp);
-        if (tmp.gram_fixups >= 0 || attempt == 1) break;
-        h->cfg.p2_mode = 1;      // fix-up list overflowed: this handle stays on the direct p = 2 path
-    }
+    st = compute_impl(h, p, divisor, rank, world, nullptr, h->d_out_tmp);
+    if (st != KRD_OK) return st;
+    KRD_CUDA(h, cudaMemcpyAsync(packed, h->d_out_tmp, bytes, cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
     return KRD_OK;
 }
 
@@ -340,13 +346,6 @@ krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
         cudaEventElapsedTime(&h->stats.ms_build, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&h->stats.ms_pairs, h->ev[1], h->ev[2]);
         cudaEventElapsedTime(&h->stats.ms_epilogue, h->ev[2], h->ev[3]);
-    }
-    if (h->fix_pending && h->d_fix) {   // synchronises with the handle's stream
-        int cnt = 0;
-        if (cudaMemcpyAsync(&cnt, h->d_fix, sizeof(int), cudaMemcpyDeviceToHost, h->stream) == cudaSuccess &&
-            cudaStreamSynchronize(h->stream) == cudaSuccess)
-            h->stats.gram_fixups = (cnt > (1 << 20)) ? -1 : cnt;
-        h->fix_pending = false;
     }
     cudaGetLastError();
     *out = h->stats;

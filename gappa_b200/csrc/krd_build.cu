@@ -251,25 +251,29 @@ __global__ void k_exact_slots(const int32_t* __restrict__ edge, const uint32_t* 
 // Segment t of edge e (k_e distinct positions b_1<..<b_k): t<k: (b_t, b_{t+1}] (b_0 = 0); t=k: (b_k, bl].
 // Lengths are the same differences genesis forms while walking (emd.cpp:154-166).
 __global__ void k_exact_len_unique(const double* __restrict__ upos, const uint32_t* __restrict__ uedge,
-                                   const uint32_t* __restrict__ ubase, int64_t U, double* __restrict__ len)
+                                   const uint32_t* __restrict__ ubase, int64_t U, double* __restrict__ len, int* __restrict__ neg)
 {
     int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= U) return;
     uint32_t e = uedge[u], r = (uint32_t)u - ubase[e];
     double lo = (r > 0) ? upos[u - 1] : 0.0;
-    len[(int64_t)ubase[e] + e + r] = upos[u] - lo;
+    const double l = upos[u] - lo;
+    len[(int64_t)ubase[e] + e + r] = l;
+    if (l < 0.0) *neg = 1;     // a position below 0: the reference keeps the signed length (emd.cpp:156)
 }
 
 __global__ void k_exact_len_last(const double* __restrict__ upos, const uint32_t* __restrict__ ubase,
                                  const double* __restrict__ bl, int E, double* __restrict__ len,
-                                 int32_t* __restrict__ seg_off)
+                                 int32_t* __restrict__ seg_off, int* __restrict__ neg)
 {
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e > E) return;
     seg_off[e] = (int32_t)(ubase[e] + e);
     if (e == E) return;
     uint32_t k = ubase[e + 1] - ubase[e];
-    len[(int64_t)ubase[e] + e + k] = (k > 0) ? bl[e] - upos[ubase[e] + k - 1] : bl[e];
+    const double l = (k > 0) ? bl[e] - upos[ubase[e] + k - 1] : bl[e];
+    len[(int64_t)ubase[e] + e + k] = l;
+    if (l < 0.0) *neg = 1;     // a position beyond the branch (or a negative branch length): emd.cpp:166 keeps the sign
 }
 
 __global__ void k_sqrt(const double* __restrict__ a, int64_t n, double* __restrict__ b)
@@ -370,7 +374,7 @@ krd_status prepare_masses(krd_handle* h)
     { krd_status rs = reserve(h, &h->d_flags, 16); if (rs != KRD_OK) return rs; }
     int* const d_flags = static_cast<int*>(h->d_flags);
     { krd_status rs = reserve(h, (void**)&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
-    zero_words(d_flags, 1, 1, 1, h->stream);   // (16 bytes reserved)
+    zero_words(d_flags, 2, 2, 1, h->stream);   // (16 bytes reserved: int [0] order / range check, int [1] negative segment length)
     if (M > 0) {
         k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
         if (h->defer_check) k_clamp_edges<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, M, E, d_flags);
@@ -417,9 +421,11 @@ krd_status prepare_masses(krd_handle* h)
         return KRD_OK;
     };
 
+    h->len_negative = false;
     if (h->cfg.bins > 0) {
         const int B = h->cfg.bins;
         if ((int64_t)E * (B + 1) > 0x7FFFFFF0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "too many segments");
+        for (double b : h->bl) if (b < 0.0) h->len_negative = true;
         krd_status st = alloc_len((int64_t)E * (B + 1));
         if (st != KRD_OK) return st;
         double nb = (double)B;
@@ -457,10 +463,13 @@ krd_status prepare_masses(krd_handle* h)
         if (st != KRD_OK) return st;
         if (M > 0) {
             k_exact_slots<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, uidx.as<uint32_t>(), ubase.as<uint32_t>(), M, h->d_slot);
-            k_exact_len_unique<<<nblk(U), 256, 0, h->stream>>>(upos.as<double>(), uedge.as<uint32_t>(), ubase.as<uint32_t>(), U, h->d_len);
+            k_exact_len_unique<<<nblk(U), 256, 0, h->stream>>>(upos.as<double>(), uedge.as<uint32_t>(), ubase.as<uint32_t>(), U, h->d_len, d_flags + 1);
         }
-        k_exact_len_last<<<nblk(E + 1), 256, 0, h->stream>>>(upos.as<double>(), ubase.as<uint32_t>(), h->d_bl, E, h->d_len, h->d_seg_off);
+        k_exact_len_last<<<nblk(E + 1), 256, 0, h->stream>>>(upos.as<double>(), ubase.as<uint32_t>(), h->d_bl, E, h->d_len, h->d_seg_off, d_flags + 1);
+        int neg = 0;
+        KRD_CUDA(h, cudaMemcpyAsync(&neg, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
         KRD_CUDA(h, cudaStreamSynchronize(h->stream));  // scratch buffers die here
+        h->len_negative = neg != 0;
     }
     k_sqrt<<<nblk(h->S_pad), 256, 0, h->stream>>>(h->d_len, h->S_pad, h->d_sqrt_len);
     KRD_CUDA(h, cudaGetLastError());
@@ -810,7 +819,8 @@ krd_status build_F(krd_handle* h)
         if (!h->d_F || !h->tiled) return fail(h, KRD_ERR_STATE, "pipelined child without a tiled builder");
     } else if (need > h->F_capacity) {
         cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
-        KRD_CUDA(h, cudaMalloc(&h->d_F, need));
+        krd_status sa = alloc_sized(h, (void**)&h->d_F, need, "the dense cumulative-mass matrix F (segments x samples x 8 B)");
+        if (sa != KRD_OK) return sa;
         h->F_capacity = need;
     }
     if (h->tiled) {

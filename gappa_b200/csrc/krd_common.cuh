@@ -25,6 +25,8 @@ enum PairMode : int {
     MODE_INT = 5,     // p = 5..16   : |a-b|^p by repeated multiplication
     MODE_P3 = 6,      // p == 3      : acc += len * |d| * d^2
     MODE_P4 = 7,      // p == 4      : acc += len * (d^2)^2
+    MODE_LIBPOW = 8,
+    MODE_P2S = 9,     // p == 2      : acc += len * (a-b)^2 without the sqrt(len) pre-scaling (some len < 0: emd.cpp:156,166 keep the sign)  // p > 30000  : acc += len * pow(|a-b|, p) with the library pow (outside kr_pow's exponent range)
     MODE_P2G = 4      // p == 2      : Gram form on the FP64 tensor cores (DMMA): acc += len * (a-c)(b-c),
                       //               W = |a-c|^2 + |b-c|^2 - 2 acc   (c = a reference column, cancels exactly in a-b)
 };
@@ -76,6 +78,7 @@ struct krd_handle {
     int32_t* d_seg_off = nullptr;  // E+1
     double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
     double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
+    bool     len_negative = false; // exact mode: a mass position outside its branch made a segment length negative
     double*  d_center = nullptr;   // S_pad: the reference column the Gram path subtracts (F[.][0])
     double*  d_norm = nullptr;     // ld: sum_s len (F[s][i] - center[s])^2
     double*  d_norm_part = nullptr;
@@ -163,6 +166,8 @@ inline cudaError_t allow_dynamic_smem(Kernel kernel, int bytes, std::atomic<unsi
     if (e == cudaSuccess && dev < 64) done_mask.fetch_or(1ull << dev, std::memory_order_release);
     return e;
 }
+
+krd_status alloc_sized(krd_handle* h, void** p, size_t bytes, const char* what);   // cudaMalloc with a sized error message
 
 // grow-only device buffer: reallocates *p only when `bytes` exceeds its recorded capacity
 krd_status reserve(krd_handle* h, void** p, size_t bytes);

@@ -160,13 +160,15 @@ __device__ __forceinline__ double kr_pow(double x, double p, const double* __res
     double w = fma(g, 9.6181291076284772e-3, 5.5504108664821580e-2);   // ln2^4/24, ln2^3/6  (degree 4: truncation 1.25e-12 relative, the bar is 1e-10)
     w = fma(g, w, 2.4022650695910071e-1);                              // ln2^2/2
     w = fma(g, w, 6.9314718055994531e-1);                              // ln2
-    // the scale 2^(k/32) is built in the exponent field: keep it a normal number (results beyond under/overflow anyway;
-    // |32 t| < 2^31 is assumed, i.e. p < 6e4 at the smallest normal x)
+    // the scale 2^(k/32) is built in the exponent field: keep it a normal number.  |32 t| < 2^31 is assumed, i.e.
+    // p <= POW_MAX_P at the smallest normal x (larger exponents run the library-pow body, MODE_LIBPOW).  A result below
+    // the normal range is flushed to exactly 0 (std::pow would return a subnormal or 0; at most 2^-1022 per operator).
+    const int under = (k + 1022 * 32) >> 31;                           // all ones when 2^(k/32) < 2^-1022
     k = min(max(k, -1021 * 32), 1023 * 32);
     const double s0 = tab[(2 * POW_LOGN + (k & (POW_EXPN - 1))) * TS];
     // x = 0 or subnormal -> exactly 0 (|F_i - F_j| is full of zeros): a MASK, not a select — a select on so common a
     // condition was compiled into a divergent branch
-    const int keep = ~((hi - 0x00100000) >> 31);
+    const int keep = ~(((hi - 0x00100000) >> 31) | under);
     const double sc = __hiloint2double((__double2hiint(s0) + ((k >> 5) << 20)) & keep, __double2loint(s0) & keep);
     return fma(sc, g * w, sc);
 }
@@ -175,42 +177,6 @@ __device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uni
     double r = (n & 1) ? x : 1.0, base = x;
     while (n >>= 1) { base *= base; if (n & 1) r *= base; }
     return r;
-}
-
-// One row of the register tile for integer p = 5 .. 16 (square-and-multiply), stage by stage over the NC columns; the
-// branches on the bits of p are warp-uniform.
-template <int NC>
-__device__ __forceinline__ void kr_row_powi(double a, const double* __restrict__ b, double l, int n, double* __restrict__ acc)
-{
-    // n = 5 .. 16: x^4 is always needed; result = x^4 [* x^8 or x^16 instead] * (x^2 if bit 1) * (x if bit 0)
-    double x1[NC], x2[NC], res[NC];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) x1[c] = fabs(a - b[c]);
-#pragma unroll
-    for (int c = 0; c < NC; ++c) x2[c] = x1[c] * x1[c];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) res[c] = x2[c] * x2[c];                       // x^4
-    if (n >= 8) {                                                               // warp-uniform branches
-#pragma unroll
-        for (int c = 0; c < NC; ++c) res[c] *= res[c];                          // x^8
-        if (n >= 16) {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) res[c] *= res[c];                      // x^16
-        } else if (n & 4) {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) res[c] *= x2[c] * x2[c];               // x^12
-        }
-    }
-    if (n & 2) {
-#pragma unroll
-        for (int c = 0; c < NC; ++c) res[c] *= x2[c];
-    }
-    if (n & 1) {
-#pragma unroll
-        for (int c = 0; c < NC; ++c) res[c] *= x1[c];
-    }
-#pragma unroll
-    for (int c = 0; c < NC; ++c) acc[c] = fma(l, res[c], acc[c]);
 }
 
 // x^N with the multiplication chain fixed at compile time (N = 7: x2, x3, x6, x7)
@@ -227,10 +193,12 @@ __device__ __forceinline__ double pair_op(double a, double b, double l, double p
 {
     if (MODE == MODE_P1) return fma(l, fabs(a - b), acc);
     if (MODE == MODE_P2) { double d = a - b; return fma(d, d, acc); }   // operands pre-scaled by sqrt(len)
+    if (MODE == MODE_P2S) { const double d = a - b; return fma(l * d, d, acc); }   // signed len (exact mode, pos outside the branch)
     if (MODE == MODE_PHALF) return fma(l, kr_sqrt_abs(a - b), acc);
     if (MODE == MODE_INT) return fma(l, kr_powi(fabs(a - b), (int)p), acc);
     if (MODE == MODE_P3) { const double d = fabs(a - b); return fma(l * d, d * d, acc); }
     if (MODE == MODE_P4) { const double d = a - b, d2 = d * d; return fma(l * d2, d2, acc); }
+    if (MODE == MODE_LIBPOW) return fma(l, pow(fabs(a - b), p), acc);   // exponents beyond kr_pow's range: slow, but any p > 0
     return fma(l, kr_pow<TS>(fabs(a - b), p, tab), acc);
 }
 
@@ -249,10 +217,13 @@ static inline cudaError_t make_pow_tables()
 }
 
 
+constexpr double POW_MAX_P = 30000.0;   // kr_pow builds 2^(p log2 x) from the integer part of 32 p log2 x: |.| < 2^31 needs p < 6e4
+
 static inline int mode_for_exponent(double p, bool gram_for_p2)
 {
+    if (p > POW_MAX_P) return MODE_LIBPOW;
     if (p == 1.0) return MODE_P1;
-    if (p == 2.0) return gram_for_p2 ? MODE_P2G : MODE_P2;
+    if (p == 2.0) return gram_for_p2 ? MODE_P2G : MODE_P2;   // (MODE_P2S instead of MODE_P2 when a segment length is negative)
     if (p == 0.5) return MODE_PHALF;
     if (p == 3.0) return MODE_P3;
     if (p == 4.0) return MODE_P4;

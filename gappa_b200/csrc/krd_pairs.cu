@@ -35,13 +35,7 @@ constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * 
 // accumulators resident the compiler has ~45 doubles left for the operators' temporaries, interleaves 4-5 dependency
 // chains and the FP64 latency shows (computing only four rows ran 1.41x faster per operator, profiles/r1o_long_ops.txt).
 // These modes need a fraction of the operand bandwidth, so the ring shrinks to 4 stages and leaves room for the spill.
-#ifndef KRD_HALVE_INT
-#define KRD_HALVE_INT 0
-#endif
-#ifndef KRD_HALVED
-#define KRD_HALVED 1
-#endif
-constexpr bool mode_is_halved(int mode) { return KRD_HALVED && (mode == MODE_PHALF || (KRD_HALVE_INT && mode == MODE_INT) || mode == MODE_GENERIC); }
+constexpr bool mode_is_halved(int mode) { return mode == MODE_PHALF || mode == MODE_GENERIC || mode == MODE_LIBPOW; }
 constexpr int stages_for(int mode) { return mode_is_halved(mode) ? 4 : ST; }
 constexpr size_t SPILL_BYTES = (size_t)32 * NT * sizeof(double);
 constexpr size_t smem_bytes_for(int mode)
@@ -102,9 +96,13 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
 
 // ---- inner operators ----------------------------------------------------------------------------
 
-// per-CTA (start, end, first item, last item) of the last pair launch in %globaltimer ns — tuning aid, read by krd_debug_cta_times
+// Tuning aid, compiled in only with -DKRD_TIMING (make EXTRA=-DKRD_TIMING ..., profiles/cta_balance.py): per-CTA
+// (start, end, first item, last item) and per-item (start, end) of the last pair launch in %globaltimer ns.
+#ifdef KRD_TIMING
 __device__ unsigned long long g_cta_time[4 * 1024];
-__device__ unsigned long long g_item_time[2 * 4096];   // (start, end) per work item as seen by warp 0 — tuning aid
+__device__ unsigned long long g_item_time[2 * 4096];
+#define KRD_STAMP(dst) do { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); (dst) = t_; } while (0)
+#endif
 
 // One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
 // (diagonal tiles: blocks that lie entirely below the diagonal).
@@ -116,15 +114,12 @@ __device__ unsigned long long g_item_time[2 * 4096];   // (start, end) per work 
 #endif
 // unroll factor of the segment loop: the short operators (p = 1, 2) are unrolled 4x; the long ones keep ONE segment
 // (64 independent operators, fixed accumulator registers) as the loop body so that it stays inside the instruction cache
-constexpr int mode_unroll(int mode) { return (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC) ? 1 : (mode == MODE_P3 || mode == MODE_P4) ? KRD_P34_UNROLL : KRD_P12_UNROLL; }
+constexpr int mode_unroll(int mode) { return (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC || mode == MODE_LIBPOW) ? 1 : (mode == MODE_P3 || mode == MODE_P4) ? KRD_P34_UNROLL : KRD_P12_UNROLL; }
 
 // Integer exponents 5..16 with the exponent as a template parameter: one segment = 64 independent, fully static operator
 // chains that the compiler interleaves freely (the run-time ladder kr_row_powi had to stop at every warp-uniform branch:
 // p = 5 ran at 64 % of its FP64 issue bound, p = 3 with a static body at 90 %).  Only the body of the exponent in use
 // (and its diagonal-tile variants) is hot, so the instruction cache sees one ~7 KB loop, not twelve.
-#ifndef KRD_INT_STATIC
-#define KRD_INT_STATIC 1
-#endif
 template <int QMIN, int N>
 __device__ __forceinline__ void chunk_math_int(const double* __restrict__ pa, const double* __restrict__ pb,
                                             const double* __restrict__ sL, double (&acc)[8][8])
@@ -155,7 +150,7 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
                                            const double* __restrict__ sL, double p, const double* __restrict__ tab,
                                            double (&acc)[8][8])
 {
-    if (MODE == MODE_INT && KRD_INT_STATIC) {
+    if (MODE == MODE_INT) {
         switch ((int)p) {   // warp-uniform
             case 5: chunk_math_int<QMIN, 5>(pa, pb, sL, acc); return;
             case 6: chunk_math_int<QMIN, 6>(pa, pb, sL, acc); return;
@@ -169,7 +164,7 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
             case 14: chunk_math_int<QMIN, 14>(pa, pb, sL, acc); return;
             case 15: chunk_math_int<QMIN, 15>(pa, pb, sL, acc); return;
             case 16: chunk_math_int<QMIN, 16>(pa, pb, sL, acc); return;
-            default: break;   // (mode_for_exponent sends nothing else here)
+            default: return;   // (mode_for_exponent sends nothing else here)
         }
     }
 #pragma unroll (mode_unroll(MODE))
@@ -194,15 +189,7 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
         }
         if (MODE == MODE_PHALF) {
 #pragma unroll
-#ifdef KRD_EXPERIMENT_HALFROWS   // register-pressure experiment only (computes half the rows: results are wrong)
-            for (int r = 0; r < 4; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
-#else
             for (int r = 0; r < 8; ++r) kr_row_sqrt<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
-#endif
-        } else if (MODE == MODE_INT) {
-            const int n = (int)p;
-#pragma unroll
-            for (int r = 0; r < 8; ++r) kr_row_powi<8 - 2 * QMIN>(a[r], b + 2 * QMIN, l, n, &acc[r][2 * QMIN]);
         } else {
 #pragma unroll
             for (int r = 0; r < 8; ++r)
@@ -236,10 +223,6 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
         if (MODE == MODE_PHALF) {
 #pragma unroll
             for (int r = 0; r < 4; ++r) kr_row_sqrt<NC>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
-        } else if (MODE == MODE_INT) {
-            const int n = (int)p;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) kr_row_powi<NC>(a[r], b + 2 * QMIN, l, n, &acc[r][2 * QMIN]);
         } else {
 #pragma unroll
             for (int r = 0; r < 4; ++r)
@@ -248,53 +231,6 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
         }
     }
 }
-
-// Exponents whose inner operator is long (sqrt: ~12, pow: ~40 instructions per pair and segment): a fully
-// unrolled 8x8 body would be tens of thousands of instructions and thrash the instruction cache.  The
-// body is therefore two rows (16 independent operators = enough ILP for the FP64 pipe) in a rolled loop,
-// and the accumulator rows ROTATE through the registers (register files cannot be indexed dynamically).
-template <int MODE>
-__device__ __forceinline__ void chunk_math_rolled(const double* __restrict__ pa, const double* __restrict__ pb,
-                                                  const double* __restrict__ sL, double p, const double* __restrict__ tab,
-                                                  double (&acc)[8][8])
-{
-#pragma unroll 1
-    for (int kk = 0; kk < KC; ++kk) {
-        double a[8], b[8];
-        const double l = sL[kk];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
-            a[2 * q] = va.x; a[2 * q + 1] = va.y;
-            const double2 vb = *reinterpret_cast<const double2*>(pb + kk * TILE + 32 * q);
-            b[2 * q] = vb.x; b[2 * q + 1] = vb.y;
-        }
-#pragma unroll 1
-        for (int it = 0; it < 4; ++it) {
-#pragma unroll
-            for (int cc = 0; cc < 8; ++cc) {
-                acc[0][cc] = pair_op<MODE, POW_TS_PAIR>(a[0], b[cc], l, p, tab, acc[0][cc]);
-                acc[1][cc] = pair_op<MODE, POW_TS_PAIR>(a[1], b[cc], l, p, tab, acc[1][cc]);
-            }
-            const double a0 = a[0], a1 = a[1];
-#pragma unroll
-            for (int r = 0; r < 6; ++r) a[r] = a[r + 2];
-            a[6] = a0; a[7] = a1;
-#pragma unroll
-            for (int cc = 0; cc < 8; ++cc) {
-                const double t0 = acc[0][cc], t1 = acc[1][cc];
-#pragma unroll
-                for (int r = 0; r < 6; ++r) acc[r][cc] = acc[r + 2][cc];
-                acc[6][cc] = t0; acc[7][cc] = t1;
-            }
-        }
-    }
-}
-
-#ifndef KRD_ROTATING_BODY
-#define KRD_ROTATING_BODY 0     // 1: the two-row rotating body also for p = 1/2 (A/B measurements)
-#endif
-constexpr bool mode_is_rolled(int mode) { return !mode_is_halved(mode) && ((KRD_ROTATING_BODY && (mode == MODE_PHALF || mode == MODE_INT)) || mode == MODE_GENERIC); }
 
 // ---- Gram form on the FP64 tensor cores (p = 2) ---------------------------------------------------
 // Warp tile 32 x 64 of the 128 x 128 CTA tile = 4 x 8 DMMA m8n8k4 accumulators (64 doubles per
@@ -355,10 +291,9 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
 
     const int it0 = P.cta_item_off[blockIdx.x], it1 = P.cta_item_off[blockIdx.x + 1];
     if (it0 == it1) return;
-    if (threadIdx.x == 0 && blockIdx.x < 1024) {
-        unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-        g_cta_time[4 * blockIdx.x] = t; g_cta_time[4 * blockIdx.x + 2] = it0; g_cta_time[4 * blockIdx.x + 3] = it1;
-    }
+#ifdef KRD_TIMING
+    if (threadIdx.x == 0 && blockIdx.x < 1024) { KRD_STAMP(g_cta_time[4 * blockIdx.x]); g_cta_time[4 * blockIdx.x + 2] = it0; g_cta_time[4 * blockIdx.x + 3] = it1; }
+#endif
 
     if (tid == 0) {
         for (int s = 0; s < STM; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NT / 32); }
@@ -406,8 +341,10 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && !mode_is_rolled(MODE)) ? (rg >> 1) : 0;
-        if (threadIdx.x == 0 && item < 4096) { unsigned long long tt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tt)); g_item_time[2 * item] = tt; }
+        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (rg >> 1) : 0;
+#ifdef KRD_TIMING
+        if (threadIdx.x == 0 && item < 4096) KRD_STAMP(g_item_time[2 * item]);
+#endif
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -438,7 +375,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                             for (int cc = 0; cc < 8; ++cc) { const double t = spill[(r * 8 + cc) * NT]; spill[(r * 8 + cc) * NT] = h4[r][cc]; h4[r][cc] = t; }
                         act ^= 1;
                     }
-                    if (MODE == MODE_GENERIC) { chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); continue; }   // one code variant
+                    if (MODE == MODE_GENERIC || MODE == MODE_LIBPOW) { chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); continue; }   // one code variant
                     switch (qmin) {
                         case 0: chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); break;
                         case 1: chunk_math_rows4<MODE, 1>(pa, pb, sL, P.p, s_tab, act, h4); break;
@@ -448,8 +385,6 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                 }
             } else if (MODE == MODE_P2G) {
                 chunk_gram(sA, sB, sL, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
-            } else if (mode_is_rolled(MODE)) {
-                chunk_math_rolled<MODE>(pa, pb, sL, P.p, s_tab, acc);
             } else {
                 switch (qmin) {
                     case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, s_tab, acc); break;
@@ -462,7 +397,9 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             if (lane == 0) mbar_arrive(&empty[s]);
         }
 
-        if (threadIdx.x == 0 && item < 4096) { unsigned long long tt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tt)); g_item_time[2 * item + 1] = tt; }
+#ifdef KRD_TIMING
+        if (threadIdx.x == 0 && item < 4096) KRD_STAMP(g_item_time[2 * item + 1]);
+#endif
         // partial tile -> workspace; row = row0 + r, col = 32*q + 2*tx + {0,1}
         double* wout = P.ws + (size_t)item * (size_t)(TILE * TILE);
         if (MODE == MODE_P2G) {
@@ -493,11 +430,10 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             for (int q = 0; q < 4; ++q)
                 *reinterpret_cast<double2*>(wout + (row0 + r) * TILE + 32 * q + 2 * tx) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
     }
+#ifdef KRD_TIMING
     __syncthreads();
-    if (threadIdx.x == 0 && blockIdx.x < 1024) {
-        unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-        g_cta_time[4 * blockIdx.x + 1] = t;
-    }
+    if (threadIdx.x == 0 && blockIdx.x < 1024) KRD_STAMP(g_cta_time[4 * blockIdx.x + 1]);
+#endif
 }
 
 // ---- epilogue: sum a tile's partials in fixed order, outer root, divisor, mirror ------------------
@@ -745,8 +681,8 @@ static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stre
     return cudaGetLastError();
 }
 
-krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
-                     double* d_out_matrix, double* d_out_packed)
+static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int rank, int world,
+                                 double* d_out_matrix, double* d_out_packed, bool allow_gram)
 {
     krd_status st = ensure_tiles(h);
     if (st != KRD_OK) return st;
@@ -761,8 +697,9 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     h->stats.pair_ctas = 0;
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
 
-    const int mode = mode_for_exponent(p, h->cfg.p2_mode != 1);   // p = 2: auto = Gram on the tensor cores + direct fix-ups
-    const bool full_diag = (mode == MODE_P2G) || mode == MODE_GENERIC || mode_is_rolled(mode);   // these modes do not skip the lower blocks of diagonal tiles
+    int mode = mode_for_exponent(p, allow_gram && h->cfg.p2_mode != 1 && !h->len_negative);   // p = 2: auto = Gram on the tensor cores + direct fix-ups
+    if (mode == MODE_P2 && h->len_negative) mode = MODE_P2S;          // sqrt(len) pre-scaling needs len >= 0
+    const bool full_diag = (mode == MODE_P2G) || mode == MODE_GENERIC || mode == MODE_LIBPOW;   // these modes do not skip the lower blocks of diagonal tiles
     // cost of a diagonal-tile chunk relative to a full one: 5/8 of the math, but the warps of a diagonal tile carry unequal
     // shares (the top row groups skip nothing).  p = 1, 2 are FP64-pipe-bound, so the lighter warps free the pipe for the
     // others (measured 0.705); the long operators are bound by each warp's own dependency chains, so the tile takes almost
@@ -821,11 +758,13 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     switch (mode) {
         case MODE_P1: e = launch_pairs<MODE_P1>(P, G, h->stream); break;
         case MODE_P2: e = launch_pairs<MODE_P2>(P, G, h->stream); break;
+        case MODE_P2S: e = launch_pairs<MODE_P2S>(P, G, h->stream); break;
         case MODE_PHALF: e = launch_pairs<MODE_PHALF>(P, G, h->stream); break;
         case MODE_P2G: e = launch_pairs<MODE_P2G>(P, G, h->stream); break;
         case MODE_INT: e = launch_pairs<MODE_INT>(P, G, h->stream); break;
         case MODE_P3: e = launch_pairs<MODE_P3>(P, G, h->stream); break;
         case MODE_P4: e = launch_pairs<MODE_P4>(P, G, h->stream); break;
+        case MODE_LIBPOW: e = launch_pairs<MODE_LIBPOW>(P, G, h->stream); break;
         default:
             e = make_pow_tables();
             if (e == cudaSuccess) e = launch_pairs<MODE_GENERIC>(P, G, h->stream);
@@ -858,6 +797,22 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     h->stats.pair_ctas = G;
     h->stats.launches += 2;
     return KRD_OK;
+}
+
+// The Gram path's epilogue lists the cells whose subtraction cancelled; when that list overflows (more than FIX_CAP
+// near-duplicate pairs) the launch is repeated on the direct FP64-core path — here, so that EVERY entry point (host,
+// device, sharded, squash) returns cells inside the tolerance.  Costs one 4-byte read-back per p = 2 Gram launch.
+krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world, double* d_out_matrix, double* d_out_packed)
+{
+    krd_status st = run_pairs_once(h, p, divisor, rank, world, d_out_matrix, d_out_packed, true);
+    if (st != KRD_OK || !h->fix_pending) return st;
+    h->fix_pending = false;
+    int cnt = 0;
+    KRD_CUDA(h, cudaMemcpyAsync(&cnt, h->d_fix, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KRD_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->stats.gram_fixups = (cnt > FIX_CAP) ? -1 : cnt;
+    if (cnt <= FIX_CAP) return KRD_OK;
+    return run_pairs_once(h, p, divisor, rank, world, d_out_matrix, d_out_packed, false);
 }
 
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out)
@@ -903,7 +858,8 @@ krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j)
     return KRD_OK;
 }
 
-/* tuning aid (not part of the product surface): per-CTA start/end (ns) and item range of the last pair launch */
+#ifdef KRD_TIMING
+/* tuning aid (variant builds only, not part of the product surface): per-CTA start/end (ns) and item range of the last pair launch */
 int krd_debug_item_times(unsigned long long* out, int n_items)
 {
     return (int)cudaMemcpyFromSymbol(out, krd::g_item_time, sizeof(unsigned long long) * 2 * (size_t)std::min(n_items, 4096));
@@ -913,6 +869,7 @@ int krd_debug_cta_times(unsigned long long* out, int n_ctas)
 {
     return (int)cudaMemcpyFromSymbol(out, krd::g_cta_time, sizeof(unsigned long long) * 4 * (size_t)std::min(n_ctas, 1024));
 }
+#endif
 
 void krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1)
 {

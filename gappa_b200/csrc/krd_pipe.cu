@@ -113,7 +113,7 @@ krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const i
     const size_t needF = (size_t)h->S_pad * h->ld * sizeof(double);
     if (needF > h->F_capacity) {
         cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
-        KRD_CUDA(h, cudaMalloc(&h->d_F, needF));
+        if ((st = alloc_sized(h, (void**)&h->d_F, needF, "the dense cumulative-mass matrix F (segments x samples x 8 B)")) != KRD_OK) return st;
         h->F_capacity = needF;
     }
     if (h->ld > T * TILE)   // reserved columns after the samples (nothing writes them here)

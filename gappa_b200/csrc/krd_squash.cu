@@ -199,6 +199,7 @@ krd_status run_squash(krd_handle* h, double p, krd_merger* out)
             case MODE_P3: launch_ova<MODE_P3>(h, c, p, rpc, part); break;
             case MODE_P4: launch_ova<MODE_P4>(h, c, p, rpc, part); break;
             case MODE_INT: launch_ova<MODE_INT>(h, c, p, rpc, part); break;
+            case MODE_LIBPOW: launch_ova<MODE_LIBPOW>(h, c, p, rpc, part); break;
             default: launch_ova<MODE_GENERIC>(h, c, p, rpc, part); break;
         }
         k_sq_ova_final<<<(unsigned)((c + 255) / 256), 256, 0, h->stream>>>(part, h->ld, c, Nt, p, active, pair, D, mergers + m);

@@ -327,22 +327,123 @@ def test_sharded_compute_equals_single(gb, world):
     plan.close()
 
 
-@pytest.mark.gpu
-def test_absurd_exponent_is_rejected_not_garbled():
-    """The general-p operator needs 32 p log2(x) inside 31 bits; beyond p = 30000 the call fails loudly."""
-    import gappa_b200
+def test_exponents_beyond_the_table_operator_use_library_pow(gb, oracle_mod):
+    """The reference accepts ANY p > 0 (emd.cpp:186-190).  The table-driven general-p operator covers p <= 30000; beyond
+    that the pair kernel runs a library-pow body (slow, correct).  Large legal exponents stay inside the tolerance."""
     from gappa_b200 import synth
     tree = synth.tree_with_edges(99, seed=3)
     masses = synth.sample_masses(tree, 12, 50, seed=3)
-    plan = gappa_b200.KrdPlan(bins=0)
+    plan = gb.KrdPlan(bins=0)
     plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
     plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
-    with pytest.raises(gappa_b200.KrdError, match="30000"):
-        plan.compute(p=1e5)
-    import oracle
-    for p in (250.5, 37.25):             # large but legal
+    for p in (250.5, 37.25, 1e5, 3.5e6):
         got = plan.compute(p=p)
-        want = oracle.port_matrix(tree, masses, p=p, bins=0)
+        want = oracle_mod.port_matrix(tree, masses, p=p, bins=0)
         assert np.all(np.isfinite(got))
         assert rel_err(got, want) <= 1e-10, p
     plan.close()
+
+
+def test_underflowing_terms_are_flushed_to_zero(gb, oracle_mod):
+    """Near-duplicate samples and a large general exponent: every |d|^p underflows, the reference returns 0 (or a
+    denormal-sized value); the table operator must not return its clamped minimum 2^-1021 per term."""
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(51, seed=13)
+    base = synth.sample_masses(tree, 3, 120, seed=13)
+    off, edge, pos, mass = [0], [], [], []
+    rng = np.random.default_rng(13)
+    for i in range(3):
+        lo, hi = base["off"][i], base["off"][i + 1]
+        for rep in range(4):                       # copies jittered by 1e-6: |F_i - F_j| ~ 1e-6, ^250 underflows
+            m = base["mass"][lo:hi] * (1.0 + 1e-6 * rng.standard_normal(hi - lo) * (rep > 0))
+            edge.append(base["edge"][lo:hi]); pos.append(base["pos"][lo:hi]); mass.append(m / m.sum())
+            off.append(off[-1] + hi - lo)
+    masses = dict(off=np.array(off, np.int64), edge=np.concatenate(edge), pos=np.concatenate(pos), mass=np.concatenate(mass))
+    for p in (250.5, 120.25):
+        got = gb.earth_movers_distance(tree, masses, p=p)
+        want = oracle_mod.port_matrix(tree, masses, p=p)
+        within = np.zeros((12, 12), bool)
+        for g in range(3):
+            within[4 * g:4 * g + 4, 4 * g:4 * g + 4] = True
+        np.fill_diagonal(within, False)
+        assert np.all(want[within] == 0.0)                       # every term underflows in the reference's std::pow
+        assert np.all(got[within] == 0.0), (p, got[within].max())
+        assert rel_err(got[~within], want[~within]) <= 1e-10, p
+
+
+@pytest.mark.parametrize("p2_mode", [1, 2])
+def test_positions_outside_the_branch_keep_signed_lengths(gb, oracle_mod, p2_mode):
+    """Exact mode: a jplace distal/proximal length outside the branch gives pos < 0 or pos > bl and the reference keeps the
+    signed segment length (emd.cpp:156,166).  The direct p = 2 path must not scale by sqrt(len) then (NaN for every pair)."""
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(41, seed=8)
+    mass = synth.sample_masses(tree, 20, 40, seed=8)
+    pos = mass["pos"].copy()
+    bl = tree["bl"][mass["edge"]]
+    pos[5] = bl[5] * 1.25            # beyond the branch
+    pos[77] = bl[77] * 1.5
+    m2 = dict(off=mass["off"], edge=mass["edge"], pos=pos, mass=mass["mass"])
+    m2 = oracle_mod.canonicalize(m2)
+    want1 = oracle_mod.port_matrix(tree, m2, p=1.0)
+    want2 = oracle_mod.port_matrix(tree, m2, p=2.0)
+    plan = gb.KrdPlan(p2_mode=p2_mode)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(m2["off"], m2["edge"], m2["pos"], m2["mass"])
+    got1, got2 = plan.compute(p=1.0), plan.compute(p=2.0)
+    plan.close()
+    assert np.all(np.isfinite(got1)) and rel_err(got1, want1) <= TOL
+    fin = np.isfinite(want2)                      # (a negative total would be NaN in the reference as well)
+    assert np.array_equal(np.isfinite(got2), fin)
+    assert rel_err(got2[fin], want2[fin]) <= TOL
+
+
+@pytest.mark.parametrize("entry", ["device", "shard", "host"])
+def test_gram_fixup_overflow_is_handled_by_every_entry_point(gb, oracle_mod, entry):
+    """More near-duplicate pairs than the Gram path's fix-up list holds (2^20): the launch is repeated on the direct path
+    inside the library for EVERY entry point, not only krd_compute (round-1 advice)."""
+    import torch
+    from gappa_b200 import synth
+    n = 1500                                              # 1500 * 1499 / 2 = 1,124,250 > 2^20 cancelling pairs
+    tree = synth.tree_with_edges(31, seed=5)
+    base = synth.sample_masses(tree, 2, 60, seed=5)
+    rng = np.random.default_rng(5)
+    lo, hi = base["off"][1], base["off"][2]
+    off, edge, pos, mass = [0, int(base["off"][1])], [base["edge"][:lo]], [base["pos"][:lo]], [base["mass"][:lo]]
+    for rep in range(n - 1):                              # sample 0 is the Gram reference column; the other n-1 are near-copies of sample 1
+        m = base["mass"][lo:hi] * (1.0 + 1e-5 * rng.standard_normal(hi - lo))
+        edge.append(base["edge"][lo:hi]); pos.append(base["pos"][lo:hi]); mass.append(m / m.sum())
+        off.append(off[-1] + hi - lo)
+    masses = dict(off=np.array(off, np.int64), edge=np.concatenate(edge), pos=np.concatenate(pos), mass=np.concatenate(mass))
+    direct = gb.KrdPlan(p2_mode=1)
+    direct.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    direct.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
+    want = direct.compute(p=2.0)
+    direct.close()
+    sub = list(range(0, n, 97))
+    idx = np.concatenate([masses["off"][s] + np.arange(masses["off"][s + 1] - masses["off"][s]) for s in sub])
+    sub_m = dict(off=np.concatenate([[0], np.cumsum([masses["off"][s + 1] - masses["off"][s] for s in sub])]).astype(np.int64),
+                 edge=masses["edge"][idx], pos=masses["pos"][idx], mass=masses["mass"][idx])
+    assert rel_err(want[np.ix_(sub, sub)], oracle_mod.port_matrix(tree, sub_m, p=2.0)) <= TOL
+    plan = gb.KrdPlan(p2_mode=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(masses["off"], masses["edge"], masses["pos"], masses["mass"])
+    if entry == "host":
+        got = plan.compute(p=2.0)
+    elif entry == "device":
+        d = torch.zeros((n, n), dtype=torch.float64, device="cuda")
+        plan.compute_device(d, p=2.0)
+        torch.cuda.synchronize()
+        got = d.cpu().numpy()
+    else:
+        world = 1                                         # (one rank's share must hold > 2^20 cancelling pairs)
+        shard = plan.shard_doubles(world)
+        g = torch.empty(shard * world, dtype=torch.float64, device="cuda")
+        for r in range(world):
+            plan.compute_shard(g[r * shard:(r + 1) * shard], r, world, p=2.0)
+        d = torch.zeros((n, n), dtype=torch.float64, device="cuda")
+        plan.unpack_shards(g, d, world)
+        torch.cuda.synchronize()
+        got = d.cpu().numpy()
+    assert plan.stats()["gram_fixups"] == -1              # the list did overflow ...
+    plan.close()
+    assert rel_err(got, want) <= TOL                      # ... and the result is the direct path's

@@ -62,7 +62,7 @@ static void pipe_quiesce(krd_handle* h)
 
 static void free_masses(krd_handle* h)   // buffers are kept for reuse; only the state is dropped
 {
-    h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr;
+    h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr; h->d_cell32 = nullptr; h->binned_input = false;
     h->have_masses = false; h->F_valid = false;
 }
 
@@ -118,7 +118,7 @@ void krd_destroy(krd_handle* h)
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
     cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_kmeans); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
-    cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
+    cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_edge_dec); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
     cudaFree(h->d_flags);
@@ -154,29 +154,38 @@ krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_no
     return st;
 }
 
-krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
-                          const double* pos, const double* mass)
+// Host arrays -> HBM + K0.  cell32 != nullptr: the compact binned form (cell = edge * bins + bin, 12 B per entry).
+static krd_status set_masses_host(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
+                                  const double* pos, const double* mass, const uint32_t* cell32, bool binned)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     krd_status st = set_masses_common(h, n_samples, sample_off);
     if (st != KRD_OK) return st;
     const int64_t M = sample_off[n_samples];
-    if (M > 0 && (!edge || !pos || !mass)) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
+    if (M > 0 && (!mass || (binned ? !cell32 : (!edge || !pos)))) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
+    if (binned && (h->cfg.bins < 1 || (int64_t)h->E * h->cfg.bins > 0xFFFFFFF0ll))
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned needs krd_config.bins >= 1 and n_edges * bins < 2^32");
     KRD_CUDA(h, cudaSetDevice(h->device));
     pipe_quiesce(h);
     free_masses(h);
-    if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass);
+    if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass, cell32, binned);
     if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = M;
     const size_t Mx = (size_t)std::max<int64_t>(M, 1);
     if ((st = reserve(h, (void**)&h->d_off, (size_t)(n_samples + 1) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_owned[0], Mx * 4)) != KRD_OK) return st;
-    if ((st = reserve(h, &h->d_owned[1], Mx * 8)) != KRD_OK) return st;
+    if (!binned && (st = reserve(h, &h->d_owned[1], Mx * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_owned[2], Mx * 8)) != KRD_OK) return st;
-    h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; h->d_mass = (double*)h->d_owned[2];
+    h->d_mass = (double*)h->d_owned[2];
     KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
-    KRD_CUDA(h, cudaMemcpyAsync(h->d_edge, edge, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
-    KRD_CUDA(h, cudaMemcpyAsync(h->d_pos, pos, (size_t)M * 8, cudaMemcpyHostToDevice, h->stream));
+    if (binned) {
+        h->binned_input = true; h->d_cell32 = (const uint32_t*)h->d_owned[0];
+        KRD_CUDA(h, cudaMemcpyAsync(h->d_owned[0], cell32, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1];
+        KRD_CUDA(h, cudaMemcpyAsync(h->d_edge, edge, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
+        KRD_CUDA(h, cudaMemcpyAsync(h->d_pos, pos, (size_t)M * 8, cudaMemcpyHostToDevice, h->stream));
+    }
     KRD_CUDA(h, cudaMemcpyAsync(h->d_mass, mass, (size_t)M * 8, cudaMemcpyHostToDevice, h->stream));
     st = prepare_masses(h);
     if (st != KRD_OK) return st;
@@ -185,12 +194,29 @@ krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sampl
     return KRD_OK;
 }
 
-krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
-                                 const double* d_pos, const double* d_mass)
+krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
+                          const double* pos, const double* mass)
+{
+    return set_masses_host(h, n_samples, sample_off, edge, pos, mass, nullptr, false);
+}
+
+krd_status krd_set_masses_binned(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* cell,
+                                 const double* mass)
+{
+    return set_masses_host(h, n_samples, sample_off, nullptr, nullptr, mass, cell, true);
+}
+
+}  // extern "C"
+
+namespace krd {
+krd_status set_masses_device_impl(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
+                                  const double* d_pos, const double* d_mass, const uint32_t* d_cell32, bool binned)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     krd_status st = set_masses_common(h, n_samples, sample_off);
     if (st != KRD_OK) return st;
+    if (binned && (h->cfg.bins < 1 || (int64_t)h->E * h->cfg.bins > 0xFFFFFFF0ll))
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned needs krd_config.bins >= 1 and n_edges * bins < 2^32");
     KRD_CUDA(h, cudaSetDevice(h->device));
     pipe_quiesce(h);
     free_masses(h);
@@ -200,11 +226,27 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
     if (h->d_off_from) launch_rebase_off(h->d_off_from, n_samples + 1, h->d_off, h->stream);
     else KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     h->d_edge = const_cast<int32_t*>(d_edge); h->d_pos = const_cast<double*>(d_pos); h->d_mass = const_cast<double*>(d_mass);
+    h->binned_input = binned; h->d_cell32 = d_cell32;
     st = prepare_masses(h);
     if (st != KRD_OK) return st;
     h->have_masses = true;
     h->stats.n_samples = n_samples; h->stats.n_edges = h->E; h->stats.n_masses = h->M;
     return KRD_OK;
+}
+}  // namespace krd
+
+extern "C" {
+
+krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
+                                 const double* d_pos, const double* d_mass)
+{
+    return set_masses_device_impl(h, n_samples, sample_off, d_edge, d_pos, d_mass, nullptr, false);
+}
+
+krd_status krd_set_masses_binned_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* d_cell,
+                                        const double* d_mass)
+{
+    return set_masses_device_impl(h, n_samples, sample_off, nullptr, nullptr, d_mass, d_cell, true);
 }
 
 static krd_status check_compute(krd_handle* h, double p, double divisor)
@@ -335,6 +377,16 @@ krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathe
     if (world < 1 || !d_gathered || !d_out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad arguments");
     KRD_CUDA(h, cudaSetDevice(h->device));
     return unpack_shards(h, world, d_gathered, d_out);
+}
+
+krd_status krd_unpack_shards_rows(krd_handle* h, int32_t world, const double* d_gathered, int32_t row0, int32_t row1, double* d_out_rows)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
+    if (world < 1 || !d_gathered || !d_out_rows || row0 < 0 || row1 < row0 || row1 > h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad arguments");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    if (h->piped) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }
+    return unpack_shard_rows(h, d_gathered, row0, row1, d_out_rows);
 }
 
 krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)

@@ -200,6 +200,24 @@ __global__ void k_slots_binned(const int32_t* __restrict__ edge, const double* _
     slot[m] = (int32_t)floor(pn);
 }
 
+// Compact binned input (krd_set_masses_binned): cell = edge * B + bin.  One pass decodes edge / slot / sample id and checks
+// the range and the order (ascending cell within a sample = MassTree order of the binified tree); flags as in
+// k_check_canonical.  `clamp`: deferred check of a pipelined child — a bad edge is recorded and replaced by edge 0.
+__global__ void k_decode_binned(const int64_t* __restrict__ off, int n, const uint32_t* __restrict__ cell, int64_t M, uint32_t B, int E,
+                                int clamp, uint32_t* __restrict__ sid, int32_t* __restrict__ edge, int32_t* __restrict__ slot,
+                                int* __restrict__ flags)
+{
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const int i = sample_of(off, n, m);
+    const uint32_t c = cell[m];
+    uint32_t e = c / B;
+    const uint32_t q = c - e * B;
+    if (e >= (uint32_t)E) { atomicOr(flags, 2); if (!clamp) return; e = 0; }
+    if (m > off[i] && cell[m - 1] > c) atomicOr(flags, 1);
+    sid[m] = (uint32_t)i; edge[m] = (int32_t)e; slot[m] = (int32_t)q;
+}
+
 // Segment table of the binned mode: edge e owns segments e*(B+1)+t, t = 0..B, bounded by the bin
 // centres c_q = q*bl/nb + bl/nb/2 (functions.cpp:240): [0,c_0], (c_0,c_1], ..., (c_{B-1}, bl].
 __global__ void k_len_binned(const double* __restrict__ bl, int E, int B, double* __restrict__ len,
@@ -375,7 +393,15 @@ krd_status prepare_masses(krd_handle* h)
     int* const d_flags = static_cast<int*>(h->d_flags);
     { krd_status rs = reserve(h, (void**)&h->d_sid, (size_t)std::max<int64_t>(M, 1) * 4); if (rs != KRD_OK) return rs; }
     zero_words(d_flags, 2, 2, 1, h->stream);   // (16 bytes reserved: int [0] order / range check, int [1] negative segment length)
-    if (M > 0) {
+    if (h->binned_input) {
+        if (h->cfg.bins < 1) return fail(h, KRD_ERR_STATE, "binned input without bins");
+        krd_status rs;
+        if ((rs = reserve(h, (void**)&h->d_slot, (size_t)std::max<int64_t>(M, 1) * 4)) != KRD_OK) return rs;
+        if ((rs = reserve(h, (void**)&h->d_edge_dec, (size_t)std::max<int64_t>(M, 1) * 4)) != KRD_OK) return rs;
+        h->d_edge = h->d_edge_dec;
+        if (M > 0) k_decode_binned<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, h->d_cell32, M, (uint32_t)h->cfg.bins, E, h->defer_check ? 1 : 0,
+                                                                   h->d_sid, h->d_edge, h->d_slot, d_flags);
+    } else if (M > 0) {
         k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
         if (h->defer_check) k_clamp_edges<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, M, E, d_flags);
         k_check_canonical<<<nblk(M), 256, 0, h->stream>>>(h->d_sid, h->d_edge, h->d_pos, M, E, d_flags);
@@ -386,6 +412,8 @@ krd_status prepare_masses(krd_handle* h)
         KRD_CUDA(h, cudaStreamSynchronize(h->stream));
     }
     if (hflags & 2) return fail(h, KRD_ERR_INVALID_ARGUMENT, "mass entry refers to an edge outside the tree");
+    if ((hflags & 1) && h->binned_input)
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned: the entries of a sample must be sorted by cell (MassTree order)");
     if (hflags & 1) {
         // sort by (sample, edge, pos), stable: three LSD passes, then gather into owned buffers
         DevBuf perm2, sedge, perm3, skeys;
@@ -429,7 +457,7 @@ krd_status prepare_masses(krd_handle* h)
         krd_status st = alloc_len((int64_t)E * (B + 1));
         if (st != KRD_OK) return st;
         double nb = (double)B;
-        if (M > 0) k_slots_binned<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, h->d_pos, h->d_bl, M, nb, std::nextafter(nb, 0.0), h->d_slot);
+        if (M > 0 && !h->binned_input) k_slots_binned<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, h->d_pos, h->d_bl, M, nb, std::nextafter(nb, 0.0), h->d_slot);
         k_len_binned<<<nblk((int64_t)E * (B + 1) + 1), 256, 0, h->stream>>>(h->d_bl, E, B, h->d_len, h->d_seg_off);
     } else {
         DevBuf perm, sedge, head, rank, uidx, upos, uedge, cnt, ubase, tmp;

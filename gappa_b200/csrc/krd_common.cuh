@@ -68,6 +68,11 @@ struct krd_handle {
     uint32_t* d_sid = nullptr;  // M: sample of each mass entry
     int32_t* d_slot = nullptr;  // M: segment index within the edge that receives this mass
     void*    d_owned[3] = {nullptr, nullptr, nullptr};  // edge/pos/mass buffers we allocated
+    // compact binned input (krd_set_masses_binned): entries arrive as (cell = edge * bins + bin, mass); d_edge / d_slot are
+    // decoded from it by K0 and d_pos stays null (the bin centre is implied)
+    bool     binned_input = false;
+    const uint32_t* d_cell32 = nullptr;   // M
+    int32_t* d_edge_dec = nullptr;        // M: decoded edge ids (owned, grow-only)
 
     // ---- segments + dense matrix ----
     int64_t S = 0, S_pad = 0;
@@ -182,10 +187,15 @@ krd_status build_F(krd_handle* h);                    // K1
 krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
                      double* d_out_matrix, double* d_out_packed);
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
+krd_status unpack_shard_rows(krd_handle* h, const double* d_gathered, int row0, int row1, double* d_out_rows);
 
 // krd_pipe.cu — pipelined ingest (krd_config.pipeline)
 bool pipe_wanted(const krd_handle* h, int32_t n_samples);
-krd_status pipe_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge, const double* pos, const double* mass);
+krd_status pipe_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge, const double* pos, const double* mass,
+                           const uint32_t* cell32, bool binned);   // binned: compact input (cell32, mass); edge / pos unused
+// krd_api.cu: masses already on the device; `binned` selects the compact form (d_cell32, d_mass)
+krd_status set_masses_device_impl(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge, const double* d_pos,
+                                  const double* d_mass, const uint32_t* d_cell32, bool binned);
 krd_status pipe_compute(krd_handle* h, double p, double divisor, double* d_out);   // all phases, or everything at once when the children are resident
 krd_status pipe_flatten(krd_handle* h);     // finish the uploads and turn the handle into an ordinary one (squash, k-means, sharding, introspection)
 void pipe_destroy(krd_handle* h);

@@ -539,6 +539,36 @@ __global__ void __launch_bounds__(256) k_unpack(const double* __restrict__ gathe
     }
 }
 
+// Same for a ROW RANGE of the matrix: out is (row1 - row0) x N, row i of the matrix at out + (i - row0) * N.  One process per
+// GPU: after the all-gather every rank unpacks only the rows it then copies to the host over its own PCIe link.
+// Both passes write coalesced: the mirrored half is read transposed (from L2) instead of written transposed.
+__global__ void __launch_bounds__(256) k_unpack_rows(const double* __restrict__ gathered, const Tile* __restrict__ tiles,
+                                                     int64_t n_tiles, int N, int row0, int row1, double* __restrict__ out)
+{
+    const int64_t t = blockIdx.x;
+    if (t >= n_tiles) return;
+    const Tile tile = tiles[t];
+    const int i0 = tile.i * TILE, j0 = tile.j * TILE;
+    const double* src = gathered + (size_t)t * (TILE * TILE);
+    if (i0 < row1 && i0 + TILE > row0) {                       // rows of block i: (i, j) for j in block j
+        for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
+            const int r = idx / TILE, c = idx % TILE;
+            const int i = i0 + r, j = j0 + c;
+            if (i < row0 || i >= row1 || i >= N || j >= N) continue;
+            if (i < j) out[(int64_t)(i - row0) * N + j] = src[idx];
+            else if (i == j) out[(int64_t)(i - row0) * N + i] = 0.0;
+        }
+    }
+    if (j0 < row1 && j0 + TILE > row0) {                       // rows of block j: the mirror (j, i) for i in block i
+        for (int idx = threadIdx.x; idx < TILE * TILE; idx += blockDim.x) {
+            const int c = idx / TILE, r = idx % TILE;          // r fastest: consecutive threads write consecutive columns i
+            const int i = i0 + r, j = j0 + c;
+            if (j < row0 || j >= row1 || i >= N || j >= N) continue;
+            if (i < j) out[(int64_t)(j - row0) * N + i] = src[r * TILE + c];
+        }
+    }
+}
+
 // ---- Gram mode: reference column and per-sample squared norms -------------------------------------
 __global__ void k_center_col(const double* __restrict__ F, int64_t ld, int64_t S_pad, double* __restrict__ c)
 {
@@ -823,6 +853,17 @@ krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, dou
     if (n_tiles == 0) return KRD_OK;
     (void)world;
     k_unpack<<<(unsigned)n_tiles, 256, 0, h->stream>>>(d_gathered, h->d_tiles, n_tiles, h->N, d_out);
+    KRD_CUDA(h, cudaGetLastError());
+    return KRD_OK;
+}
+
+krd_status unpack_shard_rows(krd_handle* h, const double* d_gathered, int row0, int row1, double* d_out_rows)
+{
+    krd_status st = ensure_tiles(h);
+    if (st != KRD_OK) return st;
+    const int64_t n_tiles = h->n_tiles_alloc;
+    if (n_tiles == 0 || row1 <= row0) return KRD_OK;
+    k_unpack_rows<<<(unsigned)n_tiles, 256, 0, h->stream>>>(d_gathered, h->d_tiles, n_tiles, h->N, row0, row1, d_out_rows);
     KRD_CUDA(h, cudaGetLastError());
     return KRD_OK;
 }

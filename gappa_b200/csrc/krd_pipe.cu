@@ -33,8 +33,6 @@ extern "C" krd_status krd_create(const krd_config* cfg, krd_handle** out);
 extern "C" void krd_destroy(krd_handle* h);
 extern "C" krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_node, const int32_t* child_node,
                                    const double* branch_length, int32_t root_node);
-extern "C" krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
-                                            const double* d_pos, const double* d_mass);
 
 namespace krd {
 
@@ -66,7 +64,8 @@ static krd_status kid_error(krd_handle* h, krd_handle* kid, krd_status st)
 
 static krd_status kid_prepare(krd_handle* h, int q, bool wait = true);
 
-krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const int32_t* edge, const double* pos, const double* mass)
+krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const int32_t* edge, const double* pos, const double* mass,
+                           const uint32_t* cell32, bool binned)
 {
     const int64_t M = off[N];
     const int T = (N + TILE - 1) / TILE;
@@ -121,9 +120,12 @@ krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const i
     const size_t Mx = (size_t)std::max<int64_t>(M, 1);
     if ((st = reserve(h, (void**)&h->d_off, (size_t)(N + 1) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_owned[0], Mx * 4)) != KRD_OK) return st;
-    if ((st = reserve(h, &h->d_owned[1], Mx * 8)) != KRD_OK) return st;
+    if (!binned && (st = reserve(h, &h->d_owned[1], Mx * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_owned[2], Mx * 8)) != KRD_OK) return st;
-    h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; h->d_mass = (double*)h->d_owned[2];
+    h->d_mass = (double*)h->d_owned[2];
+    h->binned_input = binned;
+    if (binned) { h->d_cell32 = (const uint32_t*)h->d_owned[0]; h->d_edge = nullptr; h->d_pos = nullptr; }
+    else { h->d_cell32 = nullptr; h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; }
 
     // ---- uploads, child by child, on the copy stream (after whatever the compute stream still does with the buffers) ----
     KRD_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
@@ -140,8 +142,11 @@ krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const i
         ko.resize((size_t)(s1 - s0) + 1);
         for (int i = s0; i <= s1; ++i) ko[(size_t)(i - s0)] = off[i] - m0;
         if (m1 > m0) {
-            KRD_CUDA(h, cudaMemcpyAsync(h->d_edge + m0, edge + m0, (size_t)(m1 - m0) * 4, cudaMemcpyHostToDevice, h->copy_stream));
-            KRD_CUDA(h, cudaMemcpyAsync(h->d_pos + m0, pos + m0, (size_t)(m1 - m0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
+            if (binned) KRD_CUDA(h, cudaMemcpyAsync((uint32_t*)h->d_owned[0] + m0, cell32 + m0, (size_t)(m1 - m0) * 4, cudaMemcpyHostToDevice, h->copy_stream));
+            else {
+                KRD_CUDA(h, cudaMemcpyAsync(h->d_edge + m0, edge + m0, (size_t)(m1 - m0) * 4, cudaMemcpyHostToDevice, h->copy_stream));
+                KRD_CUDA(h, cudaMemcpyAsync(h->d_pos + m0, pos + m0, (size_t)(m1 - m0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
+            }
             KRD_CUDA(h, cudaMemcpyAsync(h->d_mass + m0, mass + m0, (size_t)(m1 - m0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
         }
         KRD_CUDA(h, cudaEventRecord(h->kid_ev[(size_t)q], h->copy_stream));
@@ -194,7 +199,9 @@ static krd_status kid_prepare(krd_handle* h, int q, bool wait)
     int64_t base = 0;
     for (int k = 0; k < q; ++k) base += h->kid_off[(size_t)k].back();
     if (g_dbg) std::fprintf(stderr, "[pipe] child %d: samples %d..%d, entries %lld..%lld of %lld\n", q, s0, s0 + (int)ko.size() - 1, (long long)base, (long long)(base + ko.back()), (long long)h->M);
-    krd_status st = krd_set_masses_device(kid, (int32_t)ko.size() - 1, ko.data(), h->d_edge + base, h->d_pos + base, h->d_mass + base);
+    krd_status st = h->binned_input
+        ? set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), nullptr, nullptr, h->d_mass + base, h->d_cell32 + base, true)
+        : set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), h->d_edge + base, h->d_pos + base, h->d_mass + base, nullptr, false);
     if (st != KRD_OK) return kid_error(h, kid, st);
     if (!kid->tiled) return fail(h, KRD_ERR_STATE, "pipelined ingest: child without a tiled builder");
     return KRD_OK;
@@ -355,7 +362,7 @@ void pipe_destroy(krd_handle* h)
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     drop_graphs(h);
     if (h->cap_stream) { cudaStreamDestroy(h->cap_stream); h->cap_stream = nullptr; }
-    for (krd_handle* kid : h->kids) { kid->d_F = nullptr; kid->d_edge = nullptr; kid->d_pos = nullptr; kid->d_mass = nullptr; krd_destroy(kid); }
+    for (krd_handle* kid : h->kids) { kid->d_F = nullptr; kid->d_edge = nullptr; kid->d_pos = nullptr; kid->d_mass = nullptr; kid->d_cell32 = nullptr; krd_destroy(kid); }
     h->kids.clear();
     for (cudaEvent_t ev : h->kid_ev) cudaEventDestroy(ev);
     h->kid_ev.clear();

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -99,6 +99,12 @@ def lib():
     L.krd_set_masses.argtypes = [vp, i32, vp, vp, vp, vp]
     L.krd_set_masses_device.restype = C.c_int
     L.krd_set_masses_device.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.krd_set_masses_binned.restype = C.c_int
+    L.krd_set_masses_binned.argtypes = [vp, i32, vp, vp, vp]
+    L.krd_set_masses_binned_device.restype = C.c_int
+    L.krd_set_masses_binned_device.argtypes = [vp, i32, vp, vp, vp]
+    L.krd_unpack_shards_rows.restype = C.c_int
+    L.krd_unpack_shards_rows.argtypes = [vp, i32, vp, i32, i32, vp]
     L.krd_compute.restype = C.c_int
     L.krd_compute.argtypes = [vp, dbl, dbl, vp]
     L.krd_compute_device.restype = C.c_int
@@ -210,6 +216,28 @@ class KrdPlan:
         self._check(self._L.krd_set_masses_device(self._h, n, _ptr(off), _ptr(d_edge), _ptr(d_pos), _ptr(d_mass)))
         self.n_samples = n
 
+    def set_masses_binned(self, off, cell, mass):
+        """Compact binned form (krd_set_masses_binned): cell = edge * bins + bin (uint32), sorted within a sample. HOST arrays."""
+        if isinstance(off, (np.ndarray, list, tuple)):
+            off = np.ascontiguousarray(off, np.int64)
+        if isinstance(cell, np.ndarray):
+            cell = np.ascontiguousarray(cell, np.uint32)
+            mass = np.ascontiguousarray(mass, np.float64)
+        n = len(off) - 1
+        self._keep_host = [off, cell, mass]
+        self._check(self._L.krd_set_masses_binned(self._h, n, _ptr(off), _ptr(cell), _ptr(mass)))
+        self.n_samples = n
+
+    def set_masses_binned_device(self, off, d_cell, d_mass):
+        off = np.ascontiguousarray(off, np.int64)
+        n = len(off) - 1
+        self._keep = [d_cell, d_mass]
+        self._check(self._L.krd_set_masses_binned_device(self._h, n, _ptr(off), _ptr(d_cell), _ptr(d_mass)))
+        self.n_samples = n
+
+    def unpack_shards_rows(self, d_gathered, d_out_rows, world, row0, row1):
+        self._check(self._L.krd_unpack_shards_rows(self._h, world, _ptr(d_gathered), int(row0), int(row1), _ptr(d_out_rows)))
+
     def compute(self, p=1.0, divisor=1.0, out=None):
         """Host result (numpy n x n)."""
         n = self.n_samples
@@ -285,6 +313,19 @@ def unpack_shards_host(n_samples, packed_per_rank):
     if st != 0:
         raise KrdError(st, "krd_unpack_shards_host failed")
     return out
+
+
+def binned_cells(tree, masses, bins):
+    """Host-side encoding of BINIFIED mass trees (positions = bin centres, e.g. workloads.build output or the result of
+    mass_tree_binify_masses) as the compact form of krd_set_masses_binned: cell = edge * bins + bin, with the reference's bin
+    index expression (functions.cpp:231-237).  Pure re-encoding; no arithmetic on masses."""
+    bl = np.asarray(tree["bl"], np.float64)[masses["edge"]]
+    nb = float(bins)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        v = masses["pos"] / bl * nb
+    pn = np.where(0.0 < v, v, 0.0)
+    pn = np.where(np.nextafter(nb, 0.0) < pn, np.nextafter(nb, 0.0), pn)
+    return (masses["edge"].astype(np.int64) * bins + np.floor(pn).astype(np.int64)).astype(np.uint32)
 
 
 def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):

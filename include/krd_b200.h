@@ -85,7 +85,7 @@ typedef struct krd_stats {
     float   ms_epilogue;    /* device time of the split-sum / root / mirror epilogue */
     float   reserved_f;
     int32_t gram_fixups;    /* exponent 2, Gram path: pairs recomputed directly because |a|^2+|b|^2-2ab cancelled
-                               (-1: more than the list holds = the result is NOT within tolerance, use p2_mode 1) */
+                               (-1: more than the list holds; the launch was repeated on the direct path by the library) */
     int32_t reserved_i;
 } krd_stats;
 
@@ -112,14 +112,27 @@ krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sampl
 krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off,
                                  const int32_t* d_edge, const double* d_pos, const double* d_mass);
 
+/* The same N mass trees in COMPACT BINNED form (krd_config.bins = B >= 1 only): what mass_tree_binify_masses
+ * (tree/mass_tree/functions.cpp:222-265) leaves is one mass per occupied (edge, bin), sitting at the bin centre, so an
+ * entry is fully described by  cell = edge * B + bin  (bin = floor(min(max(0, pos / bl * B), nextafter(B, 0))),
+ * functions.cpp:231-237) and its mass: 12 bytes instead of 20 across PCIe.  libkrd_host's ingest emits this form when
+ * it bins (include/krd_host.h).  Within a sample the entries must be sorted by cell (= MassTree order); equal cells are
+ * summed.  n_edges * B must be < 2^32.  HOST pointers; honours krd_config.pipeline like krd_set_masses. */
+krd_status krd_set_masses_binned(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* cell,
+                                 const double* mass);
+/* Same with DEVICE arrays (no copy is made: they must stay valid until the next krd_set_masses*). sample_off is host. */
+krd_status krd_set_masses_binned_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* d_cell,
+                                        const double* d_mass);
+
 /* earth_movers_distance(trees, p) [/ divisor].  Builds F (level-synchronous subtree scan), runs
  * the all-pairs kernel, writes the n x n matrix.  `out` is a HOST pointer; returns after the
  * matrix is complete in host memory. divisor = 1.0 for no normalisation.  p <= 0 (or NaN) fails with
- * KRD_ERR_INVALID_EXPONENT and genesis' message (emd.cpp:186-190); p > 30000 fails with KRD_ERR_INVALID_ARGUMENT
- * (the general-p operator's exp2 argument must fit 31 bits — the one deviation from "any p > 0"). */
+ * KRD_ERR_INVALID_EXPONENT and genesis' message (emd.cpp:186-190); every p > 0 is accepted (p > 30000 runs a slower
+ * library-pow operator, the table-driven one needs 32 p log2 x inside 31 bits). */
 krd_status krd_compute(krd_handle* h, double p, double divisor, double* out);
 
-/* Same with a DEVICE output pointer (n*n doubles); asynchronous on the handle's stream. */
+/* Same with a DEVICE output pointer (n*n doubles); asynchronous on the handle's stream (except for p = 2 on the Gram
+ * path, which reads its 4-byte fix-up count back before returning). */
 krd_status krd_compute_device(krd_handle* h, double p, double divisor, double* d_out);
 
 /* Multi-GPU sharding (one process per GPU, F replicated): rank r of `world` computes its share
@@ -131,6 +144,10 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
 /* Scatter the all-gathered packed tiles (world * krd_shard_doubles doubles, DEVICE) into the
  * full symmetric n x n DEVICE matrix. */
 krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathered, double* d_out);
+/* Same for the rows [row0, row1) of the matrix only: d_out_rows is (row1 - row0) x n, DEVICE.  With one process per GPU
+ * every rank unpacks just the row block it then copies to the host over ITS PCIe link (bench.py, N > 1). */
+krd_status krd_unpack_shards_rows(krd_handle* h, int32_t world, const double* d_gathered, int32_t row0, int32_t row1,
+                                  double* d_out_rows);
 
 /* The same for a caller without an NCCL communicator (e.g. one host thread per GPU in one process, as
  * `gappa-b200 --gpus G` does): the rank's packed tiles go to a HOST buffer of krd_shard_doubles() doubles

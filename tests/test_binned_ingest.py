@@ -1,0 +1,103 @@
+"""Compact binned ingest (krd_set_masses_binned: cell = edge * bins + bin, 12 B per entry) and the row-range unpack of the
+sharded result (krd_unpack_shards_rows), through the C ABI on a B200.  The compact form must give the SAME bits as
+krd_set_masses fed with the binified mass trees, and the same matrix as the reference path (port oracle)."""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _binified(tree, n, placements, bins, seed):
+    from gappa_b200 import synth
+    raw = synth.sample_masses(tree, n, placements, seed=seed)
+    return raw, synth.binify_host(tree, raw, bins)
+
+
+@pytest.mark.parametrize("n,E,P,bins,pipeline", [(150, 61, 80, 3, 0), (70, 150, 300, 4, 0), (33, 20, 100, 40, 0),
+                                                 (700, 301, 200, 4, 1), (1300, 97, 60, 1, 1)])
+def test_compact_form_equals_full_form(n, E, P, bins, pipeline):
+    import gappa_b200
+    import oracle
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(E, seed=n)
+    raw, b = _binified(tree, n, P, bins, seed=n)
+    cell = gappa_b200.krd.binned_cells(tree, b, bins)
+    for i in range(0, n, 17):        # the binified trees are in MassTree order: cells strictly ascending within a sample
+        assert np.all(np.diff(cell[b["off"][i]:b["off"][i + 1]].astype(np.int64)) > 0)
+    full = gappa_b200.KrdPlan(bins=bins)
+    full.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    full.set_masses(b["off"], b["edge"], b["pos"], b["mass"])
+    comp = gappa_b200.KrdPlan(bins=bins, pipeline=pipeline)
+    comp.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    comp.set_masses_binned(b["off"], cell, b["mass"])
+    for p in (1.0, 0.5, 2.0):
+        Df, Dc = full.compute(p=p), comp.compute(p=p)
+        if pipeline and p != 2.0:      # phased: different partial-sum splits (DESIGN.md "Pipelined ingest")
+            assert rel_err(Dc, Df) <= (1e-12 if p >= 1 else 1e-9)
+        else:
+            assert np.array_equal(Dc, Df), p
+    Ff, _ = full.debug_F()
+    Fc, _ = comp.debug_F()
+    assert np.array_equal(Ff, Fc)
+    # and against the reference path on the RAW placements (binning included)
+    idx = list(range(min(n, 40)))
+    sub = dict(off=raw["off"][: len(idx) + 1], edge=raw["edge"][: raw["off"][len(idx)]], pos=raw["pos"][: raw["off"][len(idx)]],
+               mass=raw["mass"][: raw["off"][len(idx)]])
+    want = oracle.port_matrix(tree, sub, p=1.0, bins=bins)
+    assert rel_err(comp.compute(p=1.0)[np.ix_(idx, idx)], want) <= 1e-10
+    full.close(); comp.close()
+
+
+def test_compact_form_duplicates_are_summed_and_errors_are_reported():
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(21, seed=2)
+    raw, b = _binified(tree, 9, 50, 2, seed=2)
+    cell = gappa_b200.krd.binned_cells(tree, b, 2)
+    # every entry split into two halves with the same cell: same tree
+    off2 = b["off"] * 2
+    cell2 = np.repeat(cell, 2); mass2 = np.repeat(b["mass"] * 0.5, 2)
+    a = gappa_b200.KrdPlan(bins=2); a.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    a.set_masses_binned(b["off"], cell, b["mass"]); Da = a.compute()
+    a.set_masses_binned(off2, cell2, mass2); Db = a.compute()
+    assert rel_err(Db, Da) <= 1e-13
+    bad = cell.copy(); bad[[3, 4]] = bad[[4, 3]]                 # out of order inside sample 0
+    with pytest.raises(gappa_b200.KrdError, match="sorted"):
+        a.set_masses_binned(b["off"], bad, b["mass"])
+    bad = cell.copy(); bad[7] = 21 * 2 + 5                        # edge 23 of a 21-edge tree
+    with pytest.raises(gappa_b200.KrdError, match="outside the tree"):
+        a.set_masses_binned(b["off"], bad, b["mass"])
+    a.close()
+    e = gappa_b200.KrdPlan(bins=0); e.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    with pytest.raises(gappa_b200.KrdError, match="bins"):
+        e.set_masses_binned(b["off"], cell, b["mass"])
+    e.close()
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_row_range_unpack_equals_full_unpack(world):
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth
+    n = 333
+    tree = synth.tree_with_edges(77, seed=6)
+    raw, b = _binified(tree, n, 90, 2, seed=6)
+    plan = gappa_b200.KrdPlan(bins=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned(b["off"], gappa_b200.krd.binned_cells(tree, b, 2), b["mass"])
+    shard = plan.shard_doubles(world)
+    g = torch.empty(shard * world, dtype=torch.float64, device="cuda")
+    for r in range(world):
+        plan.compute_shard(g[r * shard:(r + 1) * shard], r, world)
+    full = torch.full((n, n), -1.0, dtype=torch.float64, device="cuda")
+    plan.unpack_shards(g, full, world)
+    rows = torch.full((n, n), -2.0, dtype=torch.float64, device="cuda")
+    for r in range(world):                                    # every rank unpacks its own row block
+        r0, r1 = r * n // world, (r + 1) * n // world
+        plan.unpack_shards_rows(g, rows[r0:r1], world, r0, r1)
+    torch.cuda.synchronize()
+    assert torch.equal(rows, full)
+    assert np.array_equal(full.cpu().numpy(), plan.compute())
+    plan.close()

@@ -1,9 +1,12 @@
 #!/usr/bin/env python
 """bench.py — KR sample-pairs/s of the B200 path (and of the reference CPU path, --impl reference).
 
-One "step" = one pass of the hot path over the workload's mass trees:
-  value : masses resident in HBM -> F build (K1) + pair kernel (K2) + epilogue -> matrix in HBM
-  e2e   : HOST (pinned) mass trees -> krd_set_masses (H2D + slots) + krd_compute -> matrix on HOST
+One "step" = one pass of the hot path over the workload's mass trees (SURVEY.md §8d):
+  value : masses resident in HBM -> F build (K1) + pair kernel (K2) + epilogue [+ exchange] + D2H -> matrix complete in HOST memory
+  e2e   : HOST (pinned) mass trees -> krd_set_masses_binned (H2D + K0) + compute -> matrix in HOST memory, through the C ABI
+Workloads: --gpus 1 runs cfg2 (BASELINE.json configs[1], the "1 B200" config) and adds a short 1-GPU measurement of cfg4
+(`strong_scaling_base`); --gpus N > 1 runs cfg4 (the north-star's multi-GPU config: 10,000 samples x 49,999 edges,
+100,000 placements per sample, bins 1, p = 1) with the cohort FIXED: strong scaling.
 Launch: `python bench.py --gpus 1 ...` or under torchrun (one rank per GPU, NCCL).
 """
 import argparse
@@ -29,7 +32,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("KRD_WORKLOAD", "cfg2"))
+    ap.add_argument("--workload", default=os.environ.get("KRD_WORKLOAD"))
     ap.add_argument("--samples", type=int)
     ap.add_argument("--edges", type=int)
     ap.add_argument("--placements", type=int)
@@ -37,6 +40,9 @@ def parse():
     ap.add_argument("--p", type=float)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-base", action="store_true", help="N = 1: skip the 1-GPU cfg4 block (strong_scaling_base)")
+    ap.add_argument("--exchange", default="allgather_rows", choices=["allgather_rows", "allgather_rank0", "own_tiles_host"],
+                    help="N > 1: how the result tiles reach host memory (SURVEY §8e asks for an A/B)")
     return ap.parse_args()
 
 
@@ -85,6 +91,19 @@ class ClockSampler:
         return out
 
 
+def config_of(spec, world):
+    """The workload as BOTH arms print it (identical keys and values: derived from the spec alone)."""
+    N, E, B = spec["samples"], spec["edges"], spec["bins"]
+    S = E * (B + 1)
+    ld = (N + 127) // 128 * 128
+    return {"workload": spec["name"], "samples": N, "edges": E, "placements_per_sample": spec["placements"], "bins": B,
+            "p": spec["p"], "segments": S, "pairs": N * (N - 1) // 2,
+            "l2": "inputs larger than L2 (dense matrix F = %.0f MB + split workspace)" % ((S + 15) // 16 * 16 * ld * 8 / 1e6),
+            "parallelism": "1 gpu" if world == 1 else
+                           f"strong scaling: cohort fixed, upper-triangular 128x128 tiles / {world} ranks, F replicated, NCCL all-gather "
+                           "of the result tiles, every rank copies its row block of the matrix to host memory"}
+
+
 def traffic_from_profile(spec, world):
     """dram__bytes_read.sum + dram__bytes_write.sum of the pair kernel per launch, from the committed
     `ncu --set full` capture of this workload (profiles/pair_kernel_traffic.json); None when there is none."""
@@ -96,35 +115,62 @@ def traffic_from_profile(spec, world):
         return None
 
 
-def cpu_reference_rate(tree, masses, p, bins, target_seconds, threads=0):
-    """Times the reference's own CPU implementation (oracle/_ref = compiled genesis, OpenMP over
-    all host threads) — or the C port when _ref is absent — on a bounded sample: the first n
-    samples of the same mass trees.  Returns dict(value pairs/s, cores, kind, sample)."""
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_reference(tree, masses, p, target_seconds, n_fixed=None):
+    """Times the reference's own CPU implementation (oracle/_ref = compiled genesis, OpenMP over ALL host threads —
+    the count is passed explicitly, torchrun exports OMP_NUM_THREADS=1) — or the C port when _ref is absent — on a
+    bounded sample: the first n samples of the same (binified) mass trees.
+    Returns (dict(value pairs/s, cores, kind, sample), matrix of those n samples)."""
     import oracle
     from gappa_b200 import workloads
     use_ref = oracle.have_ref()
     kind = "reference" if use_ref else "port"
-    cores = (oracle.ref().ref_max_threads() if use_ref else oracle.port().okrd_max_threads()) if threads == 0 else threads
+    cores = host_threads()
 
     def run(n):
         sub = workloads.head(masses, n)
         t0 = time.perf_counter()
         if use_ref:
-            _, sec = oracle.ref_matrix(tree, sub, p, bins=0, threads=threads)   # masses are already binified
+            D, sec = oracle.ref_matrix(tree, sub, p, bins=0, threads=cores)   # masses are already binified
         else:
-            oracle.port_matrix(tree, sub, p, bins=0, threads=threads)
+            D = oracle.port_matrix(tree, sub, p, bins=0, threads=cores)
             sec = time.perf_counter() - t0
-        return n * (n - 1) / 2 / sec, sec
+        return n * (n - 1) / 2 / sec, sec, D
 
     N = len(masses["off"]) - 1
-    n0 = min(N, max(2, 2 * int(np.sqrt(cores)) + 8))
-    rate, sec = run(n0)
-    n1 = int(min(N, max(n0, np.sqrt(2 * target_seconds * rate))))
-    if n1 > n0:
-        rate, sec = run(n1)
-        n0 = n1
+    n0 = min(N, n_fixed if n_fixed else max(2, 2 * int(np.sqrt(cores)) + 8))
+    rate, sec, D = run(n0)
+    if not n_fixed:
+        n1 = int(min(N, max(n0, np.sqrt(2 * target_seconds * rate))))
+        if n1 > n0:
+            rate, sec, D = run(n1)
+            n0 = n1
     return dict(value=rate, unit=UNIT, cores=int(cores), kind=kind,
-                sample=f"first {n0} of {N} samples = {n0 * (n0 - 1) // 2} pairs, {sec:.2f} s, earth_movers_distance(trees,p) only")
+                sample=f"first {n0} of {N} samples = {n0 * (n0 - 1) // 2} pairs, {sec:.2f} s, earth_movers_distance(trees,p) only"), D
+
+
+def parity_of(blocks, D_ref):
+    """max relative error of the timed results' leading block against the reference matrix of the same samples."""
+    n = D_ref.shape[0]
+    off = ~np.eye(n, dtype=bool)
+    out = {"vs": "reference (compiled genesis)" if __import__("oracle").have_ref() else "port", "pairs_checked": n * (n - 1) // 2}
+    worst = 0.0
+    for name, blk in blocks.items():
+        err = float(np.max(np.abs(blk[:n, :n][off] - D_ref[off]) / np.maximum(np.abs(D_ref[off]), 1e-300)))
+        out["max_rel_err_" + name] = err
+        worst = max(worst, err)
+    out["max_rel_err"] = worst
+    return out
+
+
+def default_workload(args, world):
+    return args.workload or ("cfg2" if world == 1 else "cfg4")
 
 
 def run_reference(args):
@@ -133,19 +179,15 @@ def run_reference(args):
     if rank != 0:
         return
     from gappa_b200 import workloads
-    spec = dict(workloads.WORKLOADS[args.workload])
-    for k in ("samples", "edges", "placements", "bins", "p"):
-        if getattr(args, k) is not None:
-            spec[k] = getattr(args, k)
     world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
-    if args.samples is None and world > 1:     # same weak-scaling rule as the b200 arm
-        spec["samples"] = int(round(spec["samples"] * np.sqrt(world) / 128.0)) * 128
+    name = default_workload(args, world)
+    spec = workloads.spec_of(name, samples=args.samples, edges=args.edges, placements=args.placements, bins=args.bins, p=args.p)
     # a bounded sample: only as many samples as the CPU can finish in a few seconds per step
     n_gen = min(spec["samples"], 160)
-    spec_b, tree, masses = workloads.build(args.workload, n_samples=n_gen, **{k: spec[k] for k in ("edges", "placements", "bins", "p")})
+    _, tree, masses = workloads.build(name, n_samples=n_gen, **{k: spec[k] for k in ("edges", "placements", "bins", "p")})
     rates, info = [], None
     for it in range(args.warmup + args.steps):
-        info = cpu_reference_rate(tree, masses, spec["p"], spec["bins"], target_seconds=max(1.0, args.cpu_seconds / max(args.steps, 1)))
+        info, _ = cpu_reference(tree, masses, spec["p"], target_seconds=max(1.0, args.cpu_seconds / max(args.steps, 1)))
         if it >= args.warmup:
             rates.append(info["value"])
     value = float(np.mean(rates))
@@ -154,202 +196,418 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": pairs_total / value * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, **spec, "note": "ms_per_step extrapolated linearly in pairs from the bounded sample"},
+        "higher_is_better": True, "scaling": "weak" if world == 1 else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": config_of(spec, world),
+        "note": "ms_per_step extrapolated linearly in pairs from the bounded sample; pairs/s of the CPU path does not depend on the cohort size",
         "cpu_baseline": info,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except (OSError, KeyError, ValueError):
+        return 6550.0, "fallback (B200_PROFILING.md copy bandwidth)"
+
+
+def rooflines(gappa_b200, local, spec, st, pairs, share, ms_step, world):
+    """Roofline of the dominant kernel (k_pairs: FP64 pipe) and of the F builder (K1: HBM)."""
+    S = st["n_segments"]
+    p = spec["p"]
+    flops = 3.0 * S * pairs * share                      # SURVEY §8d: 3 flop per (pair, segment)
+    t_pairs = st["ms_pairs"] * 1e-3
+    peak_dfma = gappa_b200.measure_fp64_peak(local, 0, 200.0)
+    peak_mix = gappa_b200.measure_fp64_peak(local, 1, 200.0)
+    peak_dmma = gappa_b200.measure_fp64_peak(local, 2, 200.0)
+    peak = max(peak_dfma, peak_dmma)
+    achieved = flops / t_pairs / 1e12
+    T = st["ld_samples"] // 128                          # executed: full tiles + 5/8 of each diagonal tile
+    executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((st["n_tiles"] - T) + 0.625 * T) * share
+    roof = {"bound": "fp64", "kernel": "k_pairs<p=%g>" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak, "traffic": traffic_from_profile(spec, world),
+            "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
+                           % (peak_dfma, peak_dmma),
+            "mix_ceiling": peak_mix, "frac_of_mix_ceiling": achieved / peak_mix,
+            "executed_tflops": executed / t_pairs / 1e12,
+            "ms_kernel": st["ms_pairs"], "ms_build_F": st["ms_build"], "ms_epilogue": st["ms_epilogue"],
+            "ctas": st["pair_ctas"], "split": st["split"]}
+    # the F builder (K1) is HBM-bound; algorithmic bytes per build (DESIGN.md K1): F written once + the tile-major entries
+    # (10 B each) + the passes over the E x ld subtree matrices
+    hp, hsrc = hbm_peak()
+    k1_bytes = float(st["f_bytes"]) + 10.0 * st["n_masses"] * K1_ENTRY_READS + 8.0 * K1_SUBTREE_PASSES * spec["edges"] * st["ld_samples"]
+    k1_gbs = k1_bytes / (st["ms_build"] * 1e-3) / 1e9 if st["ms_build"] > 0 else 0.0
+    k1 = {"bound": "hbm", "kernel": "K1 (k_tile<TOTALS>, k_subtree_level/top, k_tile<FILL>)", "achieved": k1_gbs,
+          "peak": hp, "unit": "GB/s", "frac": k1_gbs / hp, "bytes": k1_bytes,
+          "ms": st["ms_build"], "peak_source": hsrc, "share_of_step": st["ms_build"] / ms_step}
+    return roof, k1
+
+
+K1_ENTRY_READS = 2.0       # the tile-major entries are read by k_tile<TOTALS> and by k_tile<FILL>
+K1_SUBTREE_PASSES = 5.0    # T written, M read-modify-written, kids' M read, D written, D read
+
+
+def timed(torch, dist, stream, fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        fn()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms / steps
+
+
+def pinned(torch, a):
+    t = torch.from_numpy(a.view(np.int32) if a.dtype == np.uint32 else a)
+    return t.pin_memory()
+
+
+def measure_single(local, spec, tree, comp, steps, warmup, sample_clocks, e2e_steps):
+    """One GPU: `value` (resident masses -> matrix in host memory), `e2e` (host mass trees -> matrix in host memory),
+    the stats of the last device step, and the leading blocks of both results for the parity check."""
+    import torch
+    import gappa_b200
+    N, p, bins = spec["samples"], spec["p"], spec["bins"]
+    pairs = N * (N - 1) / 2
+    stream = torch.cuda.current_stream()
+    h_off, h_cell, h_mass = pinned(torch, comp["off"]), pinned(torch, comp["cell"]), pinned(torch, comp["mass"])
+    h_out = torch.empty((N, N), dtype=torch.float64).pin_memory()
+    h2d_bytes = sum(t.numel() * t.element_size() for t in (h_off, h_cell, h_mass))
+
+    plan = gappa_b200.KrdPlan(device=local, bins=bins)
+    plan.set_stream(stream.cuda_stream)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned(h_off.numpy(), h_cell, h_mass)
+    d_out = torch.empty((N, N), dtype=torch.float64, device="cuda")
+    # the end-to-end arm uses the library's pipelined ingest (krd_config.pipeline = 1): sample blocks cross PCIe while
+    # the blocks before them are prepared, built into F and paired.  Same calls, same host buffers.
+    plan_e2e = gappa_b200.KrdPlan(device=local, bins=bins, pipeline=1)
+    plan_e2e.set_stream(stream.cuda_stream)
+    plan_e2e.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+
+    def step_device():
+        plan.invalidate_F()
+        plan.compute_device(d_out, p=p)
+        h_out.copy_(d_out, non_blocking=True)
+
+    def step_e2e():
+        plan_e2e.set_masses_binned(h_off.numpy(), h_cell, h_mass)
+        plan_e2e.compute(p=p, out=h_out)
+
+    sampler = ClockSampler(local) if sample_clocks else None
+    ms_step = timed(torch, None, stream, step_device, steps, warmup)
+    st = plan.stats()
+    nb = min(N, 512)
+    blk_dev = h_out[:nb, :nb].numpy().copy()
+    clocks = None
+    if sampler:
+        # clocks: nvidia-smi samples every 20 ms; the timed region is tens of ms, so the same step keeps running (untimed)
+        # until the sampler has seen ~0.4 s of this load.  It is stopped before the e2e region: polling the driver that
+        # often delays the host-side submissions the e2e path depends on (measured +0.9 ms per step).
+        for _ in range(int(min(2000, max(1, 400.0 / max(ms_step, 0.05))))):
+            step_device()
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+    # the D2H term of `value` alone
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(3):
+        h_out.copy_(d_out, non_blocking=True)
+    e1.record(stream); torch.cuda.synchronize()
+    ms_d2h = e0.elapsed_time(e1) / 3
+    ms_e2e = timed(torch, None, stream, step_e2e, e2e_steps, 3)
+    blk_e2e = h_out[:nb, :nb].numpy().copy()
+    res = dict(N=N, pairs=pairs, ms_step=ms_step, ms_e2e=ms_e2e, ms_d2h=ms_d2h, st=st, clocks=clocks, h2d_bytes=int(h2d_bytes),
+               d2h_bytes=int(N * N * 8), blocks={"value_path": blk_dev, "e2e_path": blk_e2e}, launches=int(st["launches"]))
+    plan.close(); plan_e2e.close()
+    del d_out, h_out
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_single(args):
+    from gappa_b200 import workloads
+    import torch
+    import gappa_b200
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    ncpu = host_threads()
+    name = default_workload(args, 1)
+    over = dict(samples=args.samples, edges=args.edges, placements=args.placements, bins=args.bins, p=args.p)
+    spec, tree, comp = workloads.build_compact(name, workers=min(32, ncpu), n_samples=args.samples, cache=True, **over)
+    torch.cuda.set_device(local)
+    warmup = max(args.warmup, 3)
+    r = measure_single(local, spec, tree, comp, args.steps, warmup, True, max(2, min(args.steps, 5)))
+    st, pairs = r["st"], r["pairs"]
+    roof, k1 = rooflines(gappa_b200, local, spec, st, pairs, 1.0, r["ms_step"], 1)
+    line = {
+        "metric": METRIC, "value": pairs / (r["ms_step"] * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": warmup, "ms_per_step": r["ms_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": config_of(spec, 1),
+        "value_includes": "F build (K1) + pair kernel + epilogue + D2H of the n x n matrix into pinned host memory (%.3f ms of the step)" % r["ms_d2h"],
+        "masses": int(st["n_masses"]),
+        "e2e": {"value": pairs / (r["ms_e2e"] * 1e-3), "unit": UNIT, "ms_per_step": r["ms_e2e"],
+                "ingest": "krd_set_masses_binned (12 B per entry: cell = edge*bins+bin, mass) on a pipeline=1 handle: up to 8 sample blocks, "
+                          "upload overlapped with K0/K1/pair phases",
+                "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"]},
+        "gpu_launches": r["launches"] * args.steps,
+        "clocks": r["clocks"],
+        "roofline": roof, "roofline_build_F": k1,
+    }
+    blocks = r["blocks"]
+    del r
+    if not args.no_cpu_baseline:
+        full = workloads.expand(tree, workloads.head(comp, min(spec["samples"], 512)), spec["bins"])
+        info, D_ref = cpu_reference(tree, full, spec["p"], args.cpu_seconds)
+        line["cpu_baseline"] = info
+        line["parity"] = parity_of(blocks, D_ref)
+    del comp
+    # ---- the north-star's multi-GPU config on ONE GPU: the base of the strong-scaling numbers `--gpus N` prints ----
+    if not args.no_base and name == "cfg2" and args.samples is None:
+        try:
+            t0 = time.time()
+            spec4, tree4, comp4 = workloads.build_compact("cfg4", workers=min(32, ncpu), cache=True)
+            t_gen = time.time() - t0
+            r4 = measure_single(local, spec4, tree4, comp4, 3, 2, False, 2)
+            roof4, k14 = rooflines(gappa_b200, local, spec4, r4["st"], r4["pairs"], 1.0, r4["ms_step"], 1)
+            base = {"config": config_of(spec4, 1), "value": r4["pairs"] / (r4["ms_step"] * 1e-3), "unit": UNIT, "ms_per_step": r4["ms_step"],
+                    "steps": 3, "warmup": 2, "ms_d2h": r4["ms_d2h"], "masses": int(r4["st"]["n_masses"]),
+                    "e2e": {"value": r4["pairs"] / (r4["ms_e2e"] * 1e-3), "unit": UNIT, "ms_per_step": r4["ms_e2e"],
+                            "h2d_bytes_per_step": r4["h2d_bytes"], "d2h_bytes_per_step": r4["d2h_bytes"]},
+                    "roofline": {k: roof4[k] for k in ("achieved", "peak", "frac", "frac_of_mix_ceiling", "ms_kernel", "ms_build_F", "ms_epilogue")},
+                    "roofline_build_F": {k: k14[k] for k in ("achieved", "frac", "bytes", "ms")},
+                    "input_generation_s": t_gen}
+            if not args.no_cpu_baseline:
+                full4 = workloads.expand(tree4, workloads.head(comp4, 48), 1)
+                info4, D4 = cpu_reference(tree4, full4, 1.0, 0.0, n_fixed=48)
+                base["cpu_baseline"] = info4
+                base["parity"] = parity_of(r4["blocks"], D4)
+            line["strong_scaling_base"] = base
+        except Exception as ex:   # the headline line must survive a failure of the extra block
+            line["strong_scaling_base"] = {"error": repr(ex)[:300]}
+    print(json.dumps(line))
+
+
+def run_multi(args):
+    from gappa_b200 import workloads
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    ncpu = host_threads()
+    name = default_workload(args, world)
+    over = dict(samples=args.samples, edges=args.edges, placements=args.placements, bins=args.bins, p=args.p)
+    # inputs first (generation forks worker processes: before CUDA is touched); every rank generates 1/world of the samples
+    spec, tree, comp = workloads.build_compact(name, workers=max(1, min(32, ncpu // world)), n_samples=args.samples, rank=rank,
+                                               world=world, cache=True, **over)
+    N, p, bins = spec["samples"], spec["p"], spec["bins"]
+    pairs = N * (N - 1) / 2
+
+    import torch
+    import torch.distributed as dist
+    import gappa_b200
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stream = torch.cuda.current_stream()
+    cudart = torch.cuda.cudart()
+
+    # ---- the result in host memory: ONE n x n matrix in a shared segment, page-locked by every rank; rank r fills rows
+    # [r0, r1) over its own PCIe link ----
+    r0, r1 = rank * N // world, (rank + 1) * N // world
+    shm = "/dev/shm/krd_bench_out_%s" % os.environ.get("MASTER_PORT", "0")
+    if rank == 0:
+        with open(shm, "wb") as f:
+            f.truncate(N * N * 8)
+    dist.barrier()
+    h_full = torch.from_numpy(np.memmap(shm, dtype=np.float64, mode="r+", shape=(N, N)))
+    rc = cudart.cudaHostRegister(h_full.data_ptr(), N * N * 8, 0)
+    assert int(rc) == 0, f"cudaHostRegister failed: {rc}"
+    h_rows = h_full[r0:r1]
+
+    plan = gappa_b200.KrdPlan(device=local, bins=bins)
+    plan.set_stream(stream.cuda_stream)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+
+    # ---- sharded == single, bit for bit, on a 300-sample cohort (before anything is timed) ----
+    small = workloads.head(comp, min(N, 300))
+    ns = len(small["off"]) - 1
+    plan.set_masses_binned(small["off"], small["cell"], small["mass"])
+    sh = plan.shard_doubles(world)
+    dp = torch.empty(sh, dtype=torch.float64, device="cuda"); dg = torch.empty(sh * world, dtype=torch.float64, device="cuda")
+    plan.compute_shard(dp, rank, world, p=p)
+    dist.all_gather_into_tensor(dg, dp)
+    got = torch.full((ns, ns), -1.0, dtype=torch.float64, device="cuda")
+    plan.unpack_shards(dg, got, world)
+    one = torch.full((ns, ns), -2.0, dtype=torch.float64, device="cuda")
+    plan.compute_device(one, p=p)
+    torch.cuda.synchronize()
+    shard_ok = bool(torch.equal(got, one))
+    del dp, dg, got, one
+
+    # ---- the cohort ----
+    M = int(comp["off"][-1])
+    plan.set_masses_binned(comp["off"], comp["cell"], comp["mass"])     # (pageable source: one-time)
+    shard = plan.shard_doubles(world)
+    d_packed = torch.empty(shard, dtype=torch.float64, device="cuda")
+    d_gath = torch.empty(shard * world, dtype=torch.float64, device="cuda")
+    d_rows = torch.empty((r1 - r0, N), dtype=torch.float64, device="cuda")
+    d_out_full = torch.empty((N, N), dtype=torch.float64, device="cuda") if (args.exchange == "allgather_rank0" or rank == 0) else None
+    h_packed = None
+    if args.exchange == "own_tiles_host":
+        shm2 = shm + "_packed"
+        if rank == 0:
+            with open(shm2, "wb") as f:
+                f.truncate(shard * world * 8)
+        dist.barrier()
+        h_packed = torch.from_numpy(np.memmap(shm2, dtype=np.float64, mode="r+", shape=(world, shard)))
+        assert int(cudart.cudaHostRegister(h_packed.data_ptr(), shard * world * 8, 0)) == 0
+    # e2e ingest at N GPUs: every rank uploads 1/N of the mass entries over ITS PCIe link and the ranks all-gather the
+    # rest over NVLink (the one exchange step on the input side; F itself is built replicated)
+    per = (M + world - 1) // world
+    lo, hi = min(rank * per, M), min((rank + 1) * per, M)
+    h_cell = pinned(torch, np.ascontiguousarray(comp["cell"][lo:hi]))
+    h_mass = pinned(torch, np.ascontiguousarray(comp["mass"][lo:hi]))
+    off_np = np.ascontiguousarray(comp["off"], np.int64)
+    d_part = [torch.zeros(per, dtype=torch.int32, device="cuda"), torch.zeros(per, dtype=torch.float64, device="cuda")]
+    d_all = [torch.empty(per * world, dtype=torch.int32, device="cuda"), torch.empty(per * world, dtype=torch.float64, device="cuda")]
+    h2d_bytes = (hi - lo) * 12 + off_np.nbytes
+    copy_stream = torch.cuda.Stream()
+    up_events = [torch.cuda.Event() for _ in range(2)]
+    head_blk = workloads.head(comp, min(N, 64))
+    del comp
+
+    def exchange():
+        if args.exchange == "allgather_rows":
+            dist.all_gather_into_tensor(d_gath, d_packed)
+            plan.unpack_shards_rows(d_gath, d_rows, world, r0, r1)
+            h_rows.copy_(d_rows, non_blocking=True)
+        elif args.exchange == "allgather_rank0":        # round-1 variant: full unpack everywhere, one D2H over rank 0's link
+            dist.all_gather_into_tensor(d_gath, d_packed)
+            plan.unpack_shards(d_gath, d_out_full, world)
+            if rank == 0:
+                h_full.copy_(d_out_full, non_blocking=True)
+        else:                                           # no collective: own packed tiles to the host, unpacked there (untimed here)
+            h_packed[rank].copy_(d_packed, non_blocking=True)
+
+    def step_device():
+        plan.invalidate_F()
+        plan.compute_shard(d_packed, rank, world, p=p)
+        exchange()
+
+    def step_e2e():
+        srcs = (h_cell, h_mass)
+        copy_stream.wait_stream(stream)            # (the previous step's all-gathers have read d_part)
+        with torch.cuda.stream(copy_stream):
+            for k in (1, 0):                       # masses first: the all-gather left exposed after the last upload is the smaller array's
+                d_part[k][: hi - lo].copy_(srcs[k], non_blocking=True)
+                up_events[k].record(copy_stream)
+        for k in (1, 0):
+            stream.wait_event(up_events[k])
+            dist.all_gather_into_tensor(d_all[k], d_part[k])
+        plan.set_masses_binned_device(off_np, d_all[0], d_all[1])
+        plan.compute_shard(d_packed, rank, world, p=p)
+        exchange()
+        torch.cuda.synchronize()
+
+    warmup = max(args.warmup, 3)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms_step = timed(torch, dist, stream, step_device, args.steps, warmup)
+    st = plan.stats()
+    for _ in range(int(min(2000, max(1, 400.0 / max(ms_step, 0.05))))):    # (same count on every rank: ms_step is the max over ranks)
+        step_device()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    dist.barrier()
+    nb = min(N, 64)
+    blk_dev = None
+    ms_host_unpack = None
+    if rank == 0 and args.exchange != "own_tiles_host":
+        blk_dev = h_full[:nb, :nb].numpy().copy()
+    if args.exchange == "own_tiles_host" and rank == 0:
+        t0 = time.perf_counter()
+        Dh = gappa_b200.krd.unpack_shards_host(N, [h_packed[r].numpy() for r in range(world)])
+        ms_host_unpack = (time.perf_counter() - t0) * 1e3
+        blk_dev = Dh[:nb, :nb].copy()
+        del Dh
+    ms_e2e = timed(torch, dist, stream, step_e2e, max(2, min(args.steps, 5)), 3)
+    dist.barrier()
+    blk_e2e = h_full[:nb, :nb].numpy().copy() if (rank == 0 and args.exchange != "own_tiles_host") else None
+
+    # ---- the same cohort on ONE GPU of this job (rank 0; the others wait): the base of the strong-scaling ratio ----
+    one_gpu = None
+    if rank == 0:
+        h_one = torch.empty((N, N), dtype=torch.float64).pin_memory()
+
+        def step_one():
+            plan.invalidate_F()
+            plan.compute_device(d_out_full, p=p)
+            h_one.copy_(d_out_full, non_blocking=True)
+        ms_one = timed(torch, None, stream, step_one, 2, 1)
+        st1 = plan.stats()
+        same = bool(np.array_equal(h_one.numpy()[:nb, :nb], blk_dev)) if blk_dev is not None else None
+        one_gpu = {"value": pairs / (ms_one * 1e-3), "unit": UNIT, "ms_per_step": ms_one, "steps": 2, "warmup": 1,
+                   "ms_kernel": st1["ms_pairs"], "ms_build_F": st1["ms_build"],
+                   "note": "same cohort, same definition of value (incl. D2H of the whole matrix over one PCIe link), rank 0 alone",
+                   "leading_block_bit_identical_to_sharded": same}
+        del h_one
+    dist.barrier()
+
+    if rank == 0:
+        roof, k1 = rooflines(gappa_b200, local, spec, st, pairs, 1.0 / world, ms_step, world)
+        line = {
+            "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_of(spec, world),
+            "value_includes": "per rank: F build (K1, replicated) + pair kernel on its tile share + epilogue + exchange (%s) + D2H; max over ranks"
+                              % args.exchange,
+            "masses": int(st["n_masses"]),
+            "exchange": args.exchange, "ms_host_unpack_untimed": ms_host_unpack,
+            "shard_check": "sharded == single-GPU matrix bit for bit on the first %d samples: %s" % (ns, shard_ok),
+            "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "ingest": "every rank uploads 1/N of the compact entries (12 B each) on a copy stream, NVLink all-gather of the two arrays, "
+                              "K0 + K1 replicated, sharded pair kernel, exchange, per-rank D2H",
+                    "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int((r1 - r0) * N * 8)},
+            "one_gpu_same_job": one_gpu,
+            "gpu_launches": (int(st["launches"]) + 1) * args.steps,
+            "clocks": clocks,
+            "roofline": roof, "roofline_build_F": k1,
+        }
+        if not args.no_cpu_baseline and blk_dev is not None:
+            full = workloads.expand(tree, head_blk, bins)
+            info, D_ref = cpu_reference(tree, full, p, 0.0, n_fixed=nb)
+            line["parity"] = parity_of({"value_path": blk_dev, **({"e2e_path": blk_e2e} if blk_e2e is not None else {})}, D_ref)
+            line["parity"]["reference_sample"] = info["sample"]
+        print(json.dumps(line))
+    dist.barrier()
+    cudart.cudaHostUnregister(h_full.data_ptr())
+    dist.destroy_process_group()
+    if rank == 0:
+        for f in (shm, shm + "_packed"):
+            try:
+                os.unlink(f)
+            except OSError:
+                pass
 
 
 def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
-
-    rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-
-    # ---- inputs (host, before CUDA is touched: generation forks worker processes) ----
-    from gappa_b200 import workloads
-    ncpu = os.cpu_count() or 1
-    # Weak scaling: the cohort grows with the GPU count so that every GPU keeps the pair count of the 1-GPU
-    # workload (pairs ~ samples^2): samples = base * sqrt(world), rounded to whole 128-sample tiles.
-    n_samples = args.samples
-    scaling = "strong" if (args.samples is not None and world > 1) else "weak"   # --samples pins the cohort: total work fixed
-    if n_samples is None and world > 1:
-        base = workloads.WORKLOADS[args.workload]["samples"]
-        n_samples = int(round(base * np.sqrt(world) / 128.0)) * 128
-    spec, tree, masses = workloads.build(args.workload, workers=max(1, min(32, ncpu // world)), samples=n_samples,
-                                         edges=args.edges, placements=args.placements, bins=args.bins, p=args.p)
-    N, p, bins = spec["samples"], spec["p"], spec["bins"]
-    pairs = N * (N - 1) / 2
-
-    import torch
-    import gappa_b200
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    # pinned host copies of the mass trees (the e2e arm copies from these every step)
-    h_off = torch.from_numpy(masses["off"]).pin_memory()
-    h_edge = torch.from_numpy(masses["edge"]).pin_memory()
-    h_pos = torch.from_numpy(masses["pos"]).pin_memory()
-    h_mass = torch.from_numpy(masses["mass"]).pin_memory()
-    h_out = torch.empty((N, N) if rank == 0 else (1, 1), dtype=torch.float64).pin_memory()   # only rank 0 receives the matrix
-    h2d_bytes = sum(t.numel() * t.element_size() for t in (h_off, h_edge, h_pos, h_mass))
-
-    plan = gappa_b200.KrdPlan(device=local, bins=bins)
-    stream = torch.cuda.current_stream()
-    plan.set_stream(stream.cuda_stream)
-    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
-    plan.set_masses(h_off.numpy(), h_edge, h_pos, h_mass)
-    d_out = torch.empty((N, N), dtype=torch.float64, device="cuda")
-    plan_e2e = plan
     if world == 1:
-        # the end-to-end arm uses the library's pipelined ingest (krd_config.pipeline = 1): sample blocks cross PCIe while
-        # the blocks before them are prepared, built into F and paired.  Same calls, same host buffers.
-        plan_e2e = gappa_b200.KrdPlan(device=local, bins=bins, pipeline=1)
-        plan_e2e.set_stream(stream.cuda_stream)
-        plan_e2e.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
-    if world > 1:
-        shard = plan.shard_doubles(world)
-        d_packed = torch.empty(shard, dtype=torch.float64, device="cuda")
-        d_gath = torch.empty(shard * world, dtype=torch.float64, device="cuda")
-        # e2e ingest at N GPUs: every rank uploads 1/N of the mass entries over ITS PCIe link and the ranks
-        # all-gather the rest over NVLink (the one exchange step on the input side; F itself is built replicated)
-        M = int(h_edge.numel())
-        per = (M + world - 1) // world
-        lo, hi = min(rank * per, M), min((rank + 1) * per, M)
-        d_part = [torch.zeros(per, dtype=t.dtype, device="cuda") for t in (h_edge, h_pos, h_mass)]
-        d_full = [torch.empty(per * world, dtype=t.dtype, device="cuda") for t in (h_edge, h_pos, h_mass)]
-        h2d_bytes = (hi - lo) * 20 + h_off.numel() * 8
-        copy_stream = torch.cuda.Stream()
-        up_events = [torch.cuda.Event() for _ in range(3)]
-        up_order = (1, 2, 0)      # pos, mass, edge: the all-gather left exposed after the last upload is the smallest array's
-
-    def step_device():
-        plan.invalidate_F()
-        if world == 1:
-            plan.compute_device(d_out, p=p)
-        else:
-            plan.compute_shard(d_packed, rank, world, p=p)
-            dist.all_gather_into_tensor(d_gath, d_packed)
-            plan.unpack_shards(d_gath, d_out, world)
-
-    def step_e2e():
-        if world == 1:
-            plan_e2e.set_masses(h_off.numpy(), h_edge, h_pos, h_mass)
-            plan_e2e.compute(p=p, out=h_out)
-        else:
-            # uploads on a copy stream, array by array; the NVLink all-gather of array k runs under the upload of array k+1
-            srcs = (h_edge, h_pos, h_mass)
-            copy_stream.wait_stream(stream)            # (the previous step's all-gathers have read d_part)
-            with torch.cuda.stream(copy_stream):
-                for k in up_order:
-                    d_part[k][: hi - lo].copy_(srcs[k][lo:hi], non_blocking=True)
-                    up_events[k].record(copy_stream)
-            for k in up_order:
-                stream.wait_event(up_events[k])
-                dist.all_gather_into_tensor(d_full[k], d_part[k])
-            plan.set_masses_device(h_off.numpy(), d_full[0], d_full[1], d_full[2])
-            plan.compute_shard(d_packed, rank, world, p=p)
-            dist.all_gather_into_tensor(d_gath, d_packed)
-            plan.unpack_shards(d_gath, d_out, world)
-            if rank == 0:
-                h_out.copy_(d_out, non_blocking=True)
-            torch.cuda.synchronize()
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        torch.cuda.synchronize()
-        if dist:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            fn()
-        e1.record(stream)
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
-        if dist:
-            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms / steps
-
-    sampler = ClockSampler(local) if rank == 0 else None
-    ms_step = timed(step_device, args.steps, max(args.warmup, 3))
-    st = plan.stats()
-    # clocks: nvidia-smi samples every 20 ms; the timed region is tens of ms, so the same step keeps running (untimed) until
-    # the sampler has seen ~0.4 s of this load.  It is stopped before the e2e region: polling the driver that often delays
-    # the host-side submissions the e2e path depends on (measured +0.9 ms per step).
-    for _ in range(int(min(2000, max(1, 400.0 / max(ms_step, 0.05))))):    # (same count on every rank: ms_step is the max over ranks)
-        step_device()
-    torch.cuda.synchronize()
-    clocks = sampler.stop() if sampler else None
-    ms_e2e = timed(step_e2e, max(2, min(args.steps, 5)), 3)
-
-    if rank == 0:
-        # roofline of the dominant kernel (k_pairs): FP64 pipe
-        S = st["n_segments"]
-        share = 1.0 / world
-        flops = 3.0 * S * pairs * share                      # 3 flop per (pair, segment)
-        t_pairs = st["ms_pairs"] * 1e-3
-        peak_dfma = gappa_b200.measure_fp64_peak(local, 0, 200.0)
-        peak_mix = gappa_b200.measure_fp64_peak(local, 1, 200.0)
-        peak_dmma = gappa_b200.measure_fp64_peak(local, 2, 200.0)
-        peak = max(peak_dfma, peak_dmma)
-        achieved = flops / t_pairs / 1e12
-        T = st["ld_samples"] // 128                          # executed: full tiles + 5/8 of each diagonal tile
-        executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((st["n_tiles"] - T) + 0.625 * T) * share
-        line = {
-            "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": scaling,
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": spec["name"], "samples": N, "edges": spec["edges"], "placements_per_sample": spec["placements"],
-                       "bins": bins, "p": p, "segments": int(S), "pairs": int(pairs), "masses": int(st["n_masses"]),
-                       "l2": "inputs larger than L2 (F %.0f MB + split workspace)" % (st["f_bytes"] / 1e6),
-                       "parallelism": (f"upper-triangular tiles/{world}, F replicated, NCCL all-gather of result tiles; "
-                                       + (f"weak scaling: samples = {workloads.WORKLOADS[args.workload]['samples']}*sqrt({world}) "
-                                          "rounded to 128" if scaling == "weak" else "strong scaling: cohort fixed by --samples"))
-                                      if world > 1 else "1 gpu"},
-            "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "ingest": "pipelined (krd_config.pipeline=1): up to 8 sample blocks, upload overlapped with K0/K1/pair phases" if world == 1
-                              else "sharded upload (copy stream) + NVLink all-gather of the entries, array by array, overlapped",
-                    "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(N * N * 8)},
-            "gpu_launches": int(st["launches"]) * args.steps,
-            "clocks": clocks,
-            "roofline": {"bound": "fp64", "kernel": "k_pairs<p=%g>" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak, "traffic": traffic_from_profile(spec, world),
-                         "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
-                                        % (peak_dfma, peak_dmma),
-                         "mix_ceiling": peak_mix, "frac_of_mix_ceiling": achieved / peak_mix,
-                         "executed_tflops": executed / t_pairs / 1e12,
-                         "ms_kernel": st["ms_pairs"], "ms_build_F": st["ms_build"], "ms_epilogue": st["ms_epilogue"],
-                         "ctas": st["pair_ctas"], "split": st["split"]},
-        }
-        # second kernel group of the step: the F builder (K1) is HBM-bound; algorithmic bytes per build:
-        # F written once + the tile-major entries read twice (10 B each) + ~5 passes over the E x ld subtree matrices
-        try:
-            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]); hbm_src = "MEASURED_PEAKS.json hbm_gbs"
-        except (OSError, KeyError, ValueError):
-            hbm_peak, hbm_src = 6550.0, "fallback (B200_PROFILING.md copy bandwidth)"
-        k1_bytes = float(st["f_bytes"]) + 20.0 * st["n_masses"] + 40.0 * spec["edges"] * st["ld_samples"]
-        k1_gbs = k1_bytes / (st["ms_build"] * 1e-3) / 1e9 if st["ms_build"] > 0 else 0.0
-        line["roofline_build_F"] = {"bound": "hbm", "kernel": "K1 (k_tile<TOTALS>, k_subtree_level/top, k_tile<FILL>)", "achieved": k1_gbs,
-                                    "peak": hbm_peak, "unit": "GB/s", "frac": k1_gbs / hbm_peak, "bytes": k1_bytes,
-                                    "ms": st["ms_build"], "peak_source": hbm_src, "share_of_step": st["ms_build"] / ms_step}
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_reference_rate(tree, masses, p, bins, args.cpu_seconds)
-        print(json.dumps(line))
-    if dist:
-        dist.barrier()
-        dist.destroy_process_group()
+        return run_single(args)
+    return run_multi(args)
 
 
 if __name__ == "__main__":

@@ -16,6 +16,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PORT = os.path.join(_HERE, "libkrd_oracle.so")
+_TRUTH = os.path.join(_HERE, "libkrd_truth.so")
 _REF = os.path.join(_HERE, "_ref", "libkrd_ref.so")
 
 _i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
@@ -57,6 +58,34 @@ def port():
         L.okrd_max_threads.restype = C.c_int
         _port = L
     return _port
+
+
+_truth = None
+
+
+def truth_pairs(tree, mass, p, pairs, bins=0):
+    """binary128 ground truth (oracle/krd_truth.c) of the listed (a, b) pairs: canonicalise, optionally binify with the
+    port (so the masses are the doubles every implementation receives), exact-arithmetic walk.  Returns (value rounded
+    to double, residual value - double(value))."""
+    global _truth
+    if _truth is None:
+        if not os.path.exists(_TRUTH):
+            build(ref=False)
+        L = C.CDLL(_TRUTH)
+        L.okrd_truth_pairs.restype = C.c_int
+        L.okrd_truth_pairs.argtypes = [C.c_int, _i32p, _i32p, _f64p, C.c_int, C.c_int, _i64p, _i32p, _f64p, _f64p,
+                                       C.c_double, C.c_int64, _i32p, _i32p, _f64p, _f64p]
+        _truth = L
+    mc = canonicalize(mass)
+    if bins > 0:
+        mc = binify(tree, mc, bins)
+    pr = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+    a = np.ascontiguousarray(pr[:, 0]); b = np.ascontiguousarray(pr[:, 1])
+    out = np.zeros(len(pr)); lo = np.zeros(len(pr))
+    rc = _truth.okrd_truth_pairs(*_t(tree), *_m(mc), float(p), len(pr), a, b, out, lo)
+    if rc != 0:
+        raise RuntimeError("okrd_truth_pairs failed: %d" % rc)
+    return out, lo
 
 
 def have_ref():

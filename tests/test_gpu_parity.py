@@ -179,8 +179,7 @@ def test_tiled_builder_equals_general_builder(gb, n, E, P, bins):
     assert np.array_equal(res[0][1], res[1][1])
     assert np.max(np.abs(res[0][0] - res[1][0])) <= 1e-14
     assert rel_err(res[0][2], res[1][2]) <= 1e-12
-    # p < 1 amplifies ulp-level differences of F where two samples tie: sqrt(1e-16) = 1e-8
-    assert rel_err(res[0][3], res[1][3]) <= 1e-8
+    assert rel_err(res[0][3], res[1][3]) <= 1e-10    # p = 1/2 (random cohorts have no ties: tests/test_p_below_one.py)
 
 
 @pytest.mark.parametrize("p", [3.0, 4.0, 5.0, 6.0, 7.0, 8.0, 11.0, 16.0, 17.0, 2.5, 0.3, 0.75, 1.0000001])
@@ -193,8 +192,7 @@ def test_every_exponent_mode_vs_oracle(gb, oracle_mod, p):
     got = gb.earth_movers_distance(tree, mass, p=p, bins=3)
     want = oracle_mod.port_matrix(tree, mass, p=p, bins=3)
     off = ~np.eye(150, dtype=bool)
-    # p < 1 amplifies ulp-level ties of F
-    assert rel_err(got[off], want[off]) <= (TOL if p >= 1 else 1e-8)
+    assert rel_err(got[off], want[off]) <= TOL
     assert np.array_equal(got, got.T) and np.all(np.diag(got) == 0)
 
 

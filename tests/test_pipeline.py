@@ -35,10 +35,10 @@ def test_pipelined_equals_ordinary(n, bins):
     for p in (1.0, 0.5, 3.0, 2.0, 1.7):
         want = ref.compute(p=p)
         got = pip.compute(p=p)                    # first call: phased (p = 2 takes the Gram path: all blocks first)
-        assert _close(got, want, 1e-12 if p >= 1 else 1e-8), p
+        assert _close(got, want, 1e-12 if p >= 1 else 1e-10), p
         assert np.array_equal(got, got.T)
         again = pip.compute(p=p)                  # F valid, children resident: one launch over all tiles
-        assert _close(again, want, 1e-12 if p >= 1 else 1e-8)
+        assert _close(again, want, 1e-12 if p >= 1 else 1e-10)
         pip.invalidate_F()
         assert np.array_equal(pip.compute(p=p), again)    # rebuild + same schedule: bit-identical
         pip.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])   # next cohort: phased again
@@ -141,7 +141,7 @@ def test_pipelined_blocks_without_masses():
     pip = _plan(tree, sub, 3, pipeline=1)
     for p in (1.0, 0.5):
         want, got = ref.compute(p=p), pip.compute(p=p)
-        assert _close(got, want, 1e-12 if p >= 1 else 1e-8), p
+        assert _close(got, want, 1e-12 if p >= 1 else 1e-10), p
         assert np.all(got[640:768, 640:768] == 0.0)          # empty samples are at distance 0 from each other
         pip.set_masses(sub["off"], sub["edge"], sub["pos"], sub["mass"])
     ref.close(); pip.close()

@@ -39,7 +39,7 @@ def test_squash_matches_reference(bins, p):
     idx, dst = z["idx_" + key], z["dst_" + key]
     assert np.array_equal(m["index_a"], idx[:, 0]) and np.array_equal(m["index_b"], idx[:, 1])   # same merge sequence
     got = np.stack([m["distance_a"], m["distance_b"]], 1)
-    assert np.max(np.abs(got - dst) / np.maximum(dst, 1e-300)) <= (1e-10 if p >= 1 else 1e-8)   # p<1 amplifies ties, DESIGN.md
+    assert np.max(np.abs(got - dst) / np.maximum(dst, 1e-300)) <= 1e-10
     n = len(idx) + 1
     if p >= 1:
         assert krd.squash_tree_string([str(i) for i in range(n)], m) == str(z["tree_" + key])

@@ -96,6 +96,7 @@ krd_status krd_create(const krd_config* cfg, krd_handle** out)
     if (cfg) c = *cfg;
     if (c.device < 0 || c.device >= n_dev) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "device ordinal out of range");
     if (c.bins < 0) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "bins must be >= 0");
+    if (c.max_f_mb < 0) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "max_f_mb must be >= 0");
     cudaDeviceProp prop;
     if ((e = cudaSetDevice(c.device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, c.device)) != cudaSuccess)
         return cuda_fail(nullptr, e, "cudaSetDevice");
@@ -118,7 +119,8 @@ void krd_destroy(krd_handle* h)
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
     cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_kmeans); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
-    cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_edge_dec); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
+    cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_edge_dec); cudaFree(h->d_grow); cudaFree(h->d_cum); cudaFree(h->d_acc);
+    for (cudaEvent_t ev : h->slab_ev) cudaEventDestroy(ev); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
     cudaFree(h->d_flags);
@@ -270,7 +272,9 @@ static krd_status compute_impl(krd_handle* h, double p, double divisor, int rank
             // (a late child was not in MassTree order: the handle has been flattened, continue the ordinary way)
         }
     }
+    if (h->streamed) return compute_streamed(h, p, divisor, rank, world, d_out, d_packed);
     h->stats.launches = 0;
+    h->slabs_total = 0;
     cudaEventRecord(h->ev[0], h->stream);
     if (!h->F_valid) {
         krd_status st = build_F(h);
@@ -398,6 +402,14 @@ krd_status krd_get_stats(const krd_handle* hc, krd_stats* out)
         cudaEventElapsedTime(&h->stats.ms_build, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&h->stats.ms_pairs, h->ev[1], h->ev[2]);
         cudaEventElapsedTime(&h->stats.ms_epilogue, h->ev[2], h->ev[3]);
+        h->stats.ms_slabs = 0.f;
+        if (h->streamed && h->slabs_total > 0) {   // ev[1]..ev[2] spans all slabs: take the slab builds out of the pair time
+            float sum = 0.f, t = 0.f;
+            for (int b = 0; b < h->slabs_timed; ++b)
+                if (cudaEventElapsedTime(&t, h->slab_ev[(size_t)2 * b], h->slab_ev[(size_t)2 * b + 1]) == cudaSuccess) sum += t;
+            h->stats.ms_slabs = sum * (float)h->slabs_total / (float)std::max(h->slabs_timed, 1);
+            h->stats.ms_pairs = std::max(0.f, h->stats.ms_pairs - h->stats.ms_slabs);
+        }
     }
     cudaGetLastError();
     *out = h->stats;
@@ -434,7 +446,7 @@ krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const in
 krd_status krd_invalidate_F(krd_handle* h)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
-    h->F_valid = false;
+    h->F_valid = false; h->cum_valid = false;
     return KRD_OK;
 }
 

@@ -9,7 +9,9 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
+#include <cstdio>
 
 #include "krd_common.cuh"
 
@@ -356,6 +358,7 @@ static krd_status sort_edge_pos(krd_handle* h, uint32_t* perm /*M*/, uint32_t* s
 }
 
 static krd_status prepare_tiled(krd_handle* h);
+static krd_status prepare_exact(krd_handle* h);
 
 // Segment table of binned mode without any mass data (the parent of a pipelined ingest needs len / seg_off for the pair
 // kernel while its children hold the masses): same kernels as prepare_masses.
@@ -508,7 +511,9 @@ krd_status prepare_masses(krd_handle* h)
     h->stats.n_segments = h->S;
     h->stats.ld_samples = h->ld;
     h->stats.f_bytes = (int64_t)h->S_pad * h->ld * 8;
+    h->exact_fast = false; h->streamed = false; h->cum_valid = false;
     if (h->cfg.builder == 1) { h->tiled = false; return KRD_OK; }   // forced legacy builder (A/B tests)
+    if (h->cfg.bins == 0) { h->tiled = false; return prepare_exact(h); }
     return prepare_tiled(h);
 }
 
@@ -802,6 +807,30 @@ static krd_status prepare_tiled(krd_handle* h)
     return KRD_OK;
 }
 
+// M[e] = T[e] + D[e], D[e] = sum over child edges of M[kid] on the E x ldm matrices (T is in d_M on entry): one launch per
+// wide level, the narrow top of the tree in one launch.
+static krd_status subtree_passes(krd_handle* h, int64_t ldm, int* n_launch)
+{
+    const int L = (int)h->lvl_off.size() - 1;
+    const size_t smem_top = (size_t)2 * h->top_edges * TOP_COLS * 8 +
+                            (size_t)(2 * h->top_edges + 1 + h->top_kids + h->top_levels + 1) * 4;
+    const bool use_top = h->top_edges > 0 && smem_top <= 190 * 1024;   // (a huge multifurcation would not fit)
+    const int l_end = use_top ? h->top_level : L;
+    for (int l = 1; l < l_end; ++l, ++*n_launch) {   // level 0 = leaf edges: nothing below them
+        const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
+        dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ncols / 128));
+        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, ldm, h->d_M, h->d_D);
+    }
+    if (use_top) {
+        static std::atomic<unsigned long long> top_configured{0};
+        KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
+        k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
+                                                                                 ldm, h->d_M, h->d_D);
+        ++*n_launch;
+    }
+    return KRD_OK;
+}
+
 static krd_status build_F_tiled(krd_handle* h)
 {
     const int B1 = h->cfg.bins + 1;
@@ -814,24 +843,8 @@ static krd_status build_F_tiled(krd_handle* h)
     const int64_t ldm = h->ncols;   // stride of M / D: the handle's own columns (a pipelined child owns a slice of the parent's F)
     k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
                                                       nullptr, h->d_M, nullptr);
-    const int L = (int)h->lvl_off.size() - 1;
-    const size_t smem_top = (size_t)2 * h->top_edges * TOP_COLS * 8 +
-                            (size_t)(2 * h->top_edges + 1 + h->top_kids + h->top_levels + 1) * 4;
-    const bool use_top = h->top_edges > 0 && smem_top <= 190 * 1024;   // (a huge multifurcation would not fit)
-    const int l_end = use_top ? h->top_level : L;
     int n_launch = 2;
-    for (int l = 1; l < l_end; ++l, ++n_launch) {   // level 0 = leaf edges: nothing below them
-        const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
-        dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ncols / 128));
-        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, ldm, h->d_M, h->d_D);
-    }
-    if (use_top) {
-        static std::atomic<unsigned long long> top_configured{0};
-        KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
-        k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
-                                                                                 ldm, h->d_M, h->d_D);
-        ++n_launch;
-    }
+    { krd_status sp = subtree_passes(h, ldm, &n_launch); if (sp != KRD_OK) return sp; }
     k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
                                                      h->d_D, nullptr, h->d_F);
     KRD_CUDA(h, cudaGetLastError());
@@ -839,17 +852,245 @@ static krd_status build_F_tiled(krd_handle* h)
     return KRD_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+//  K1 exact (bins = 0): F written exactly once, whole or slab by slab
+// ------------------------------------------------------------------------------------------------
+//
+// In exact mode every distinct (edge, position) of ANY sample cuts a segment, so F has S ~ (number of mass entries) rows
+// while a column changes only where ITS sample has a mass: column i over edge e is piecewise constant with
+// (entries of i on e) + 1 pieces.  The builder therefore never scatters and scans; per entry it prepares
+//     grow[m] = seg_off[edge] + slot        the row of F at which the entry's mass starts to count (going proximal)
+//     cum[m]  = D[e][i] + masses of (i, e) at rows >= grow[m], summed distal -> proximal  (emd.cpp:141-166)
+// from the E x N subtree matrices (T -> M, D: the same level passes as the binned builder), and a row of F is then a pure
+// look-up:  F[r][i] = cum[m*] if the first entry m* of sample i with grow >= r lies on the edge of row r, else D[e(r)][i].
+// k_exact_slab sweeps a row range in order, one thread per sample column carrying its entry pointer in registers: one
+// binary search per (column, row range), one coalesced 512 B store per row and 64 columns, no read of F at all.
+// The same kernel fills the whole matrix (resident) or one slab of it (streamed, krd_config.max_f_mb).
+
+__global__ void k_exact_grow(const int32_t* __restrict__ edge, const int32_t* __restrict__ slot, const int32_t* __restrict__ seg_off,
+                             int64_t M, int32_t* __restrict__ grow)
+{
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < M) grow[m] = seg_off[edge[m]] + slot[m];
+}
+
+// The LAST entry of every (sample, edge) run walks its run distal -> proximal.  Entries of equal slot (duplicate
+// positions in the input) are one mass: summed in input order first, like the std::map's += (operators.cpp:169).
+//   CUM = false: T[e][i] = mass of sample i on edge e            (-> subtree passes)
+//   CUM = true : cum[m]  = D[e][i] + running sum                 (needs the finished D)
+template <bool CUM>
+__global__ void __launch_bounds__(256)
+k_exact_runs(const uint32_t* __restrict__ sid, const int64_t* __restrict__ off, const int32_t* __restrict__ edge,
+             const int32_t* __restrict__ slot, const double* __restrict__ mass, int64_t M, int64_t ldm,
+             const double* __restrict__ D, double* __restrict__ T, double* __restrict__ cum)
+{
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const uint32_t i = sid[m];
+    const int e = edge[m];
+    if (m + 1 < off[i + 1] && edge[m + 1] == e) return;      // not the last entry of its run
+    const int64_t lo = off[i];
+    double acc = CUM ? D[(int64_t)e * ldm + i] : 0.0;
+    int64_t q = m;
+    while (q >= lo && edge[q] == e) {
+        const int s = slot[q];
+        int64_t g0 = q;
+        while (g0 - 1 >= lo && edge[g0 - 1] == e && slot[g0 - 1] == s) --g0;
+        double sum = mass[g0];
+        for (int64_t k = g0 + 1; k <= q; ++k) sum += mass[k];
+        acc += sum;
+        if (CUM) for (int64_t k = g0; k <= q; ++k) cum[k] = acc;
+        q = g0 - 1;
+    }
+    if (!CUM) T[(int64_t)e * ldm + i] = acc;
+}
+
+constexpr int XS_COLS = 64;   // sample columns per CTA of k_exact_slab (one thread each)
+
+__global__ void __launch_bounds__(XS_COLS)
+k_exact_slab(const int64_t* __restrict__ off, const int32_t* __restrict__ grow, const int32_t* __restrict__ edge,
+             const double* __restrict__ cum, const int32_t* __restrict__ seg_off, int E, const double* __restrict__ D,
+             int64_t ldm, int N, int64_t S, int64_t row0, int64_t row1, int64_t rows_per_cta, double* __restrict__ F, int64_t ld)
+{
+    const int i = blockIdx.y * XS_COLS + threadIdx.x;
+    int64_t r = row0 + (int64_t)blockIdx.x * rows_per_cta;
+    const int64_t r_end = min(row1, r + rows_per_cta);
+    if (r >= r_end) return;
+    // edge of row r: the largest e with seg_off[e] <= r (rows >= S are the zero padding of the last chunk)
+    int e = E;
+    if (r < S) {
+        int lo = 0, hi = E;      // seg_off[lo] <= r < seg_off[hi]
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (seg_off[mid] <= r) lo = mid; else hi = mid; }
+        e = lo;
+    }
+    int64_t e_end = (e < E) ? (int64_t)seg_off[e + 1] : INT64_MAX;
+    const bool col = i < N;
+    double d = (col && e < E) ? D[(int64_t)e * ldm + i] : 0.0;
+    // first entry of this sample with grow >= r
+    int64_t m = 0, m_end = 0;
+    if (col) {
+        m = off[i]; m_end = off[i + 1];
+        int64_t lo = m, hi = m_end;
+        while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (grow[mid] < r) lo = mid + 1; else hi = mid; }
+        m = lo;
+    }
+    int64_t g_next = INT64_MAX; int e_next = -1; double c_next = 0.0;
+    if (m < m_end) { g_next = grow[m]; e_next = edge[m]; c_next = cum[m]; }
+    double* out = F + (r - row0) * ld + i;
+    for (; r < r_end; ++r, out += ld) {
+        if (r >= e_end) {        // (every edge owns at least one row)
+            ++e;
+            e_end = (e < E) ? (int64_t)seg_off[e + 1] : INT64_MAX;
+            d = (col && e < E) ? D[(int64_t)e * ldm + i] : 0.0;
+        }
+        while (g_next < r) {
+            ++m;
+            if (m < m_end) { g_next = grow[m]; e_next = edge[m]; c_next = cum[m]; }
+            else { g_next = INT64_MAX; e_next = -1; }
+        }
+        *out = (r < S && col) ? ((e_next == e) ? c_next : d) : 0.0;
+    }
+}
+
+krd_status needs_resident_F(krd_handle* h)
+{
+    char msg[320];
+    std::snprintf(msg, sizeof msg, "this operation needs the dense matrix F resident (%.2f GB for %lld segments x %d samples); "
+                  "it is being streamed in slabs - use --bins, fewer samples, or raise krd_config.max_f_mb",
+                  (double)h->S_pad * h->ld * 8 / 1e9, (long long)h->S, h->N);
+    return fail(h, KRD_ERR_STATE, msg);
+}
+
+// K0 part: per-entry rows, buffers, and the resident / streamed decision
+static krd_status prepare_exact(krd_handle* h)
+{
+    h->exact_fast = false; h->streamed = false; h->cum_valid = false; h->slab_rows = 0;
+    if (h->cfg.bins != 0 || h->cfg.builder == 1 || h->E == 0 || h->N == 0 || h->ld_fixed) return KRD_OK;
+    const size_t Mx = (size_t)std::max<int64_t>(h->M, 1);
+    krd_status st;
+    if ((st = reserve(h, (void**)&h->d_grow, Mx * 4)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_cum, Mx * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;
+    if (h->M > 0) k_exact_grow<<<nblk(h->M), 256, 0, h->stream>>>(h->d_edge, h->d_slot, h->d_seg_off, h->M, h->d_grow);
+    KRD_CUDA(h, cudaGetLastError());
+    // resident or streamed?
+    size_t free_b = 0, total_b = 0;
+    KRD_CUDA(h, cudaMemGetInfo(&free_b, &total_b));
+    free_b += h->F_capacity;                                       // (our own old F is reusable)
+    const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
+    const size_t cap = h->cfg.max_f_mb > 0 ? (size_t)h->cfg.max_f_mb << 20 : (size_t)(0.6 * (double)free_b);
+    if (need > cap) {
+        if (h->extra_cols > 0) return needs_resident_F(h);
+        const size_t row_bytes = (size_t)h->ld * sizeof(double);
+        size_t slab = h->cfg.max_f_mb > 0 ? cap : std::min(cap, std::max<size_t>((size_t)256 << 20, std::min<size_t>((size_t)2 << 30, free_b / 4)));
+        int64_t rows = (int64_t)(slab / row_bytes) / KC * KC;
+        if (rows < KC) rows = KC;
+        h->streamed = true;
+        h->slab_rows = std::min<int64_t>(rows, h->S_pad);
+        h->stats.f_bytes = (int64_t)h->slab_rows * h->ld * 8;
+    }
+    h->exact_fast = true;
+    return KRD_OK;
+}
+
+// T -> M, D -> cum: everything of the exact builder that does not depend on the row range
+static krd_status exact_prefix(krd_handle* h, int* n_launch)
+{
+    const int64_t ldm = h->ncols;
+    zero_words(h->d_M, ldm, ldm, h->E, h->stream);
+    zero_words(h->d_D, ldm, ldm, h->E, h->stream);
+    *n_launch = 2;
+    if (h->M > 0) {
+        k_exact_runs<false><<<nblk(h->M), 256, 0, h->stream>>>(h->d_sid, h->d_off, h->d_edge, h->d_slot, h->d_mass, h->M, ldm, nullptr, h->d_M, nullptr);
+        ++*n_launch;
+    }
+    krd_status st = subtree_passes(h, ldm, n_launch);
+    if (st != KRD_OK) return st;
+    if (h->M > 0) {
+        k_exact_runs<true><<<nblk(h->M), 256, 0, h->stream>>>(h->d_sid, h->d_off, h->d_edge, h->d_slot, h->d_mass, h->M, ldm, h->d_D, nullptr, h->d_cum);
+        ++*n_launch;
+    }
+    KRD_CUDA(h, cudaGetLastError());
+    h->cum_valid = true;
+    return KRD_OK;
+}
+
+static krd_status exact_rows(krd_handle* h, int64_t row0, int64_t row1, double* F)
+{
+    const int64_t rows = row1 - row0;
+    const int col_groups = (int)(h->ld / XS_COLS);
+    const int64_t want_ctas = (int64_t)h->num_sms * 32;            // 32 CTAs of 64 threads per SM
+    int64_t parts = std::max<int64_t>(1, want_ctas / col_groups);
+    int64_t rpc = std::max<int64_t>(32, (rows + parts - 1) / parts);
+    parts = (rows + rpc - 1) / rpc;
+    dim3 grid((unsigned)parts, (unsigned)col_groups);
+    k_exact_slab<<<grid, XS_COLS, 0, h->stream>>>(h->d_off, h->d_grow, h->d_edge, h->d_cum, h->d_seg_off, h->E, h->d_D, h->ncols, h->N,
+                                                  h->S, row0, row1, rpc, F, h->ld);
+    KRD_CUDA(h, cudaGetLastError());
+    return KRD_OK;
+}
+
+static krd_status ensure_F_buffer(krd_handle* h, size_t need)
+{
+    if (need <= h->F_capacity) return KRD_OK;
+    cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
+    krd_status sa = alloc_sized(h, (void**)&h->d_F, need, "the dense cumulative-mass matrix F (segments x samples x 8 B)");
+    if (sa != KRD_OK) return sa;
+    h->F_capacity = need;
+    return KRD_OK;
+}
+
+// Streamed exact mode: slab after slab, the pair kernel accumulates per-tile sums across the slabs (krd_pairs.cu).
+krd_status compute_streamed(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed)
+{
+    krd_status st = ensure_F_buffer(h, (size_t)h->slab_rows * h->ld * sizeof(double));
+    if (st != KRD_OK) return st;
+    h->stats.launches = 0;
+    cudaEventRecord(h->ev[0], h->stream);
+    if (!h->cum_valid) {
+        int nl = 0;
+        if ((st = exact_prefix(h, &nl)) != KRD_OK) return st;
+        h->stats.launches += nl;
+    }
+    cudaEventRecord(h->ev[1], h->stream);
+    const int64_t n_slabs = (h->S_pad + h->slab_rows - 1) / h->slab_rows;
+    constexpr int TIMED = 32;
+    while ((int)h->slab_ev.size() < 2 * TIMED) { cudaEvent_t ev; KRD_CUDA(h, cudaEventCreate(&ev)); h->slab_ev.push_back(ev); }
+    h->slabs_timed = (int32_t)std::min<int64_t>(n_slabs, TIMED); h->slabs_total = (int32_t)n_slabs;
+    for (int64_t b = 0; b < n_slabs; ++b) {
+        const int64_t row0 = b * h->slab_rows, row1 = std::min(h->S_pad, row0 + h->slab_rows);
+        if (b < TIMED) cudaEventRecord(h->slab_ev[(size_t)2 * b], h->stream);
+        if ((st = exact_rows(h, row0, row1, h->d_F)) != KRD_OK) return st;
+        if (b < TIMED) cudaEventRecord(h->slab_ev[(size_t)2 * b + 1], h->stream);
+        SlabArgs slab{h->d_F, row0, row1 - row0, b == 0, b == n_slabs - 1};
+        if ((st = run_pairs_slab(h, p, divisor, rank, world, d_out, d_packed, slab)) != KRD_OK) return st;
+        h->stats.launches += 1;
+    }
+    cudaEventRecord(h->ev[3], h->stream);
+    return KRD_OK;
+}
+
 krd_status build_F(krd_handle* h)
 {
     h->norms_valid = false;
+    if (h->streamed) return needs_resident_F(h);
     const size_t need = (size_t)h->S_pad * h->ld * sizeof(double);
     if (h->ld_fixed) {   // child of a pipelined ingest: d_F points into the parent's matrix
         if (!h->d_F || !h->tiled) return fail(h, KRD_ERR_STATE, "pipelined child without a tiled builder");
-    } else if (need > h->F_capacity) {
-        cudaFree(h->d_F); h->d_F = nullptr; h->F_capacity = 0;
-        krd_status sa = alloc_sized(h, (void**)&h->d_F, need, "the dense cumulative-mass matrix F (segments x samples x 8 B)");
+    } else {
+        krd_status sa = ensure_F_buffer(h, need);
         if (sa != KRD_OK) return sa;
-        h->F_capacity = need;
+    }
+    if (h->exact_fast) {
+        int nl = 0;
+        krd_status st = exact_prefix(h, &nl);
+        if (st == KRD_OK) st = exact_rows(h, 0, h->S_pad, h->d_F);
+        if (st != KRD_OK) return st;
+        h->build_launches = nl + 1;
+        h->F_valid = true;
+        return KRD_OK;
     }
     if (h->tiled) {
         krd_status st = build_F_tiled(h);

@@ -106,6 +106,17 @@ struct krd_handle {
     void*    d_flags = nullptr;    // K0: canonical-order / range check flags
     double*  d_D = nullptr;        // E x ncols: mass strictly below every edge (sum of its child edges' M)
 
+    // ---- exact mode (bins = 0): single-write builder and segment-axis streaming, krd_build.cu "K1 exact" ----
+    bool     exact_fast = false;   // the resident masses can use the single-write exact builder
+    int32_t* d_grow = nullptr;     // M: global segment (row of F) of every entry = seg_off[edge] + slot
+    double*  d_cum = nullptr;      // M: value of F at that row for the entry's sample (mass below the edge + own masses at or above)
+    bool     cum_valid = false;    // d_M / d_D / d_cum describe the resident masses
+    bool     streamed = false;     // F does not fit: d_F is ONE slab of slab_rows rows, rebuilt slab after slab inside every compute
+    int64_t  slab_rows = 0;
+    double*  d_acc = nullptr;      // streamed: per-tile sums carried from slab to slab
+    std::vector<cudaEvent_t> slab_ev;   // (begin, end) of the first slab builds of the last streamed compute (timing only)
+    int32_t  slabs_timed = 0, slabs_total = 0;
+
     // ---- pair kernel workspace ----
     double* d_ws = nullptr;
     size_t  ws_capacity = 0;
@@ -182,10 +193,16 @@ void launch_rebase_off(const int64_t* d_src, int n, int64_t* d_dst, cudaStream_t
 krd_status build_tree(krd_handle* h);                 // host preprocessing + upload
 krd_status prepare_masses(krd_handle* h);             // canonical order, slots, segment table
 krd_status build_F(krd_handle* h);                    // K1
+krd_status needs_resident_F(krd_handle* h);           // the sized error of a streamed handle asked for something that needs all of F
 
 // krd_pairs.cu
 krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int world,
                      double* d_out_matrix, double* d_out_packed);
+// One slab of a streamed compute: rows [row0, row0 + rows) of F are at `F`; the per-tile sums are carried in h->d_acc.
+struct SlabArgs { const double* F; int64_t row0, rows; bool first, last; };
+krd_status run_pairs_slab(krd_handle* h, double p, double divisor, int rank, int world, double* d_out_matrix, double* d_out_packed,
+                          const SlabArgs& slab);
+krd_status compute_streamed(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed);   // krd_build.cu
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
 krd_status unpack_shard_rows(krd_handle* h, const double* d_gathered, int row0, int row1, double* d_out_rows);
 

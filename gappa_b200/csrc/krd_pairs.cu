@@ -450,6 +450,8 @@ struct EpiParams {
     int4* fix;          // Gram mode: pairs whose Gram difference cancelled too much; fix[0].x = count, entries from fix[1]
     int fix_cap;
     int split;          // CTAs per tile (row bands of 128 / split rows ... 16384 / split cells)
+    double* acc;        // streamed exact mode: per-tile sums carried across the slabs ([n_tiles][TILE*TILE]), else nullptr
+    int acc_first, acc_last;   // first slab: acc is not read; last slab: the sum is finished (root, divisor, mirror) instead of stored
 };
 
 // |a-b|^2 = |a|^2 + |b|^2 - 2ab loses  eps * (|a|^2+|b|^2) / |a-b|^2  relative accuracy.  Cells below this
@@ -467,8 +469,9 @@ __global__ void __launch_bounds__(256) k_epilogue(const EpiParams P)
     const double inv_p = 1.0 / P.p;
     const int BAND = TILE * TILE / P.split;
     for (int idx = band * BAND + threadIdx.x; idx < (band + 1) * BAND; idx += blockDim.x) {
-        double v = 0.0;
+        double v = (P.acc && !P.acc_first) ? P.acc[(size_t)t * (TILE * TILE) + idx] : 0.0;
         for (int s = i0; s < i1; ++s) v += P.ws[(size_t)s * (size_t)(TILE * TILE) + idx];
+        if (P.acc && !P.acc_last) { P.acc[(size_t)t * (TILE * TILE) + idx] = v; continue; }
         const int r = idx / TILE, c = idx % TILE;
         const int64_t i = (int64_t)tile.i * TILE + r, j = (int64_t)tile.j * TILE + c;
         if (P.norm) {   // |a-b|^2 from the Gram entry
@@ -712,8 +715,9 @@ static cudaError_t launch_pairs(const PairParams& P, int grid, cudaStream_t stre
 }
 
 static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int rank, int world,
-                                 double* d_out_matrix, double* d_out_packed, bool allow_gram)
+                                 double* d_out_matrix, double* d_out_packed, bool allow_gram, const SlabArgs* slab = nullptr)
 {
+    if (slab) allow_gram = false;    // (the Gram path needs whole-column norms)
     krd_status st = ensure_tiles(h);
     if (st != KRD_OK) return st;
     const int64_t n_tiles_all = h->n_tiles_alloc;
@@ -722,7 +726,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     krd_rank_tiles(n_tiles_all, rank, world, &t0, &t1);
     if (h->force_t0 >= 0) { t0 = h->force_t0; t1 = h->force_t1; }   // pipelined ingest: one phase of the phase-major list
     const int n_tiles = (int)(t1 - t0);
-    if (d_out_packed && n_tiles < per_rank)   // ragged tail: keep the all-gather payload defined
+    if (d_out_packed && n_tiles < per_rank && (!slab || slab->last))   // ragged tail: keep the all-gather payload defined
         KRD_CUDA(h, cudaMemsetAsync(d_out_packed + (size_t)n_tiles * TILE * TILE, 0, (size_t)(per_rank - n_tiles) * TILE * TILE * 8, h->stream));
     h->stats.pair_ctas = 0;
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
@@ -745,7 +749,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
     if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
 
-    const int n_chunks = (int)(h->S_pad / KC);
+    const int n_chunks = (int)((slab ? slab->rows : h->S_pad) / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
     const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 4096 + (int64_t)(diag_cost * 2048.0);
     if (key != h->sched_key) {
@@ -782,7 +786,8 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
 
     PairParams P;
     P.center = h->d_center;
-    P.F = h->d_F; P.len = (mode == MODE_P2) ? h->d_sqrt_len : h->d_len;
+    P.F = slab ? slab->F : h->d_F;
+    P.len = ((mode == MODE_P2) ? h->d_sqrt_len : h->d_len) + (slab ? slab->row0 : 0);
     P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p;
     cudaError_t e;
     switch (mode) {
@@ -807,6 +812,12 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     Q.ws = h->d_ws; Q.tiles = h->d_tiles + t0; Q.tile_item_off = d_tile_off; Q.n_tiles = n_tiles; Q.N = h->N;
     Q.p = p; Q.divisor = divisor; Q.out = d_out_matrix; Q.packed = d_out_packed;
     Q.norm = nullptr; Q.fix = nullptr; Q.fix_cap = 0;
+    Q.acc = nullptr; Q.acc_first = Q.acc_last = 1;
+    if (slab && !(slab->first && slab->last)) {
+        krd_status sa = reserve(h, (void**)&h->d_acc, (size_t)n_tiles * TILE * TILE * sizeof(double));
+        if (sa != KRD_OK) return sa;
+        Q.acc = h->d_acc; Q.acc_first = slab->first; Q.acc_last = slab->last;
+    }
     if (mode == MODE_P2G) {
         krd_status sf = reserve(h, (void**)&h->d_fix, (size_t)(FIX_CAP + 1) * sizeof(int4));
         if (sf != KRD_OK) return sf;
@@ -843,6 +854,12 @@ krd_status run_pairs(krd_handle* h, double p, double divisor, int rank, int worl
     h->stats.gram_fixups = (cnt > FIX_CAP) ? -1 : cnt;
     if (cnt <= FIX_CAP) return KRD_OK;
     return run_pairs_once(h, p, divisor, rank, world, d_out_matrix, d_out_packed, false);
+}
+
+krd_status run_pairs_slab(krd_handle* h, double p, double divisor, int rank, int world, double* d_out_matrix, double* d_out_packed,
+                          const SlabArgs& slab)
+{
+    return run_pairs_once(h, p, divisor, rank, world, d_out_matrix, d_out_packed, false, &slab);
 }
 
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out)

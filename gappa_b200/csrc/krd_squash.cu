@@ -145,10 +145,17 @@ static void launch_ova(krd_handle* h, int c, double p, int64_t rpc, double* part
 krd_status run_squash(krd_handle* h, double p, krd_merger* out)
 {
     const int N = h->N, Nt = 2 * N - 1;
+    if (h->streamed) return needs_resident_F(h);
     if (h->ld < Nt) {     // widen F: one extra column per merged cluster, then redo the (resident) masses' preparation
         h->extra_cols = N;
         krd_status st = prepare_masses(h);
-        if (st != KRD_OK) return st;
+        if (st != KRD_OK) {      // (e.g. the widened matrix no longer fits: back to the plain layout, the handle stays usable)
+            const std::string msg = h->err;
+            h->extra_cols = 0;
+            if (prepare_masses(h) != KRD_OK) h->have_masses = false;
+            h->err = msg;
+            return st;
+        }
     }
     if (!h->F_valid) { krd_status st = build_F(h); if (st != KRD_OK) return st; }
 

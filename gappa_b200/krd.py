@@ -34,7 +34,7 @@ EXPORTS = [
 
 class KrdConfig(C.Structure):
     _fields_ = [("device", C.c_int), ("bins", C.c_int), ("split", C.c_int), ("builder", C.c_int),
-                ("p2_mode", C.c_int), ("pipeline", C.c_int), ("reserved", C.c_int * 2)]
+                ("p2_mode", C.c_int), ("pipeline", C.c_int), ("max_f_mb", C.c_int), ("reserved", C.c_int * 1)]
 
 
 class KrdStats(C.Structure):
@@ -42,7 +42,7 @@ class KrdStats(C.Structure):
                 ("n_segments", C.c_int64), ("ld_samples", C.c_int64), ("f_bytes", C.c_int64),
                 ("n_tiles", C.c_int64), ("split", C.c_int32), ("pair_ctas", C.c_int32),
                 ("levels", C.c_int32), ("launches", C.c_int32), ("ms_build", C.c_float),
-                ("ms_pairs", C.c_float), ("ms_epilogue", C.c_float), ("reserved_f", C.c_float),
+                ("ms_pairs", C.c_float), ("ms_epilogue", C.c_float), ("ms_slabs", C.c_float),
                 ("gram_fixups", C.c_int32), ("reserved_i", C.c_int32)]
 
     def as_dict(self):
@@ -159,10 +159,10 @@ def _ptr(a):
 class KrdPlan:
     """One handle of the C ABI: tree + masses resident in HBM, distance matrices on demand."""
 
-    def __init__(self, device=0, bins=0, split=0, builder=0, p2_mode=0, pipeline=0):
+    def __init__(self, device=0, bins=0, split=0, builder=0, p2_mode=0, pipeline=0, max_f_mb=0):
         self._L = lib()
         self._h = C.c_void_p()
-        cfg = KrdConfig(device=device, bins=bins, split=split, builder=builder, p2_mode=p2_mode, pipeline=pipeline)
+        cfg = KrdConfig(device=device, bins=bins, split=split, builder=builder, p2_mode=p2_mode, pipeline=pipeline, max_f_mb=max_f_mb)
         st = self._L.krd_create(C.byref(cfg), C.byref(self._h))
         if st != KRD_OK:
             raise KrdError(st, self._L.krd_last_error(None).decode())

@@ -67,7 +67,13 @@ typedef struct krd_config {
                           entries are not in MassTree order makes the call start over on the ordinary, sorting path).  Results agree with the ordinary path to rounding (different partial-sum
                           splits).  Sharded compute is not available on such a handle; krd_squash / krd_kmeans /
                           introspection first turn it into an ordinary one. */
-    int reserved[2];   /* must be 0 */
+    int max_f_mb;      /* exact mode (bins = 0): cap, in MiB, on the resident dense matrix F (0 = auto: 60 % of the free device
+                          memory).  F has one row per segment, S = n_edges + #distinct (edge, position) over all samples, so
+                          it outgrows HBM quickly (1,000 samples x 30k positions: 245 GB).  Beyond the cap the segment axis is
+                          STREAMED: only the n_edges x n subtree-mass matrices stay resident, F is rebuilt slab after slab
+                          inside every krd_compute* and the pair kernel accumulates over the slabs.  krd_squash / krd_kmeans /
+                          krd_debug_copy_F need the resident form and fail with a sized message otherwise. */
+    int reserved[1];   /* must be 0 */
 } krd_config;
 
 typedef struct krd_stats {
@@ -83,7 +89,7 @@ typedef struct krd_stats {
     float   ms_build;       /* device time of the F builder in the last compute (CUDA events) */
     float   ms_pairs;       /* device time of the pair kernel alone in the last compute */
     float   ms_epilogue;    /* device time of the split-sum / root / mirror epilogue */
-    float   reserved_f;
+    float   ms_slabs;       /* streamed exact mode: device time of the slab builds inside the last compute (ms_pairs excludes it) */
     int32_t gram_fixups;    /* exponent 2, Gram path: pairs recomputed directly because |a|^2+|b|^2-2ab cancelled
                                (-1: more than the list holds; the launch was repeated on the direct path by the library) */
     int32_t reserved_i;

@@ -34,7 +34,7 @@ def test_compact_form_equals_full_form(n, E, P, bins, pipeline):
     comp.set_masses_binned(b["off"], cell, b["mass"])
     for p in (1.0, 0.5, 2.0):
         Df, Dc = full.compute(p=p), comp.compute(p=p)
-        if pipeline and p != 2.0:      # phased: different partial-sum splits (DESIGN.md "Pipelined ingest")
+        if pipeline:                   # phase-major tile order: different partial-sum splits (DESIGN.md "Pipelined ingest")
             assert rel_err(Dc, Df) <= (1e-12 if p >= 1 else 1e-10)
         else:
             assert np.array_equal(Dc, Df), p

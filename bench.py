@@ -399,6 +399,79 @@ def run_single(args):
     print(json.dumps(line))
 
 
+def run_exact(args):
+    """--workload exact1k (bins = 0, exact positions): the mode `gappa analyze krd` runs.  S ~ number of mass entries, so
+    the dense matrix does not fit and the library streams the segment axis in slabs (DESIGN.md "Exact mode")."""
+    from gappa_b200 import workloads
+    import torch
+    import gappa_b200
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    name = default_workload(args, 1)
+    spec, tree, masses = workloads.build(name, workers=min(32, host_threads()), n_samples=args.samples, samples=args.samples,
+                                         edges=args.edges, placements=args.placements, p=args.p)
+    N, p = spec["samples"], spec["p"]
+    pairs = N * (N - 1) / 2
+    torch.cuda.set_device(local)
+    stream = torch.cuda.current_stream()
+    h = [pinned(torch, masses[k]) for k in ("off", "edge", "pos", "mass")]
+    h_out = torch.empty((N, N), dtype=torch.float64).pin_memory()
+    plan = gappa_b200.KrdPlan(device=local, bins=0)
+    plan.set_stream(stream.cuda_stream)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(h[0].numpy(), h[1], h[2], h[3])
+    d_out = torch.empty((N, N), dtype=torch.float64, device="cuda")
+
+    def step_device():
+        plan.invalidate_F()
+        plan.compute_device(d_out, p=p)
+        h_out.copy_(d_out, non_blocking=True)
+
+    def step_e2e():
+        plan.set_masses(h[0].numpy(), h[1], h[2], h[3])
+        plan.compute(p=p, out=h_out)
+
+    steps, warmup = max(1, min(args.steps, 3)), 1
+    sampler = ClockSampler(local)
+    ms_step = timed(torch, None, stream, step_device, steps, warmup)
+    clocks = sampler.stop()
+    st = plan.stats()
+    nb = min(N, 256)
+    blk = h_out[:nb, :nb].numpy().copy()
+    ms_e2e = timed(torch, None, stream, step_e2e, 2, 1)
+    blk2 = h_out[:nb, :nb].numpy().copy()
+    S = st["n_segments"]
+    spec_cfg = config_of(spec, 1)
+    spec_cfg["segments"] = int(S)
+    spec_cfg["l2"] = "inputs larger than L2 (F is streamed: %.0f MB slabs of a %.0f GB matrix)" % (st["f_bytes"] / 1e6, S * st["ld_samples"] * 8 / 1e9)
+    peak_dfma = gappa_b200.measure_fp64_peak(local, 0, 200.0); peak_mix = gappa_b200.measure_fp64_peak(local, 1, 200.0)
+    peak_dmma = gappa_b200.measure_fp64_peak(local, 2, 200.0)
+    peak = max(peak_dfma, peak_dmma)
+    achieved = 3.0 * S * pairs / (st["ms_pairs"] * 1e-3) / 1e12
+    hp, hsrc = hbm_peak()
+    slab_gbs = S * st["ld_samples"] * 8.0 / (st["ms_slabs"] * 1e-3) / 1e9 if st["ms_slabs"] > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": pairs / (ms_step * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": spec_cfg, "masses": int(st["n_masses"]),
+        "value_includes": "per-entry cumulative values (T, subtree passes, cum) + every slab of F built and paired + epilogue + D2H",
+        "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "ingest": "krd_set_masses (20 B per entry) + K0 exact (radix sort of the (edge, pos) keys, segment table)",
+                "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in h)), "d2h_bytes_per_step": int(N * N * 8)},
+        "gpu_launches": int(st["launches"]) * steps, "clocks": clocks,
+        "roofline": {"bound": "fp64", "kernel": "k_pairs<p=%g> over all slabs" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": achieved / peak, "traffic": None, "mix_ceiling": peak_mix, "frac_of_mix_ceiling": achieved / peak_mix,
+                     "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s" % (peak_dfma, peak_dmma),
+                     "ms_kernel": st["ms_pairs"], "ms_prefix": st["ms_build"], "ms_slabs": st["ms_slabs"]},
+        "roofline_build_F": {"bound": "hbm", "kernel": "k_exact_slab (F written once, slab by slab)", "achieved": slab_gbs, "peak": hp, "unit": "GB/s",
+                             "frac": slab_gbs / hp, "bytes": S * st["ld_samples"] * 8.0, "ms": st["ms_slabs"], "peak_source": hsrc,
+                             "share_of_step": st["ms_slabs"] / ms_step},
+    }
+    if not args.no_cpu_baseline:
+        info, D_ref = cpu_reference(tree, workloads.head(masses, nb), p, args.cpu_seconds)
+        line["cpu_baseline"] = info
+        line["parity"] = parity_of({"value_path": blk, "e2e_path": blk2}, D_ref)
+    print(json.dumps(line))
+
+
 def run_multi(args):
     from gappa_b200 import workloads
     rank = int(os.environ.get("RANK", "0"))
@@ -606,6 +679,9 @@ def main():
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world == 1:
+        from gappa_b200 import workloads
+        if workloads.WORKLOADS[default_workload(args, 1)]["bins"] == 0 and not args.bins:
+            return run_exact(args)
         return run_single(args)
     return run_multi(args)
 

@@ -27,6 +27,10 @@ WORKLOADS = {
     "cfg4": dict(samples=10_000, edges=49_999, placements=100_000, bins=1, p=1.0),
     "cfg5": dict(samples=20_000, edges=19_999, placements=100_000, bins=1, p=0.5),
     "tiny": dict(samples=200, edges=999, placements=2000, bins=4, p=1.0),
+    # exact positions (what `gappa analyze krd` runs without --bins): SURVEY's CPU probe shape at 1,000 samples; the dense matrix
+    # would hold ~3e7 segments x 1,024 columns = 245 GB, so the segment axis is streamed (krd_config.max_f_mb)
+    "exact1k": dict(samples=1000, edges=9999, placements=30_000, bins=0, p=1.0),
+    "exact_tiny": dict(samples=150, edges=999, placements=3000, bins=0, p=1.0),
 }
 
 
@@ -96,6 +100,11 @@ def expand(tree, compact, bins):
 def _gen_chunk(args):
     tree, first, count, placements, bins, seed = args
     return compact_samples(tree, first, count, placements, bins, seed)
+
+
+def _gen_raw(args):
+    tree, first, count, placements, seed = args
+    return synth.sample_masses(tree, count, placements, seed=seed, first_sample=first)
 
 
 def _generate(tree, first, count, spec, seed, workers):
@@ -182,7 +191,21 @@ def build(name=None, seed=42, first_sample=0, n_samples=None, workers=None, **ov
     workers = workers or min(os.cpu_count() or 1, 32)
     if spec["bins"] > 0:
         return spec, tree, expand(tree, _generate(tree, first_sample, n, spec, seed, workers), spec["bins"])
-    raw = synth.sample_masses(tree, n, spec["placements"], seed=seed, first_sample=first_sample)
+    chunk = max(1, min(32, (n + workers - 1) // workers))
+    jobs = [(tree, first_sample + s0, min(chunk, n - s0), spec["placements"], seed) for s0 in range(0, n, chunk)]
+    if workers > 1 and len(jobs) > 1:
+        with ProcessPoolExecutor(max_workers=workers) as ex:
+            parts = list(ex.map(_gen_raw, jobs))
+    else:
+        parts = [_gen_raw(j) for j in jobs]
+    off = np.zeros(n + 1, np.int64)
+    k = 0
+    for prt in parts:
+        c = len(prt["off"]) - 1
+        off[k + 1:k + c + 1] = off[k] + prt["off"][1:]
+        k += c
+    raw = dict(off=off, edge=np.concatenate([q["edge"] for q in parts]), pos=np.concatenate([q["pos"] for q in parts]),
+               mass=np.concatenate([q["mass"] for q in parts]))
     return spec, tree, raw
 
 

@@ -4,7 +4,7 @@ HBM) against the resident form and against the port, through the C ABI on a B200
 import numpy as np
 import pytest
 
-from conftest import rel_err
+from conftest import assert_matches_reference_p_below_one, rel_err
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-10
@@ -30,7 +30,6 @@ def test_exact_builder_equals_legacy_builder(n, E, P):
     assert Fa.shape == Fb.shape and np.max(np.abs(Fa - Fb), initial=0.0) <= 1e-14
     for p in (1.0, 2.0, 3.0):
         assert rel_err(a.compute(p=p), b.compute(p=p)) <= 1e-12, p
-    assert a.stats()["launches"] < b.stats()["launches"] or P == 0
     a.close(); b.close()
 
 
@@ -54,6 +53,9 @@ def test_streamed_equals_resident_and_port(n, E, P, mb, oracle_mod):
         assert np.array_equal(Ds, Ds.T) and np.all(np.diag(Ds) == 0)
         assert rel_err(Ds, Dr) <= (1e-12 if p >= 1 else 1e-10), p
         assert np.array_equal(st.compute(p=p), Ds)                      # run-to-run bit identity
+        if p < 1:     # tiny trees tie: port first, else the binary128 truth within the tie bound
+            assert_matches_reference_p_below_one(tree, mass, sub, p, 0, Ds[np.ix_(sub, sub)])
+            continue
         want = oracle_mod.port_matrix(tree, subm, p=p)
         assert rel_err(Ds[np.ix_(sub, sub)], want) <= TOL, p
     assert st.stats()["ms_slabs"] > 0

@@ -124,7 +124,7 @@ void krd_destroy(krd_handle* h)
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
     for (void* q : h->d_scratch) cudaFree(q);
     cudaFree(h->d_flags);
-    cudaFree(h->d_ws); for (auto& kv : h->scheds) cudaFree(kv.second.d); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp);
+    cudaFree(h->d_ws); for (auto& kv : h->scheds) cudaFree(kv.second.d); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp); cudaFree(h->d_shard); cudaFree(h->d_gathered);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     delete h;
 }

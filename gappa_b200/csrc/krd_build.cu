@@ -635,7 +635,7 @@ template <bool FILL>
 __global__ void __launch_bounds__(256)
 k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, const int64_t* __restrict__ tile_ptr,
        int N, int64_t ld, int64_t ldm, int E, int EB, int B1, const double* __restrict__ Dsub, double* __restrict__ Msub,
-       double* __restrict__ F)
+       double* __restrict__ F, const int32_t* __restrict__ kid_off, int64_t zero_row_off)
 {
     extern __shared__ double tile[];   // [rows][FTS]
     const int b = blockIdx.x, i0 = blockIdx.y * FT;
@@ -691,8 +691,9 @@ k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, cons
         const double* dcol = Dsub + (int64_t)e0 * ldm + i0 + il;
         for (int el = eg; el < ne; el += 2 * (256 / FT)) {
             const int el2 = el + 256 / FT;
-            double acc = dcol[(int64_t)el * ldm];
-            double acc2 = (el2 < ne) ? dcol[(int64_t)el2 * ldm] : 0.0;
+            // (leaf edges have nothing below them: their D row is never read)
+            double acc = (kid_off[e0 + el + 1] > kid_off[e0 + el]) ? dcol[(int64_t)el * ldm] : 0.0;
+            double acc2 = (el2 < ne && kid_off[e0 + el2 + 1] > kid_off[e0 + el2]) ? dcol[(int64_t)el2 * ldm] : 0.0;
             double* t = tile + (size_t)el * B1 * FTS + il;
             for (int s = B1 - 1; s >= 0; --s) { acc += t[s * FTS]; t[s * FTS] = acc; }
             if (el2 < ne) {
@@ -707,6 +708,7 @@ k_tile(const uint16_t* __restrict__ cell, const double* __restrict__ tmass, cons
     for (int k = tid; k < rows * FT; k += 256) {
         const int r = k / FT, cc = k % FT;
         dst[(int64_t)r * ldo + cc] = tile[r * FTS + cc];
+        if (!FILL && zero_row_off) dst[(int64_t)r * ldo + zero_row_off + cc] = 0.0;   // bins = 1: the D row of the edge, inside F
     }
 }
 
@@ -784,9 +786,10 @@ static krd_status prepare_tiled(krd_handle* h)
     if ((st = reserve(h, (void**)&h->d_cell, (size_t)std::max<int64_t>(h->M, 1) * 2)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_tmass, (size_t)std::max<int64_t>(h->M, 1) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_tile_ptr, (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
-    if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;   // E x ncols (stride ncols)
-    if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;
-    zero_words(h->d_D, h->ncols, h->ncols, h->E, h->stream);   // leaf edges: nothing below
+    if (B1 != 2) {   // (bins = 1 keeps M and D inside F: build_F_tiled)
+        if ((st = reserve(h, (void**)&h->d_M, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;   // E x ncols (stride ncols)
+        if ((st = reserve(h, (void**)&h->d_D, (size_t)h->E * h->ncols * 8)) != KRD_OK) return st;   // (leaf rows are never read)
+    }
     // scratch lives in the handle (grow-only): no cudaMalloc/cudaFree, no host sync on this path
     if ((st = reserve(h, &h->d_scratch[0], (size_t)(n_slices + h->N) * 8)) != KRD_OK) return st;
     if ((st = reserve(h, &h->d_scratch[1], (size_t)(n_slices + 1) * 8)) != KRD_OK) return st;
@@ -809,8 +812,9 @@ static krd_status prepare_tiled(krd_handle* h)
 
 // M[e] = T[e] + D[e], D[e] = sum over child edges of M[kid] on the E x ldm matrices (T is in d_M on entry): one launch per
 // wide level, the narrow top of the tree in one launch.
-static krd_status subtree_passes(krd_handle* h, int64_t ldm, int* n_launch)
+static krd_status subtree_passes(krd_handle* h, int64_t ldm, int* n_launch, double* Msub = nullptr, double* Dsub = nullptr)
 {
+    if (!Msub) { Msub = h->d_M; Dsub = h->d_D; }
     const int L = (int)h->lvl_off.size() - 1;
     const size_t smem_top = (size_t)2 * h->top_edges * TOP_COLS * 8 +
                             (size_t)(2 * h->top_edges + 1 + h->top_kids + h->top_levels + 1) * 4;
@@ -819,13 +823,13 @@ static krd_status subtree_passes(krd_handle* h, int64_t ldm, int* n_launch)
     for (int l = 1; l < l_end; ++l, ++*n_launch) {   // level 0 = leaf edges: nothing below them
         const int cnt = h->lvl_off[l + 1] - h->lvl_off[l];
         dim3 g2((unsigned)std::min(cnt, 1 << 20), (unsigned)(h->ncols / 128));
-        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, ldm, h->d_M, h->d_D);
+        k_subtree_level<<<g2, 128, 0, h->stream>>>(h->d_lvl_edges, h->lvl_off[l], cnt, h->d_kid_off, h->d_kid_edge, ldm, Msub, Dsub);
     }
     if (use_top) {
         static std::atomic<unsigned long long> top_configured{0};
         KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
         k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
-                                                                                 ldm, h->d_M, h->d_D);
+                                                                                 ldm, Msub, Dsub);
         ++*n_launch;
     }
     return KRD_OK;
@@ -840,13 +844,27 @@ static krd_status build_F_tiled(krd_handle* h)
     if (h->S_pad > h->S)   // rows past the last segment feed the pair kernel's last chunk: keep them zero (own columns only)
         zero_words(h->d_F + (size_t)h->S * h->ld, h->ld, h->ncols, h->S_pad - h->S, h->stream);
     dim3 grid((unsigned)h->n_eblocks, (unsigned)(h->ncols / FT));
+    if (B1 == 2) {
+        // bins = 1: edge e owns the rows 2e = M[e] (mass at its proximal end) and 2e+1 = D[e] (mass below it) — F IS the pair
+        // of subtree matrices, interleaved.  The totals go straight into the even rows (zeros into the odd ones) and the
+        // subtree passes run on F itself with a row stride of two: no separate M / D, no fill pass (4.5 instead of ~7.5
+        // passes over E x ld at cfg4 / cfg5, the multi-GPU configs).
+        const int64_t ld2 = 2 * h->ld;
+        k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ld2, h->E, h->EB, B1,
+                                                          nullptr, h->d_F, nullptr, h->d_kid_off, h->ld);
+        int n_launch = 1;
+        { krd_status sp = subtree_passes(h, ld2, &n_launch, h->d_F, h->d_F + h->ld); if (sp != KRD_OK) return sp; }
+        KRD_CUDA(h, cudaGetLastError());
+        h->build_launches = n_launch;
+        return KRD_OK;
+    }
     const int64_t ldm = h->ncols;   // stride of M / D: the handle's own columns (a pipelined child owns a slice of the parent's F)
     k_tile<false><<<grid, 256, smem_tot, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
-                                                      nullptr, h->d_M, nullptr);
+                                                      nullptr, h->d_M, nullptr, h->d_kid_off, 0);
     int n_launch = 2;
     { krd_status sp = subtree_passes(h, ldm, &n_launch); if (sp != KRD_OK) return sp; }
     k_tile<true><<<grid, 256, smem_fill, h->stream>>>(h->d_cell, h->d_tmass, h->d_tile_ptr, h->N, h->ld, ldm, h->E, h->EB, B1,
-                                                     h->d_D, nullptr, h->d_F);
+                                                     h->d_D, nullptr, h->d_F, h->d_kid_off, 0);
     KRD_CUDA(h, cudaGetLastError());
     h->build_launches = n_launch;   // totals + level passes + top-of-tree + fill
     return KRD_OK;

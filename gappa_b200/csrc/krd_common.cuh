@@ -146,6 +146,8 @@ struct krd_handle {
     std::vector<cudaGraphExec_t> phase_exec;     // executable graph of every phase, updated in place call after call
     bool capturing = false;                      // inside a stream capture (a phase of the pipelined ingest): no timing events
     int64_t n_tiles_alloc = 0;
+    double* d_shard = nullptr;    // krd_compute_allgather: this rank's packed tiles ...
+    double* d_gathered = nullptr; // ... and all ranks' after the NCCL all-gather
     double* d_out_tmp = nullptr;  // device N*N for krd_compute (host out)
     double* d_out_tmp_sq = nullptr;   // squash clustering: initial N*N distances
     void*   d_squash = nullptr;       // squash clustering state (distance matrix of 2N-1 clusters, counts, mergers, ...)

@@ -12,7 +12,9 @@
 //        [--ignore-multiplicities] [--out-dir d] [--file-prefix s] [--file-suffix s]  -> k_<k>_assignments.csv, overview.csv
 //        (gappa src/commands/analyze/kmeans_phylogenetic.cpp:134-199; additive: --seed n, --init-centroids i,j,...)
 //   additive: --krd-exponent (alias), --bins B (mass_tree_binify_masses first), --device d, --gpus G (analyze krd: tiles
-//             sharded over devices d..d+G-1, one host thread per GPU),
+//             sharded over devices d..d+G-1, one host thread per GPU; --exchange nccl (default: NCCL all-gather of the
+//             result tiles over NVLink, every GPU then copies its row block of the matrix to the host) | host (no
+//             collective: every GPU copies its own packed tiles to the host, unpacked there)),
 //             --write-binary f (raw row-major doubles, for full-precision comparisons)
 //
 // Exit code 0 on success; on error prints "Error: <message>" like src/main.cpp:167-173 and exits 1.
@@ -49,6 +51,7 @@ struct KrdOptions {
     std::string out_dir = ".", prefix, suffix, matrix_format = "matrix", log_file, write_binary;
     bool compress = false, omit_labels = false, allow_overwrite = false, verbose = false;
     int threads = 0, bins = 0, device = 0, gpus = 1;
+    std::string exchange = "nccl";
 };
 
 const char* kUsage =
@@ -64,7 +67,7 @@ const char* kUsage =
     "  --seed INT  --init-centroids LIST (phylogenetic-kmeans, additive) k-means++ seed / explicit start samples.\n"
     "Matrix Output:\n  --out-dir TEXT=.  --file-prefix TEXT  --file-suffix TEXT  --compress\n"
     "  --matrix-format TEXT=matrix       matrix | list | triangular\n  --omit-matrix-labels\n"
-    "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --gpus INT  --help\n";
+    "Global Options:\n  --allow-file-overwriting  --verbose  --threads UINT  --log-file TEXT  --device INT  --gpus INT  --exchange nccl|host  --help\n";
 
 [[noreturn]] void usage_error(const std::string& msg)
 {
@@ -130,6 +133,7 @@ KrdOptions parse_args(int argc, char** argv)
         else if (a == "--bins") o.bins = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--device") o.device = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
         else if (a == "--gpus") o.gpus = number([](const std::string& s, size_t* u) { return std::stoi(s, u); });
+        else if (a == "--exchange") o.exchange = value();
         else if (a == "--write-binary") o.write_binary = value();
         else if (a == "--k") o.ks = value();
         else if (a == "--write-overview-file") o.overview_file = true;
@@ -146,6 +150,7 @@ KrdOptions parse_args(int argc, char** argv)
     parse_matrix_format(o.matrix_format);   // validates
     if (o.bins < 0) usage_error("--bins: must be >= 0");
     if (o.gpus < 1 || o.gpus > 64) usage_error("--gpus: must be in 1..64");
+    if (o.exchange != "nccl" && o.exchange != "host") usage_error("--exchange: must be nccl or host");
     if (o.threads <= 0) {
         o.threads = (int)std::thread::hardware_concurrency();
         if (o.threads <= 0) o.threads = 1;
@@ -246,19 +251,44 @@ int run_krd(const KrdOptions& o, Log& log)
         workers.clear();
         auto cleanup = [&]() { for (auto* h : hs) if (h) krd_destroy(h); };
         for (const auto& e : errors) if (!e.empty()) { cleanup(); throw std::runtime_error(e); }
-        shard = krd_shard_doubles(hs[0], G);
-        packed.assign((size_t)shard * (size_t)G, 0.0);
-        // phase 2: every GPU computes and returns its share
-        for (int g = 0; g < G; ++g) workers.emplace_back([&, g]() {
-            try {
-                check_krd(hs[(size_t)g], krd_compute_shard_host(hs[(size_t)g], o.exponent, divisor, g, G, packed.data() + (size_t)g * (size_t)shard));
-                krd_get_stats(hs[(size_t)g], &stats[(size_t)g]);
-            } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
-        });
-        for (auto& w : workers) w.join();
-        cleanup();
-        for (const auto& e : errors) if (!e.empty()) throw std::runtime_error(e);
-        if (krd_unpack_shards_host(n, G, packed.data(), matrix.data()) != KRD_OK) throw std::runtime_error("krd_unpack_shards_host failed");
+        if (o.exchange == "nccl") {
+            // phase 2 (default): every GPU computes its share, the packed tiles are all-gathered with NCCL over NVLink and
+            // every GPU copies ITS row block of the finished matrix to the host over its own PCIe link
+            std::vector<void*> comms((size_t)G, nullptr);
+            std::vector<int32_t> devs((size_t)G);
+            for (int g = 0; g < G; ++g) devs[(size_t)g] = o.device + g;
+            if (krd_nccl_init_all(G, devs.data(), comms.data()) != KRD_OK) {
+                const std::string msg = krd_last_error(nullptr);
+                cleanup();
+                throw std::runtime_error(msg + " (use --exchange host to run without NCCL)");
+            }
+            for (int g = 0; g < G; ++g) workers.emplace_back([&, g]() {
+                try {
+                    const int32_t r0 = (int32_t)((int64_t)g * n / G), r1 = (int32_t)((int64_t)(g + 1) * n / G);
+                    check_krd(hs[(size_t)g], krd_compute_allgather_host(hs[(size_t)g], o.exponent, divisor, g, G, comms[(size_t)g], r0, r1,
+                                                                        matrix.data() + (size_t)r0 * (size_t)n));
+                    krd_get_stats(hs[(size_t)g], &stats[(size_t)g]);
+                } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
+            });
+            for (auto& w : workers) w.join();
+            krd_nccl_destroy(G, comms.data());
+            cleanup();
+            for (const auto& e : errors) if (!e.empty()) throw std::runtime_error(e);
+        } else {
+            shard = krd_shard_doubles(hs[0], G);
+            packed.assign((size_t)shard * (size_t)G, 0.0);
+            // phase 2 (--exchange host): every GPU computes and returns its own packed tiles; no collective
+            for (int g = 0; g < G; ++g) workers.emplace_back([&, g]() {
+                try {
+                    check_krd(hs[(size_t)g], krd_compute_shard_host(hs[(size_t)g], o.exponent, divisor, g, G, packed.data() + (size_t)g * (size_t)shard));
+                    krd_get_stats(hs[(size_t)g], &stats[(size_t)g]);
+                } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
+            });
+            for (auto& w : workers) w.join();
+            cleanup();
+            for (const auto& e : errors) if (!e.empty()) throw std::runtime_error(e);
+            if (krd_unpack_shards_host(n, G, packed.data(), matrix.data()) != KRD_OK) throw std::runtime_error("krd_unpack_shards_host failed");
+        }
         st = stats[0];
         for (const auto& q : stats) { st.ms_pairs = std::max(st.ms_pairs, q.ms_pairs); st.ms_build = std::max(st.ms_build, q.ms_build); }
     }

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -105,6 +105,14 @@ def lib():
     L.krd_set_masses_binned_device.argtypes = [vp, i32, vp, vp, vp]
     L.krd_unpack_shards_rows.restype = C.c_int
     L.krd_unpack_shards_rows.argtypes = [vp, i32, vp, i32, i32, vp]
+    L.krd_compute_allgather.restype = C.c_int
+    L.krd_compute_allgather.argtypes = [vp, dbl, dbl, i32, i32, vp, i32, i32, vp]
+    L.krd_compute_allgather_host.restype = C.c_int
+    L.krd_compute_allgather_host.argtypes = [vp, dbl, dbl, i32, i32, vp, i32, i32, vp]
+    L.krd_nccl_init_all.restype = C.c_int
+    L.krd_nccl_init_all.argtypes = [i32, vp, vp]
+    L.krd_nccl_destroy.restype = None
+    L.krd_nccl_destroy.argtypes = [i32, vp]
     L.krd_compute.restype = C.c_int
     L.krd_compute.argtypes = [vp, dbl, dbl, vp]
     L.krd_compute_device.restype = C.c_int
@@ -238,6 +246,13 @@ class KrdPlan:
     def unpack_shards_rows(self, d_gathered, d_out_rows, world, row0, row1):
         self._check(self._L.krd_unpack_shards_rows(self._h, world, _ptr(d_gathered), int(row0), int(row1), _ptr(d_out_rows)))
 
+    def compute_allgather_host(self, rank, world, comm, row0, row1, p=1.0, divisor=1.0, out_rows=None):
+        """krd_compute_allgather_host: this rank's tile share, NCCL all-gather (comm = ncclComm_t as int), rows [row0, row1) on the host."""
+        if out_rows is None:
+            out_rows = np.zeros((row1 - row0, self.n_samples), np.float64)
+        self._check(self._L.krd_compute_allgather_host(self._h, float(p), float(divisor), rank, world, C.c_void_p(comm), row0, row1, _ptr(out_rows)))
+        return out_rows
+
     def compute(self, p=1.0, divisor=1.0, out=None):
         """Host result (numpy n x n)."""
         n = self.n_samples
@@ -340,6 +355,21 @@ def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):
         return plan.compute(p=p, divisor=divisor)
     finally:
         plan.close()
+
+
+def nccl_init_all(devices):
+    """ncclCommInitAll for devices of this process (krd_nccl_init_all): list of communicators (ints)."""
+    devs = np.ascontiguousarray(devices, np.int32)
+    comms = (C.c_void_p * len(devs))()
+    st = lib().krd_nccl_init_all(len(devs), _ptr(devs), C.cast(comms, C.c_void_p))
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
+    return [int(c) for c in comms]
+
+
+def nccl_destroy(comms):
+    arr = (C.c_void_p * len(comms))(*comms)
+    lib().krd_nccl_destroy(len(comms), C.cast(arr, C.c_void_p))
 
 
 def measure_fp64_peak(device=0, mode=0, ms=200.0):

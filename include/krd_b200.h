@@ -155,6 +155,22 @@ krd_status krd_unpack_shards(krd_handle* h, int32_t world, const double* d_gathe
 krd_status krd_unpack_shards_rows(krd_handle* h, int32_t world, const double* d_gathered, int32_t row0, int32_t row1,
                                   double* d_out_rows);
 
+/* The three steps above in ONE call for a caller that owns an NCCL communicator (ncclComm_t passed as void*; one process per
+ * GPU, or one thread per GPU with communicators from krd_nccl_init_all): this rank's tile share, ncclAllGather of the packed
+ * tiles on the handle's stream, unpack of the rows [row0, row1) of the matrix into d_out ((row1 - row0) x n doubles, DEVICE;
+ * row0 = 0, row1 = n for the whole matrix).  Every rank of the communicator must make the call.  NCCL is loaded at run
+ * time (libnccl.so.2, or $KRD_NCCL_LIB); without it the call fails with KRD_ERR_STATE and nothing else is affected.
+ * This is the north-star's "NCCL all-gather of result tiles over NVLink"  behind the C ABI. */
+krd_status krd_compute_allgather(krd_handle* h, double p, double divisor, int32_t rank, int32_t world, void* nccl_comm,
+                                 int32_t row0, int32_t row1, double* d_out);
+/* Same with a HOST output: the rows [row0, row1) of the matrix ((row1 - row0) x n doubles) are copied to out_rows over this
+ * GPU's own PCIe link; returns when they are complete in host memory. */
+krd_status krd_compute_allgather_host(krd_handle* h, double p, double divisor, int32_t rank, int32_t world, void* nccl_comm,
+                                      int32_t row0, int32_t row1, double* out_rows);
+/* Communicators for n devices of THIS process (ncclCommInitAll), and their release. */
+krd_status krd_nccl_init_all(int32_t n, const int32_t* devices, void** comms);
+void       krd_nccl_destroy(int32_t n, void** comms);
+
 /* The same for a caller without an NCCL communicator (e.g. one host thread per GPU in one process, as
  * `gappa-b200 --gpus G` does): the rank's packed tiles go to a HOST buffer of krd_shard_doubles() doubles
  * (D2H over that GPU's own PCIe link), and the concatenation of all ranks' buffers, in rank order, is

@@ -244,11 +244,12 @@ def test_cli_multi_gpu_matches_single(tmp_path):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
-    for g, d in ((1, "o1"), (2, "o2")):
+    # --exchange nccl (default): NCCL all-gather of the result tiles inside the one-process CLI; host: per-GPU D2H of own tiles
+    for g, d, ex in ((1, "o1", "nccl"), (2, "o2", "nccl"), (2, "o3", "host")):
         r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path / d), "--gpus", str(g),
-                            "--write-binary", str(tmp_path / f"{d}.bin")], capture_output=True, text=True)
+                            "--exchange", ex, "--write-binary", str(tmp_path / f"{d}.bin")], capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
-    assert (tmp_path / "o1.bin").read_bytes() == (tmp_path / "o2.bin").read_bytes()
+    assert (tmp_path / "o1.bin").read_bytes() == (tmp_path / "o2.bin").read_bytes() == (tmp_path / "o3.bin").read_bytes()
     assert (tmp_path / "o2" / "krd_matrix.csv").read_bytes() == open(os.path.join(GOLD, "csv", "matrix.csv"), "rb").read()
 
 

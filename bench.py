@@ -235,16 +235,22 @@ def rooflines(gappa_b200, local, spec, st, pairs, share, ms_step, world):
     # the F builder (K1) is HBM-bound; algorithmic bytes per build: F written once + the tile-major entries
     # (10 B each) + the passes over the E x ld subtree matrices
     hp, hsrc = hbm_peak()
-    k1_bytes = float(st["f_bytes"]) + 10.0 * st["n_masses"] * K1_ENTRY_READS + 8.0 * K1_SUBTREE_PASSES * spec["edges"] * st["ld_samples"]
+    X = 8.0 * spec["edges"] * st["ld_samples"]           # one pass over an E x ld matrix
+    if spec["bins"] == 1:
+        # bins = 1: M and D ARE the rows of F.  Totals + zeros written (2 X = F), kids' M read (X), D written and M
+        # read-modify-written for the inner edges (1.5 X); the tile-major entries are read once
+        k1_bytes = 10.0 * st["n_masses"] + 4.5 * X
+        k1_name = "K1, bins = 1 (k_tile<TOTALS> into F, k_subtree_level/top on F)"
+    else:
+        # F written once + the tile-major entries read twice + T written, M read-modify-written, kids' M read, D written
+        # (inner edges), D read (inner edges): 4 X
+        k1_bytes = float(st["f_bytes"]) + 20.0 * st["n_masses"] + 4.0 * X
+        k1_name = "K1 (k_tile<TOTALS>, k_subtree_level/top, k_tile<FILL>)"
     k1_gbs = k1_bytes / (st["ms_build"] * 1e-3) / 1e9 if st["ms_build"] > 0 else 0.0
-    k1 = {"bound": "hbm", "kernel": "K1 (k_tile<TOTALS>, k_subtree_level/top, k_tile<FILL>)", "achieved": k1_gbs,
+    k1 = {"bound": "hbm", "kernel": k1_name, "achieved": k1_gbs,
           "peak": hp, "unit": "GB/s", "frac": k1_gbs / hp, "bytes": k1_bytes,
           "ms": st["ms_build"], "peak_source": hsrc, "share_of_step": st["ms_build"] / ms_step}
     return roof, k1
-
-
-K1_ENTRY_READS = 2.0       # the tile-major entries are read by k_tile<TOTALS> and by k_tile<FILL>
-K1_SUBTREE_PASSES = 5.0    # T written, M read-modify-written, kids' M read, D written, D read
 
 
 def timed(torch, dist, stream, fn, steps, warmup):
@@ -524,7 +530,9 @@ def run_multi(args):
     one = torch.full((ns, ns), -2.0, dtype=torch.float64, device="cuda")
     plan.compute_device(one, p=p)
     torch.cuda.synchronize()
-    shard_ok = bool(torch.equal(got, one))
+    # (the two runs cut the segment axis differently between CTAs, so their partial sums round differently: a few ulp)
+    shard_diff = float(((got - one).abs() / one.abs().clamp_min(1e-300)).max().item())
+    assert shard_diff <= 1e-12, f"sharded result differs from the single-GPU result: {shard_diff}"
     del dp, dg, got, one
 
     # ---- the cohort ----
@@ -627,11 +635,12 @@ def run_multi(args):
             h_one.copy_(d_out_full, non_blocking=True)
         ms_one = timed(torch, None, stream, step_one, 2, 1)
         st1 = plan.stats()
-        same = bool(np.array_equal(h_one.numpy()[:nb, :nb], blk_dev)) if blk_dev is not None else None
+        one_blk = h_one.numpy()[:nb, :nb]
+        same = float(np.max(np.abs(one_blk - blk_dev) / np.maximum(np.abs(blk_dev), 1e-300))) if blk_dev is not None else None
         one_gpu = {"value": pairs / (ms_one * 1e-3), "unit": UNIT, "ms_per_step": ms_one, "steps": 2, "warmup": 1,
                    "ms_kernel": st1["ms_pairs"], "ms_build_F": st1["ms_build"],
                    "note": "same cohort, same definition of value (incl. D2H of the whole matrix over one PCIe link), rank 0 alone",
-                   "leading_block_bit_identical_to_sharded": same}
+                   "leading_block_max_rel_diff_to_sharded": same}
         del h_one
     dist.barrier()
 
@@ -646,7 +655,7 @@ def run_multi(args):
                               % args.exchange,
             "masses": int(st["n_masses"]),
             "exchange": args.exchange, "ms_host_unpack_untimed": ms_host_unpack,
-            "shard_check": "sharded == single-GPU matrix bit for bit on the first %d samples: %s" % (ns, shard_ok),
+            "shard_check": {"samples": ns, "max_rel_diff_sharded_vs_single_gpu": shard_diff, "bound": 1e-12},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "ingest": "every rank uploads 1/N of the compact entries (12 B each) on a copy stream, NVLink all-gather of the two arrays, "
                               "K0 + K1 replicated, sharded pair kernel, exchange, per-rank D2H",

@@ -118,7 +118,7 @@ void krd_destroy(krd_handle* h)
     free_masses(h);
     for (void* q : h->d_owned) cudaFree(q);
     cudaFree(h->d_off);
-    cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_kmeans); cudaFree(h->d_fix); cudaFree(h->d_center); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
+    cudaFree(h->d_out_tmp_sq); cudaFree(h->d_squash); cudaFree(h->d_kmeans); cudaFree(h->d_fix); cudaFree(h->d_Fg); cudaFree(h->d_norm); cudaFree(h->d_norm_part); cudaFree(h->d_top); cudaFree(h->d_lvl_edges); cudaFree(h->d_kid_off); cudaFree(h->d_kid_edge); cudaFree(h->d_bl);
     cudaFree(h->d_sid); cudaFree(h->d_slot); cudaFree(h->d_edge_dec); cudaFree(h->d_grow); cudaFree(h->d_cum); cudaFree(h->d_acc);
     for (cudaEvent_t ev : h->slab_ev) cudaEventDestroy(ev); cudaFree(h->d_seg_off); cudaFree(h->d_len); cudaFree(h->d_sqrt_len); cudaFree(h->d_F);
     cudaFree(h->d_cell); cudaFree(h->d_tmass); cudaFree(h->d_tile_ptr); cudaFree(h->d_M); cudaFree(h->d_D);
@@ -303,6 +303,7 @@ krd_status krd_compute(krd_handle* h, double p, double divisor, double* out)
     if (st != KRD_OK) return st;
     if (h->N == 0) return KRD_OK;
     if (!out) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    KRD_CUDA(h, cudaSetDevice(h->device));    // (the scratch matrix below must live on THIS handle's device)
     const size_t bytes = (size_t)h->N * h->N * 8;
     if (bytes > h->out_tmp_capacity) {
         cudaFree(h->d_out_tmp); h->d_out_tmp = nullptr; h->out_tmp_capacity = 0;

@@ -84,8 +84,8 @@ struct krd_handle {
     double*  d_len = nullptr;      // S_pad (+ KC slack), zero padded
     double*  d_sqrt_len = nullptr; // same, sqrt(len) (direct p=2 path)
     bool     len_negative = false; // exact mode: a mass position outside its branch made a segment length negative
-    double*  d_center = nullptr;   // S_pad: the reference column the Gram path subtracts (F[.][0])
-    double*  d_norm = nullptr;     // ld: sum_s len (F[s][i] - center[s])^2
+    double*  d_Fg = nullptr;       // S_pad x ld: Gram path operands, sqrt(len) (F - F[.][0]) (k_gram_prescale)
+    double*  d_norm = nullptr;     // ld: sum_s len (F[s][i] - F[s][0])^2
     double*  d_norm_part = nullptr;
     bool     norms_valid = false;
     void*    d_fix = nullptr;      // int4[1 + cap]: Gram-path cells to recompute directly

@@ -50,7 +50,6 @@ struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `ti
 struct PairParams {
     const double* F;
     const double* len;     // len or sqrt(len) (MODE_P2)
-    const double* center;  // MODE_P2G: reference column subtracted from both operands
     const Tile* tiles;
     const WorkItem* items;
     const int32_t* cta_item_off;   // gridDim.x + 1
@@ -243,20 +242,22 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
+// The operands arrive pre-centred and pre-scaled (Ft = sqrt(len) (F - c), written once per F by k_gram_prescale): the loop
+// is LDS + DMMA only.  FP64 vector instructions and DMMA share one datapath (profiles/r1q_pipes_overlap.txt), so the 4 DADD +
+// 8 DADD + 8 DMUL per 32 DMMA that round 1 spent on centring and scaling inside this loop cost tensor cycles one for one.
 __device__ __forceinline__ void chunk_gram(const double* __restrict__ sA, const double* __restrict__ sB,
-                                           const double* __restrict__ sL, int wr, int wc, int lane, double (&acc)[8][8])
+                                           int wr, int wc, int lane, double (&acc)[8][8])
 {
     const int kq = lane & 3, rq = lane >> 2;
 #pragma unroll
     for (int kk = 0; kk < KC; kk += 4) {
-        const double l = sL[kk + kq], c = sL[KC + kk + kq];
         const double* pa = sA + (kk + kq) * TILE + wr + rq;
         const double* pb = sB + (kk + kq) * TILE + wc + rq;
         double a[4], b[8];
 #pragma unroll
-        for (int mi = 0; mi < 4; ++mi) a[mi] = pa[8 * mi] - c;
+        for (int mi = 0; mi < 4; ++mi) a[mi] = pa[8 * mi];
 #pragma unroll
-        for (int ni = 0; ni < 8; ++ni) b[ni] = (pb[8 * ni] - c) * l;
+        for (int ni = 0; ni < 8; ++ni) b[ni] = pb[8 * ni];
 #pragma unroll
         for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
@@ -319,13 +320,12 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             double* sB = sA + KC * TILE;
             double* sL = sB + KC * TILE;
             const int64_t k0 = (int64_t)p_chunk * KC;
-            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((dg ? 1 : 2) * KC * TILE * 8 + (MODE == MODE_P2G ? 2 : 1) * KC * 8));
+            if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((dg ? 1 : 2) * KC * TILE * 8 + KC * 8));
             __syncwarp();
             const int r = lane & 15;
             if (lane < 16) tma_load_1d(sA + r * TILE, P.F + (int64_t)t.i * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
             else if (!dg) tma_load_1d(sB + r * TILE, P.F + (int64_t)t.j * TILE + (k0 + r) * P.ld, TILE * 8, &full[s]);
             if (lane == 0) tma_load_1d(sL, P.len + k0, KC * 8, &full[s]);
-            if (MODE == MODE_P2G && lane == 1) tma_load_1d(sL + KC, P.center + k0, KC * 8, &full[s]);
         }
         ++p_flat;
         if (++p_chunk >= p_w.c1) {
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                     }
                 }
             } else if (MODE == MODE_P2G) {
-                chunk_gram(sA, sB, sL, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
+                chunk_gram(sA, sB, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
             } else {
                 switch (qmin) {
                     case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, s_tab, acc); break;
@@ -572,21 +572,21 @@ __global__ void __launch_bounds__(256) k_unpack_rows(const double* __restrict__ 
     }
 }
 
-// ---- Gram mode: reference column and per-sample squared norms -------------------------------------
-__global__ void k_center_col(const double* __restrict__ F, int64_t ld, int64_t S_pad, double* __restrict__ c)
-{
-    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s < S_pad) c[s] = F[s * ld];
-}
-
+// ---- Gram mode: centred + scaled copy of F and per-sample squared norms ------------------------------
+// Ft[s][i] = sqrt(len[s]) (F[s][i] - F[s][0]) and the partial sums of Ft^2 over a row range, one pass over F.  Column 0 is
+// the reference column c: it cancels exactly in a - b and only keeps the norms (hence the cancellation) small.
 __global__ void __launch_bounds__(128)
-k_col_norm_part(const double* __restrict__ F, const double* __restrict__ len, const double* __restrict__ c, int64_t ld,
-                int64_t S_pad, int64_t rows_per_chunk, double* __restrict__ part)
+k_gram_prescale(const double* __restrict__ F, const double* __restrict__ sqrt_len, int64_t ld, int64_t S_pad,
+                int64_t rows_per_chunk, double* __restrict__ Ft, double* __restrict__ part)
 {
     const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
     const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S_pad, s0 + rows_per_chunk);
     double acc = 0.0;
-    for (int64_t s = s0; s < s1; ++s) { const double d = F[s * ld + i] - c[s]; acc = fma(len[s] * d, d, acc); }
+    for (int64_t s = s0; s < s1; ++s) {
+        const double v = sqrt_len[s] * (F[s * ld + i] - F[s * ld]);
+        Ft[s * ld + i] = v;
+        acc = fma(v, v, acc);
+    }
     part[(int64_t)blockIdx.y * ld + i] = acc;
 }
 
@@ -602,18 +602,17 @@ __global__ void k_norm_reduce(const double* __restrict__ part, int64_t ld, int n
 static krd_status ensure_norms(krd_handle* h)
 {
     if (h->norms_valid) return KRD_OK;
-    const int NCH = 64;
+    const int NCH = 128;
     krd_status st;
-    if ((st = reserve(h, (void**)&h->d_center, (size_t)h->S_pad * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_norm, (size_t)h->ld * 8)) != KRD_OK) return st;
     if ((st = reserve(h, (void**)&h->d_norm_part, (size_t)NCH * h->ld * 8)) != KRD_OK) return st;
+    if ((st = reserve(h, (void**)&h->d_Fg, (size_t)h->S_pad * h->ld * 8)) != KRD_OK) return st;   // (the caller falls back to the direct path)
     const int64_t rpc = (h->S_pad + NCH - 1) / NCH;
-    k_center_col<<<(unsigned)((h->S_pad + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, h->d_center);
-    k_col_norm_part<<<dim3((unsigned)(h->ld / 128), NCH), 128, 0, h->stream>>>(h->d_F, h->d_len, h->d_center, h->ld, h->S_pad, rpc, h->d_norm_part);
+    k_gram_prescale<<<dim3((unsigned)(h->ld / 128), NCH), 128, 0, h->stream>>>(h->d_F, h->d_sqrt_len, h->ld, h->S_pad, rpc, h->d_Fg, h->d_norm_part);
     k_norm_reduce<<<(unsigned)((h->ld + 255) / 256), 256, 0, h->stream>>>(h->d_norm_part, h->ld, NCH, h->d_norm);
     KRD_CUDA(h, cudaGetLastError());
     h->norms_valid = true;
-    h->stats.launches += 3;
+    h->stats.launches += 2;
     return KRD_OK;
 }
 
@@ -747,7 +746,10 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
         diag_cost = 0.725 + 0.025 * mults;
     }
     if (const char* ov = std::getenv("KRD_DIAG_COST")) { const double v = std::atof(ov); if (v > 0.1 && v <= 1.5) diag_cost = v; }
-    if (mode == MODE_P2G) { krd_status sn = ensure_norms(h); if (sn != KRD_OK) return sn; }
+    if (mode == MODE_P2G && ensure_norms(h) != KRD_OK) {   // no room for the scaled copy of F: the direct path needs none
+        cudaGetLastError();
+        return run_pairs_once(h, p, divisor, rank, world, d_out_matrix, d_out_packed, false, slab);
+    }
 
     const int n_chunks = (int)((slab ? slab->rows : h->S_pad) / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
@@ -785,8 +787,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     }
 
     PairParams P;
-    P.center = h->d_center;
-    P.F = slab ? slab->F : h->d_F;
+    P.F = slab ? slab->F : (mode == MODE_P2G) ? h->d_Fg : h->d_F;
     P.len = ((mode == MODE_P2) ? h->d_sqrt_len : h->d_len) + (slab ? slab->row0 : 0);
     P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p;
     cudaError_t e;

@@ -43,7 +43,7 @@ constexpr size_t smem_bytes_for(int mode)
     return (size_t)stages_for(mode) * STAGE_DOUBLES * sizeof(double) + 2 * stages_for(mode) * sizeof(uint64_t) + (mode_is_halved(mode) ? SPILL_BYTES : 0);
 }
 constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
-constexpr double DIAG_COST_SKIP = 0.705;  // measured (profiles/cta_balance.py) cost of a diagonal-tile chunk relative to a full one (5/8 of the math, same pipeline overheads)
+constexpr double DIAG_COST_SKIP = 0.64;   // cost of a diagonal-tile chunk relative to a full one for the short operators (36/64 of the math at 16-column granularity + the same pipeline overheads; 0.705 measured at 32-column granularity, 40/64)
 
 struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
@@ -56,6 +56,7 @@ struct PairParams {
     double* ws;            // [item][TILE*TILE]
     int64_t ld;
     double p;
+    int N;                 // samples (columns >= N are zero padding: ragged last block)
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
@@ -141,6 +142,70 @@ __device__ __forceinline__ void chunk_math_int(const double* __restrict__ pa, co
         for (int r = 0; r < 8; ++r)
 #pragma unroll
             for (int cc = 2 * QMIN; cc < 8; ++cc) acc[r][cc] = fma(l, kr_pow_n<N>(fabs(a[r] - b[cc])), acc[r][cc]);
+    }
+}
+
+// Short operators (p = 1, 2, 3, 4): the thread's eight columns are 16 q + tx, q = 0..7 — one column per lane and step — so
+// that whole steps can be skipped warp-uniformly at a granularity of 16 columns: steps q < QMIN on diagonal tiles (row
+// group g needs columns >= 16 g only: 36/64 of the tile instead of 40/64 with 32-column blocks, and the two warps of an SM
+// sub-partition, g and 7 - g, carry 9/16 together whatever g is) and steps q >= QMAX on the tiles of a ragged last column
+// block (1,000 samples: 104 of 128 columns -> 7 of 8 steps instead of 8).  B operand fetch is one LDS.64 per step (16 lanes
+// x 8 B contiguous, the other half-warp reads the same addresses), A stays LDS.128 broadcast.
+constexpr bool mode_is_fine(int mode) { return mode == MODE_P1 || mode == MODE_P2 || mode == MODE_P2S || mode == MODE_P3 || mode == MODE_P4; }
+
+template <int MODE, int QMIN, int QMAX>
+__device__ __forceinline__ void chunk_math16(const double* __restrict__ pa, const double* __restrict__ pb,
+                                             const double* __restrict__ sL, double (&acc)[8][8])
+{
+#pragma unroll (mode_unroll(MODE))
+    for (int kk = 0; kk < KC; ++kk) {
+        double a[8], b[8];
+        const double l = sL[kk];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double2 va = *reinterpret_cast<const double2*>(pa + kk * TILE + 2 * q);
+            a[2 * q] = va.x; a[2 * q + 1] = va.y;
+        }
+#pragma unroll
+        for (int q = QMIN; q < QMAX; ++q) b[q] = pb[kk * TILE + 16 * q];
+        if (MODE == MODE_P2) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) a[q] *= l;
+#pragma unroll
+            for (int q = QMIN; q < QMAX; ++q) b[q] *= l;
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int q = QMIN; q < QMAX; ++q) acc[r][q] = pair_op<MODE, 1>(a[r], b[q], l, 0.0, nullptr, acc[r][q]);
+    }
+}
+
+template <int MODE>
+__device__ __forceinline__ void chunk_math16_dispatch(int qmin, int qmax, const double* __restrict__ pa, const double* __restrict__ pb,
+                                                      const double* __restrict__ sL, double (&acc)[8][8])
+{
+    if (qmax == 8) {
+        switch (qmin) {   // warp-uniform
+            case 0: chunk_math16<MODE, 0, 8>(pa, pb, sL, acc); break;
+            case 1: chunk_math16<MODE, 1, 8>(pa, pb, sL, acc); break;
+            case 2: chunk_math16<MODE, 2, 8>(pa, pb, sL, acc); break;
+            case 3: chunk_math16<MODE, 3, 8>(pa, pb, sL, acc); break;
+            case 4: chunk_math16<MODE, 4, 8>(pa, pb, sL, acc); break;
+            case 5: chunk_math16<MODE, 5, 8>(pa, pb, sL, acc); break;
+            case 6: chunk_math16<MODE, 6, 8>(pa, pb, sL, acc); break;
+            default: chunk_math16<MODE, 7, 8>(pa, pb, sL, acc); break;
+        }
+    } else {
+        switch (qmax) {   // CTA-uniform: ragged last column block (never a diagonal tile here)
+            case 1: chunk_math16<MODE, 0, 1>(pa, pb, sL, acc); break;
+            case 2: chunk_math16<MODE, 0, 2>(pa, pb, sL, acc); break;
+            case 3: chunk_math16<MODE, 0, 3>(pa, pb, sL, acc); break;
+            case 4: chunk_math16<MODE, 0, 4>(pa, pb, sL, acc); break;
+            case 5: chunk_math16<MODE, 0, 5>(pa, pb, sL, acc); break;
+            case 6: chunk_math16<MODE, 0, 6>(pa, pb, sL, acc); break;
+            default: chunk_math16<MODE, 0, 7>(pa, pb, sL, acc); break;
+        }
     }
 }
 
@@ -341,7 +406,9 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (rg >> 1) : 0;
+        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (mode_is_fine(MODE) ? rg : (rg >> 1)) : 0;
+        // fine modes: column steps of 16 at or beyond the last sample are skipped (off-diagonal tiles of the ragged last block)
+        const int qmax = (mode_is_fine(MODE) && !diag) ? min(8, (P.N - t.j * TILE + 15) >> 4) : 8;
 #ifdef KRD_TIMING
         if (threadIdx.x == 0 && item < 4096) KRD_STAMP(g_item_time[2 * item]);
 #endif
@@ -363,7 +430,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             const double* sB = diag ? sA : sA + KC * TILE;
             const double* sL = sA + 2 * KC * TILE;
             const double* pa = sA + row0;
-            const double* pb = sB + 2 * tx;
+            const double* pb = sB + (mode_is_fine(MODE) ? tx : 2 * tx);
             if (mode_is_halved(MODE)) {
                 // rows [4 act, 4 act + 4) are in registers (acc[0..3]), the other four in `spill`; one exchange per chunk
 #pragma unroll 1
@@ -385,6 +452,8 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                 }
             } else if (MODE == MODE_P2G) {
                 chunk_gram(sA, sB, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
+            } else if (mode_is_fine(MODE)) {
+                chunk_math16_dispatch<MODE>(qmin, qmax, pa, pb, sL, acc);
             } else {
                 switch (qmin) {
                     case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, s_tab, acc); break;
@@ -422,6 +491,13 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                     *reinterpret_cast<double2*>(wout + (row0 + 4 * (act ^ 1) + r) * TILE + 32 * q + 2 * tx) =
                         make_double2(spill[(r * 8 + 2 * q) * NT], spill[(r * 8 + 2 * q + 1) * NT]);
                 }
+            continue;
+        }
+        if (mode_is_fine(MODE)) {    // columns 16 q + tx
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int q = 0; q < 8; ++q) wout[(row0 + r) * TILE + 16 * q + tx] = acc[r][q];
             continue;
         }
 #pragma unroll
@@ -670,19 +746,21 @@ krd_status set_custom_tiles(krd_handle* h, const std::vector<Tile>& tiles)
 }
 
 // Stream-K schedule: cut the cost axis (tiles x chunks, diagonal tiles cheaper) into `G` equal spans.
-static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, double DIAG_COST, std::vector<WorkItem>& items,
-                          std::vector<int32_t>& cta_off, std::vector<int32_t>& tile_off)
+static void make_schedule(const Tile* tiles, int n_tiles, int n_chunks, int G, double DIAG_COST, double ragged_cost, int ragged_block,
+                          std::vector<WorkItem>& items, std::vector<int32_t>& cta_off, std::vector<int32_t>& tile_off)
 {
     items.clear(); cta_off.assign(G + 1, 0); tile_off.assign(n_tiles + 1, 0);
-    std::vector<double> pre(n_tiles + 1, 0.0);
-    for (int t = 0; t < n_tiles; ++t)
-        pre[t + 1] = pre[t] + ((tiles[t].i == tiles[t].j) ? DIAG_COST : 1.0) * n_chunks;
+    std::vector<double> pre(n_tiles + 1, 0.0), wt(n_tiles, 1.0);
+    for (int t = 0; t < n_tiles; ++t) {
+        wt[t] = (tiles[t].i == tiles[t].j) ? DIAG_COST : (tiles[t].j == ragged_block) ? ragged_cost : 1.0;
+        pre[t + 1] = pre[t] + wt[t] * n_chunks;
+    }
     const double total = pre[n_tiles];
     const int min_chunks = 8;   // do not create slivers: snap cuts that close to a tile border
     int g = 0;                  // CTA that owns the current position
     std::vector<int32_t> item_cta;
     for (int t = 0; t < n_tiles; ++t) {
-        const double w = (tiles[t].i == tiles[t].j) ? DIAG_COST : 1.0;
+        const double w = wt[t];
         int c = 0;
         while (c < n_chunks) {
             // end of CTA g's span, in chunks of this tile
@@ -739,7 +817,14 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     // as long as a full one (measured: p = 3, 4 0.8; halved modes p = 1/2 0.72, integer p 0.85; profiles/cta_balance.py).  Diagonal tiles also run FOUR
     // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
     // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
-    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_P3 || mode == MODE_P4) ? 0.75 : DIAG_COST_SKIP;
+    // short operators skip at 16-column granularity: the off-diagonal tiles of a ragged last column block run qmax of 8 steps
+    int ragged_block = -1; double ragged_cost = 1.0;
+    if (mode_is_fine(mode) && h->N % TILE != 0) {
+        const int qmax = (h->N % TILE + 15) / 16;
+        if (qmax < 8) { ragged_block = h->N / TILE; ragged_cost = 0.06 + 0.94 * qmax / 8.0; }
+    }
+    if (const char* ov = std::getenv("KRD_RAGGED_COST")) { const double v = std::atof(ov); if (v > 0.05 && v <= 1.5) ragged_cost = v; }
     if (mode == MODE_INT) {   // static bodies (chunk_math_int): 0.80 measured for 3 multiplications (p = 5), 0.85-0.875 for 6 (p = 15)
         int mults = 0;
         for (int n = (int)p; n > 1; n = (n & 1) ? n - 1 : n / 2) ++mults;
@@ -753,14 +838,15 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
 
     const int n_chunks = (int)((slab ? slab->rows : h->S_pad) / KC);
     const int G = h->cfg.split > 0 ? h->cfg.split : h->num_sms;
-    const int64_t key = (((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 4096 + (int64_t)(diag_cost * 2048.0);
+    const int64_t key = ((((t0 * 1000003 + t1) * 1000003 + n_chunks) * 1024 + G) * 4096 + (int64_t)(diag_cost * 2048.0)) * 4099 +
+                        (ragged_block < 0 ? 0 : (int64_t)(ragged_cost * 2048.0) + 1);
     if (key != h->sched_key) {
         auto it = h->scheds.find(key);
         if (it == h->scheds.end()) {
             if (h->capturing) return fail(h, KRD_ERR_STATE, "schedule not cached inside a captured phase");   // (re-issued launch by launch)
             if (h->scheds.size() >= 64) drop_schedules(h);
             std::vector<WorkItem> items; std::vector<int32_t> cta_off, tile_off;
-            make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, items, cta_off, tile_off);
+            make_schedule(h->h_tiles.data() + t0, n_tiles, n_chunks, G, diag_cost, ragged_cost, ragged_block, items, cta_off, tile_off);
             const size_t b_items = items.size() * sizeof(WorkItem), b_cta = cta_off.size() * 4, b_tile = tile_off.size() * 4;
             void* d = nullptr;
             KRD_CUDA(h, cudaMalloc(&d, b_items + b_cta + b_tile));
@@ -789,7 +875,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     PairParams P;
     P.F = slab ? slab->F : (mode == MODE_P2G) ? h->d_Fg : h->d_F;
     P.len = ((mode == MODE_P2) ? h->d_sqrt_len : h->d_len) + (slab ? slab->row0 : 0);
-    P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p;
+    P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p; P.N = h->N;
     cudaError_t e;
     switch (mode) {
         case MODE_P1: e = launch_pairs<MODE_P1>(P, G, h->stream); break;

@@ -222,14 +222,14 @@ def rooflines(gappa_b200, local, spec, st, pairs, share, ms_step, world):
     peak_dmma = gappa_b200.measure_fp64_peak(local, 2, 200.0)
     peak = max(peak_dfma, peak_dmma)
     achieved = flops / t_pairs / 1e12
-    # executed: full tiles + 36/64 of each diagonal tile + qmax/8 of the off-diagonal tiles of a ragged last column block
+    # executed: full tiles + 40/64 of each diagonal tile + qmax/8 of the off-diagonal tiles of a ragged last column block
     # (the short operators skip at 16-column granularity)
     T = st["ld_samples"] // 128
     rag = spec["samples"] % 128
     qmax = (rag + 15) // 16 if rag else 8
     off_tiles = st["n_tiles"] - T
     rag_tiles = (T - 1) if qmax < 8 else 0
-    executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((off_tiles - rag_tiles) + rag_tiles * qmax / 8.0 + 0.5625 * T) * share
+    executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((off_tiles - rag_tiles) + rag_tiles * qmax / 8.0 + 0.625 * T) * share
     roof = {"bound": "fp64", "kernel": "k_pairs<p=%g>" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak, "traffic": traffic_from_profile(spec, world),
             "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"

@@ -428,20 +428,29 @@ krd_status krd_squash(krd_handle* h, double p, krd_merger* out)
     return run_squash(h, p, out);
 }
 
-krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids, int32_t* assignments,
-                      double* distances, int32_t* iterations)
+krd_status krd_kmeans_ex(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids, const int32_t* init_assignments,
+                         int32_t* assignments, double* distances, int32_t* iterations)
 {
     krd_status st = check_compute(h, 1.0, 1.0);
     if (st != KRD_OK) return st;
     if (k > h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "Cannot run Kmeans with more clusters (k) than data points.");   // kmeans.hpp:538-544
-    if (k < 1 || k > 32) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: k must be in 1..32");
+    if (k < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "Cannot run Kmeans with k == 0.");                                 // kmeans.hpp:532-536
     if (max_iterations < 1) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: max_iterations must be >= 1");
     if (!init_centroids || !assignments || !distances) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null argument");
     for (int c = 0; c < k; ++c)
         if (init_centroids[c] < 0 || init_centroids[c] >= h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: initial centroid is not a sample index");
+    if (init_assignments)
+        for (int d = 0; d < h->N; ++d)
+            if (init_assignments[d] < 0 || init_assignments[d] >= k) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means: initial assignment is not a cluster index");
     KRD_CUDA(h, cudaSetDevice(h->device));
     if ((st = pipe_flatten(h)) != KRD_OK) return st;
-    return run_kmeans(h, k, max_iterations, init_centroids, assignments, distances, iterations);
+    return run_kmeans(h, k, max_iterations, init_centroids, init_assignments, assignments, distances, iterations);
+}
+
+krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids, int32_t* assignments,
+                      double* distances, int32_t* iterations)
+{
+    return krd_kmeans_ex(h, k, max_iterations, init_centroids, nullptr, assignments, distances, iterations);
 }
 
 krd_status krd_invalidate_F(krd_handle* h)

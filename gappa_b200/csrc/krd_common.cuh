@@ -226,7 +226,7 @@ krd_status run_squash(krd_handle* h, double p, krd_merger* out);
 int64_t tiles_per_rank(int64_t n_tiles, int world);
 
 // krd_kmeans.cu
-krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, int32_t* assignments,
-                      double* distances, int32_t* iterations_out);
+krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, const int32_t* init_assignments,
+                      int32_t* assignments, double* distances, int32_t* iterations_out);
 
 }  // namespace krd

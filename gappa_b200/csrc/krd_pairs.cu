@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cmath>
+#include <type_traits>
 
 #include "krd_common.cuh"
 #include "krd_ops.cuh"
@@ -43,7 +44,7 @@ constexpr size_t smem_bytes_for(int mode)
     return (size_t)stages_for(mode) * STAGE_DOUBLES * sizeof(double) + 2 * stages_for(mode) * sizeof(uint64_t) + (mode_is_halved(mode) ? SPILL_BYTES : 0);
 }
 constexpr int FIX_CAP = 1 << 20;    // capacity of the Gram path's fix-up list (pairs)
-constexpr double DIAG_COST_SKIP = 0.705;  // cost of a diagonal-tile chunk relative to a full one for the short operators (36/64 of the math at 16-column granularity + the same pipeline overheads; 0.705 measured at 32-column granularity, 40/64)
+constexpr double DIAG_COST_SKIP = 0.705;  // measured (profiles/cta_balance.py) cost of a diagonal-tile chunk relative to a full one (5/8 of the math, same pipeline overheads)
 
 struct WorkItem { int32_t tile, c0, c1, pad; };   // chunks [c0, c1) of tile `tile` (index into the rank's tile list)
 
@@ -107,7 +108,7 @@ __device__ unsigned long long g_item_time[2 * 4096];
 // One chunk (KC segments) of one tile for one thread; column blocks q < QMIN are skipped
 // (diagonal tiles: blocks that lie entirely below the diagonal).
 #ifndef KRD_P12_UNROLL
-#define KRD_P12_UNROLL 4
+#define KRD_P12_UNROLL 2
 #endif
 #ifndef KRD_P34_UNROLL
 #define KRD_P34_UNROLL 2
@@ -145,19 +146,25 @@ __device__ __forceinline__ void chunk_math_int(const double* __restrict__ pa, co
     }
 }
 
-// Short operators (p = 1, 2, 3, 4): the thread's eight columns are 16 q + tx, q = 0..7 — one column per lane and step — so
-// that whole steps can be skipped warp-uniformly at a granularity of 16 columns: steps q < QMIN on diagonal tiles (row
-// group g needs columns >= 16 g only: 36/64 of the tile instead of 40/64 with 32-column blocks, and the two warps of an SM
-// sub-partition, g and 7 - g, carry 9/16 together whatever g is) and steps q >= QMAX on the tiles of a ragged last column
-// block (1,000 samples: 104 of 128 columns -> 7 of 8 steps instead of 8).  B operand fetch is one LDS.64 per step (16 lanes
+// Short operators (p = 1, 2, 3, 4), OFF-DIAGONAL tiles: the thread's eight columns are 16 q + tx, q = 0..7 — one column per
+// lane and step — so that whole steps can be skipped CTA-uniformly at a granularity of 16 columns: steps q >= QMAX on the
+// tiles of a ragged last column block (1,000 samples: 104 of 128 columns -> 7 of 8 steps instead of 8).  (QMIN is kept
+// for experiments; diagonal tiles use the 32-column-block body chunk_math<MODE, QMIN>.)  B operand fetch is one LDS.64 per step (16 lanes
 // x 8 B contiguous, the other half-warp reads the same addresses), A stays LDS.128 broadcast.
-constexpr bool mode_is_fine(int mode) { return mode == MODE_P1 || mode == MODE_P2 || mode == MODE_P2S || mode == MODE_P3 || mode == MODE_P4; }
+#ifndef KRD_FINE
+#define KRD_FINE 1      // 0: every tile on the 32-column-block body (A/B measurements: make EXTRA=-DKRD_FINE=0 ...)
+#endif
+constexpr bool mode_is_fine(int mode) { return KRD_FINE && (mode == MODE_P1 || mode == MODE_P2 || mode == MODE_P2S || mode == MODE_P3 || mode == MODE_P4); }
 
+#ifndef KRD_FINE_UNROLL
+#define KRD_FINE_UNROLL 2
+#endif
+constexpr int fine_unroll(int mode) { return mode_unroll(mode) < KRD_FINE_UNROLL ? mode_unroll(mode) : KRD_FINE_UNROLL; }
 template <int MODE, int QMIN, int QMAX>
 __device__ __forceinline__ void chunk_math16(const double* __restrict__ pa, const double* __restrict__ pb,
                                              const double* __restrict__ sL, double (&acc)[8][8])
 {
-#pragma unroll (mode_unroll(MODE))
+#pragma unroll (fine_unroll(MODE))
     for (int kk = 0; kk < KC; ++kk) {
         double a[8], b[8];
         const double l = sL[kk];
@@ -182,30 +189,18 @@ __device__ __forceinline__ void chunk_math16(const double* __restrict__ pa, cons
 }
 
 template <int MODE>
-__device__ __forceinline__ void chunk_math16_dispatch(int qmin, int qmax, const double* __restrict__ pa, const double* __restrict__ pb,
+__device__ __forceinline__ void chunk_math16_dispatch(int qmax, const double* __restrict__ pa, const double* __restrict__ pb,
                                                       const double* __restrict__ sL, double (&acc)[8][8])
 {
-    if (qmax == 8) {
-        switch (qmin) {   // warp-uniform
-            case 0: chunk_math16<MODE, 0, 8>(pa, pb, sL, acc); break;
-            case 1: chunk_math16<MODE, 1, 8>(pa, pb, sL, acc); break;
-            case 2: chunk_math16<MODE, 2, 8>(pa, pb, sL, acc); break;
-            case 3: chunk_math16<MODE, 3, 8>(pa, pb, sL, acc); break;
-            case 4: chunk_math16<MODE, 4, 8>(pa, pb, sL, acc); break;
-            case 5: chunk_math16<MODE, 5, 8>(pa, pb, sL, acc); break;
-            case 6: chunk_math16<MODE, 6, 8>(pa, pb, sL, acc); break;
-            default: chunk_math16<MODE, 7, 8>(pa, pb, sL, acc); break;
-        }
-    } else {
-        switch (qmax) {   // CTA-uniform: ragged last column block (never a diagonal tile here)
-            case 1: chunk_math16<MODE, 0, 1>(pa, pb, sL, acc); break;
-            case 2: chunk_math16<MODE, 0, 2>(pa, pb, sL, acc); break;
-            case 3: chunk_math16<MODE, 0, 3>(pa, pb, sL, acc); break;
-            case 4: chunk_math16<MODE, 0, 4>(pa, pb, sL, acc); break;
-            case 5: chunk_math16<MODE, 0, 5>(pa, pb, sL, acc); break;
-            case 6: chunk_math16<MODE, 0, 6>(pa, pb, sL, acc); break;
-            default: chunk_math16<MODE, 0, 7>(pa, pb, sL, acc); break;
-        }
+    switch (qmax) {   // CTA-uniform; < 8 only on the off-diagonal tiles of a ragged last column block
+        case 8: chunk_math16<MODE, 0, 8>(pa, pb, sL, acc); break;
+        case 1: chunk_math16<MODE, 0, 1>(pa, pb, sL, acc); break;
+        case 2: chunk_math16<MODE, 0, 2>(pa, pb, sL, acc); break;
+        case 3: chunk_math16<MODE, 0, 3>(pa, pb, sL, acc); break;
+        case 4: chunk_math16<MODE, 0, 4>(pa, pb, sL, acc); break;
+        case 5: chunk_math16<MODE, 0, 5>(pa, pb, sL, acc); break;
+        case 6: chunk_math16<MODE, 0, 6>(pa, pb, sL, acc); break;
+        default: chunk_math16<MODE, 0, 7>(pa, pb, sL, acc); break;
     }
 }
 
@@ -399,19 +394,27 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     };
     for (int c = 0; c < STM - LAG; ++c) produce_one();
 
-    double acc[8][8];
-    double h4[4][8];   // halved modes: the four accumulator rows that are in registers
     int flat = 0;
     for (int item = it0; item < it1; ++item) {
         const WorkItem w = P.items[item];
         const Tile t = P.tiles[w.tile];
         const bool diag = (t.i == t.j);
-        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (mode_is_fine(MODE) ? (rg & ~1) : (rg >> 1)) : 0;   // fine modes: steps of 16 columns, skipped in PAIRS on diagonal tiles (four code variants at once, not eight: eight thrashed the instruction cache, cfg2 3.5 -> 4.7 ms)
+        // Diagonal tiles keep the 32-column-block layout for every mode (four skip variants at once): in the 16-column layout
+        // their chunks cost 0.85 of a full one instead of 0.705 (measured at cfg2, eight variants thrashed the instruction
+        // cache outright: 3.5 -> 4.7 ms), which ate the whole gain of the ragged-block skip.  `fine` is per work item.
+        const bool fine_item = mode_is_fine(MODE) && !diag;
+        const int qmin = (diag && MODE != MODE_P2G && MODE != MODE_GENERIC && MODE != MODE_LIBPOW) ? (rg >> 1) : 0;
         // fine modes: column steps of 16 at or beyond the last sample are skipped (off-diagonal tiles of the ragged last block)
-        const int qmax = (mode_is_fine(MODE) && !diag) ? min(8, (P.N - t.j * TILE + 15) >> 4) : 8;
+        const int qmax = fine_item ? min(8, (P.N - t.j * TILE + 15) >> 4) : 8;
 #ifdef KRD_TIMING
         if (threadIdx.x == 0 && item < 4096) KRD_STAMP(g_item_time[2 * item]);
 #endif
+        // The item's chunk loop and write-out, instantiated once per accumulator LAYOUT (fine = 16-column steps, else
+        // 32-column blocks) with its own accumulators: with both layouts in one body ptxas spilled (228 B, cfg2 3.5 -> 4.0 ms).
+        auto run_item = [&](auto fine_c) {
+        constexpr bool fine = decltype(fine_c)::value;
+        double acc[8][8];
+        double h4[4][8];   // halved modes: the four accumulator rows that are in registers
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
@@ -430,7 +433,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
             const double* sB = diag ? sA : sA + KC * TILE;
             const double* sL = sA + 2 * KC * TILE;
             const double* pa = sA + row0;
-            const double* pb = sB + (mode_is_fine(MODE) ? tx : 2 * tx);
+            const double* pb = sB + (fine ? tx : 2 * tx);
             if (mode_is_halved(MODE)) {
                 // rows [4 act, 4 act + 4) are in registers (acc[0..3]), the other four in `spill`; one exchange per chunk
 #pragma unroll 1
@@ -452,8 +455,8 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                 }
             } else if (MODE == MODE_P2G) {
                 chunk_gram(sA, sB, 32 * (warp & 3), 64 * (warp >> 2), lane, acc);
-            } else if (mode_is_fine(MODE)) {
-                chunk_math16_dispatch<MODE>(qmin, qmax, pa, pb, sL, acc);
+            } else if (fine) {
+                chunk_math16_dispatch<MODE>(qmax, pa, pb, sL, acc);
             } else {
                 switch (qmin) {
                     case 0: chunk_math<MODE, 0>(pa, pb, sL, P.p, s_tab, acc); break;
@@ -480,7 +483,7 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                 for (int ni = 0; ni < 8; ++ni)
                     *reinterpret_cast<double2*>(wout + (wr + 8 * mi + (lane >> 2)) * TILE + wc + 8 * ni + 2 * (lane & 3)) =
                         make_double2(acc[2 * mi][ni], acc[2 * mi + 1][ni]);
-            continue;
+            return;
         }
         if (mode_is_halved(MODE)) {
 #pragma unroll
@@ -491,20 +494,22 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                     *reinterpret_cast<double2*>(wout + (row0 + 4 * (act ^ 1) + r) * TILE + 32 * q + 2 * tx) =
                         make_double2(spill[(r * 8 + 2 * q) * NT], spill[(r * 8 + 2 * q + 1) * NT]);
                 }
-            continue;
+            return;
         }
-        if (mode_is_fine(MODE)) {    // columns 16 q + tx
+        if (fine) {    // columns 16 q + tx
 #pragma unroll
             for (int r = 0; r < 8; ++r)
 #pragma unroll
                 for (int q = 0; q < 8; ++q) wout[(row0 + r) * TILE + 16 * q + tx] = acc[r][q];
-            continue;
+            return;
         }
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
             for (int q = 0; q < 4; ++q)
                 *reinterpret_cast<double2*>(wout + (row0 + r) * TILE + 32 * q + 2 * tx) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
+        };   // run_item
+        if (mode_is_fine(MODE) && fine_item) run_item(std::true_type{}); else run_item(std::false_type{});
     }
 #ifdef KRD_TIMING
     __syncthreads();
@@ -817,7 +822,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     // as long as a full one (measured: p = 3, 4 0.8; halved modes p = 1/2 0.72, integer p 0.85; profiles/cta_balance.py).  Diagonal tiles also run FOUR
     // code variants at once (one per skip count), so the unrolled bodies must stay small: with the p = 3 body unrolled 4x
     // the diagonal tiles ran up to 50 % slower than full ones (instruction-cache misses); unrolled 2x they do not.  KRD_DIAG_COST overrides (tuning aid).
-    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_P3 || mode == MODE_P4) ? 0.75 : DIAG_COST_SKIP;
+    double diag_cost = full_diag ? 1.0 : (mode == MODE_PHALF) ? 0.72 : (mode == MODE_P3 || mode == MODE_P4) ? 0.8 : DIAG_COST_SKIP;
     // short operators skip at 16-column granularity: the off-diagonal tiles of a ragged last column block run qmax of 8 steps
     int ragged_block = -1; double ragged_cost = 1.0;
     if (mode_is_fine(mode) && h->N % TILE != 0) {

@@ -41,8 +41,10 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-base", action="store_true", help="N = 1: skip the 1-GPU cfg4 block (strong_scaling_base)")
-    ap.add_argument("--exchange", default="allgather_rows", choices=["allgather_rows", "allgather_rank0", "own_tiles_host"],
+    ap.add_argument("--exchange", default="p2p_rows", choices=["host_tiles", "p2p_rows", "allgather_rows", "allgather_rank0", "own_tiles_host"],
                     help="N > 1: how the result tiles reach host memory (SURVEY §8e asks for an A/B)")
+    ap.add_argument("--tail", type=float, default=0.125, help="--exchange host_tiles: fraction of a rank's tiles in the short LAST launch; the copies "
+                    "of the long first launch run under it (0 = one launch)")
     return ap.parse_args()
 
 
@@ -101,7 +103,7 @@ def config_of(spec, world):
             "l2": "inputs larger than L2 (dense matrix F = %.0f MB + split workspace)" % ((S + 15) // 16 * 16 * ld * 8 / 1e6),
             "parallelism": "1 gpu" if world == 1 else
                            f"strong scaling: cohort fixed, upper-triangular 128x128 tiles / {world} ranks, F replicated, NCCL all-gather "
-                           "of the result tiles, every rank copies its row block of the matrix to host memory"}
+                           "of the result tiles or stores into the owners' row blocks over NVLink peer memory (see `exchange`), every rank copies its row block of the matrix to host memory"}
 
 
 def traffic_from_profile(spec, world):
@@ -549,6 +551,33 @@ def run_multi(args):
     d_gath = torch.empty(shard * world, dtype=torch.float64, device="cuda")
     d_rows = torch.empty((r1 - r0, N), dtype=torch.float64, device="cuda")
     d_out_full = torch.empty((N, N), dtype=torch.float64, device="cuda") if (args.exchange == "allgather_rank0" or rank == 0) else None
+    # p2p_rows: row blocks every rank can write (cudaMalloc + CUDA IPC inside the library), two sets used alternately so that
+    # a rank never writes a block its owner may still be copying to the host
+    bounds = np.array([r * N // world for r in range(world + 1)], np.int32)
+    p2p_ptrs, p2p_own, p2p_mine, step_no = None, None, [], [0]
+    if args.exchange == "p2p_rows":
+        class _Raw:
+            def __init__(self, ptr, shape):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f8", "data": (ptr, False), "version": 2}
+        mine = [gappa_b200.krd.p2p_alloc(local, max(1, (r1 - r0) * N * 8)) for _ in range(2)]
+        p2p_mine = [m[0] for m in mine]
+        handles = [None] * world
+        dist.all_gather_object(handles, [m[1] for m in mine])
+        p2p_ptrs = [[p2p_mine[k] if r == rank else gappa_b200.krd.p2p_open(local, handles[r][k]) for r in range(world)] for k in range(2)]
+        p2p_own = [torch.as_tensor(_Raw(p2p_mine[k], (r1 - r0, N)), device=torch.device("cuda", local)) for k in range(2)]
+        d_flag = torch.zeros(1, dtype=torch.float32, device="cuda")
+    PH = 1
+    if args.exchange == "host_tiles":
+        # the rank's contiguous share of the tile list, cut UNEVENLY: a long first launch and a short last one (--tail); per piece
+        # the packed tiles + their transposes
+        n_tiles_all = len(gappa_b200.krd.tile_list(N)[0])
+        t0r, t1r = gappa_b200.krd.rank_tiles(n_tiles_all, rank, world)
+        cut = t1r - int(round((t1r - t0r) * max(0.0, min(0.9, args.tail))))
+        pieces = [(a, b) for a, b in ((t0r, cut), (cut, t1r)) if b > a]
+        PH = len(pieces)
+        d_pk = [torch.empty((b - a) * 128 * 128, dtype=torch.float64, device="cuda") for a, b in pieces]
+        d_sc = [torch.empty((b - a) * 128 * 128, dtype=torch.float64, device="cuda") for a, b in pieces]
+        out_stream = torch.cuda.Stream()
     h_packed = None
     if args.exchange == "own_tiles_host":
         shm2 = shm + "_packed"
@@ -573,11 +602,26 @@ def run_multi(args):
     head_blk = workloads.head(comp, min(N, 64))
     del comp
 
-    def exchange():
-        if args.exchange == "allgather_rows":
+    def exchange(ev=None):
+        mark = (lambda k: ev[k].record(stream)) if ev else (lambda k: None)
+        if args.exchange == "p2p_rows":
+            # every rank stores its tiles (and their mirrors) straight into the owners' row blocks over NVLink; a one-element
+            # all-reduce on the same stream is the barrier after which this rank's block is complete
+            k = step_no[0] % 2
+            step_no[0] += 1
+            plan.scatter_shard_rows(rank, world, d_packed, bounds, p2p_ptrs[k])
+            mark(1)
+            dist.all_reduce(d_flag)
+            mark(2)
+            h_rows.copy_(p2p_own[k], non_blocking=True)
+            mark(3)
+        elif args.exchange == "allgather_rows":
             dist.all_gather_into_tensor(d_gath, d_packed)
+            mark(1)
             plan.unpack_shards_rows(d_gath, d_rows, world, r0, r1)
+            mark(2)
             h_rows.copy_(d_rows, non_blocking=True)
+            mark(3)
         elif args.exchange == "allgather_rank0":        # round-1 variant: full unpack everywhere, one D2H over rank 0's link
             dist.all_gather_into_tensor(d_gath, d_packed)
             plan.unpack_shards(d_gath, d_out_full, world)
@@ -586,8 +630,23 @@ def run_multi(args):
         else:                                           # no collective: own packed tiles to the host, unpacked there (untimed here)
             h_packed[rank].copy_(d_packed, non_blocking=True)
 
+    def step_host_tiles(collect=None):
+        # No collective: every cell of the host matrix is written by exactly one rank, by the copy engines, and the copies
+        # of the long first piece run under the pair launch of the short last one (the pair kernel fills every SM; the
+        # copy engines are free)
+        stream.wait_stream(out_stream)             # (the previous step's copies have read d_pk / d_sc)
+        for q, (a, b) in enumerate(pieces):
+            plan.compute_tile_range(d_pk[q], a, b, p=p)
+            if collect is not None:
+                torch.cuda.synchronize()
+                collect.append(plan.stats())
+            plan.tile_range_to_host_async(a, b, d_pk[q], d_sc[q], h_full, out_stream.cuda_stream)
+        stream.wait_stream(out_stream)             # the step ends when the last copy has landed
+
     def step_device():
         plan.invalidate_F()
+        if args.exchange == "host_tiles":
+            return step_host_tiles()
         plan.compute_shard(d_packed, rank, world, p=p)
         exchange()
 
@@ -602,14 +661,26 @@ def run_multi(args):
             stream.wait_event(up_events[k])
             dist.all_gather_into_tensor(d_all[k], d_part[k])
         plan.set_masses_binned_device(off_np, d_all[0], d_all[1])
-        plan.compute_shard(d_packed, rank, world, p=p)
-        exchange()
+        if args.exchange == "host_tiles":
+            step_host_tiles()
+        else:
+            plan.compute_shard(d_packed, rank, world, p=p)
+            exchange()
         torch.cuda.synchronize()
 
     warmup = max(args.warmup, 3)
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step = timed(torch, dist, stream, step_device, args.steps, warmup)
     st = plan.stats()
+    if args.exchange == "host_tiles":          # one traced step: per-launch times of the PH sub-shares (K1 runs in the first)
+        plan.invalidate_F()
+        per = []
+        step_host_tiles(per)
+        torch.cuda.synchronize()
+        st = dict(per[-1])
+        st["ms_pairs"] = float(sum(q["ms_pairs"] for q in per)); st["ms_epilogue"] = float(sum(q["ms_epilogue"] for q in per))
+        st["ms_build"] = per[0]["ms_build"]; st["launches"] = int(sum(q["launches"] for q in per)) + PH
+        st["ms_pairs_per_launch"] = [q["ms_pairs"] for q in per]
     for _ in range(int(min(2000, max(1, 400.0 / max(ms_step, 0.05))))):    # (same count on every rank: ms_step is the max over ranks)
         step_device()
     torch.cuda.synchronize()
@@ -619,6 +690,7 @@ def run_multi(args):
     blk_dev = None
     ms_host_unpack = None
     if rank == 0 and args.exchange != "own_tiles_host":
+        torch.cuda.synchronize()
         blk_dev = h_full[:nb, :nb].numpy().copy()
     if args.exchange == "own_tiles_host" and rank == 0:
         t0 = time.perf_counter()
@@ -626,6 +698,18 @@ def run_multi(args):
         ms_host_unpack = (time.perf_counter() - t0) * 1e3
         blk_dev = Dh[:nb, :nb].copy()
         del Dh
+    # one traced step: where the time after the pair kernel goes (CUDA events on this rank's stream)
+    breakdown = None
+    if args.exchange in ("p2p_rows", "allgather_rows"):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        dist.barrier(); torch.cuda.synchronize()
+        plan.invalidate_F()
+        plan.compute_shard(d_packed, rank, world, p=p)
+        ev[0].record(stream)
+        exchange(ev)
+        torch.cuda.synchronize()
+        names = ("scatter_peer_stores", "barrier_allreduce", "d2h_row_block") if args.exchange == "p2p_rows" else ("nccl_allgather", "unpack_row_block", "d2h_row_block")
+        breakdown = {nm: ev[k].elapsed_time(ev[k + 1]) for k, nm in enumerate(names)}
     ms_e2e = timed(torch, dist, stream, step_e2e, max(2, min(args.steps, 5)), 3)
     dist.barrier()
     blk_e2e = h_full[:nb, :nb].numpy().copy() if (rank == 0 and args.exchange != "own_tiles_host") else None
@@ -660,7 +744,8 @@ def run_multi(args):
             "value_includes": "per rank: F build (K1, replicated) + pair kernel on its tile share + epilogue + exchange (%s) + D2H; max over ranks"
                               % args.exchange,
             "masses": int(st["n_masses"]),
-            "exchange": args.exchange, "ms_host_unpack_untimed": ms_host_unpack,
+            "exchange": args.exchange, "launches_per_step": PH, "tail_fraction": args.tail if args.exchange == "host_tiles" else None,
+            "ms_pairs_per_launch": st.get("ms_pairs_per_launch"), "exchange_breakdown_ms_rank0": breakdown, "ms_host_unpack_untimed": ms_host_unpack,
             "shard_check": {"samples": ns, "max_rel_diff_sharded_vs_single_gpu": shard_diff, "bound": 1e-12},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "ingest": "every rank uploads 1/N of the compact entries (12 B each) on a copy stream, NVLink all-gather of the two arrays, "
@@ -678,6 +763,16 @@ def run_multi(args):
             line["parity"]["reference_sample"] = info["sample"]
         print(json.dumps(line))
     dist.barrier()
+    if p2p_ptrs:
+        torch.cuda.synchronize()
+        p2p_own = None
+        for k in range(2):
+            for r in range(world):
+                if r != rank:
+                    gappa_b200.krd.p2p_close(p2p_ptrs[k][r])
+        dist.barrier()
+        for q in p2p_mine:
+            gappa_b200.krd.p2p_free(q)
     cudart.cudaHostUnregister(h_full.data_ptr())
     dist.destroy_process_group()
     if rank == 0:

@@ -105,6 +105,7 @@ krd_status krd_create(const krd_config* cfg, krd_handle** out)
     if (!h) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "out of host memory");
     h->cfg = c; h->device = c.device; h->num_sms = prop.multiProcessorCount;
     for (auto& ev : h->ev) cudaEventCreate(&ev);
+    cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming);
     *out = h;
     return KRD_OK;
 }
@@ -126,6 +127,7 @@ void krd_destroy(krd_handle* h)
     cudaFree(h->d_flags);
     cudaFree(h->d_ws); for (auto& kv : h->scheds) cudaFree(kv.second.d); cudaFree(h->d_tiles); cudaFree(h->d_out_tmp); cudaFree(h->d_shard); cudaFree(h->d_gathered);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->ev_copy) cudaEventDestroy(h->ev_copy);
     delete h;
 }
 
@@ -331,6 +333,21 @@ krd_status krd_compute_shard(krd_handle* h, double p, double divisor, int32_t ra
     if (world < 1 || rank < 0 || rank >= world) return fail(h, KRD_ERR_INVALID_ARGUMENT, "bad rank/world");
     if (!d_packed) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
     return compute_impl(h, p, divisor, rank, world, nullptr, d_packed);
+}
+
+krd_status krd_compute_tile_range(krd_handle* h, double p, double divisor, int64_t t0, int64_t t1, double* d_packed)
+{
+    krd_status st = check_compute(h, p, divisor);
+    if (st != KRD_OK) return st;
+    if (!d_packed) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null output");
+    if (t0 < 0 || t1 < t0 || t1 > krd_tile_count(h->N)) return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_compute_tile_range: bad tile range");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    if (h->piped) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }
+    if (t0 == t1) return KRD_OK;
+    h->force_t0 = t0; h->force_t1 = t1;
+    st = compute_impl(h, p, divisor, 0, 1, nullptr, d_packed);
+    h->force_t0 = h->force_t1 = -1;
+    return st;
 }
 
 krd_status krd_compute_shard_host(krd_handle* h, double p, double divisor, int32_t rank, int32_t world, double* packed)

@@ -157,6 +157,7 @@ struct krd_handle {
     std::unordered_map<void**, size_t> caps;   // capacities of buffers managed by krd::reserve
 
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_copy = nullptr;   // krd_shard_to_host_async: the tile transposes are done (compute stream -> copy stream)
     krd_stats stats{};
 };
 
@@ -207,6 +208,7 @@ krd_status run_pairs_slab(krd_handle* h, double p, double divisor, int rank, int
 krd_status compute_streamed(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed);   // krd_build.cu
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
 krd_status unpack_shard_rows(krd_handle* h, const double* d_gathered, int row0, int row1, double* d_out_rows);
+krd_status rank_tile_range(krd_handle* h, int rank, int world, const Tile** d_tiles, int64_t* t0, int64_t* t1);   // device tile list + the rank's share
 
 // krd_pipe.cu — pipelined ingest (krd_config.pipeline)
 bool pipe_wanted(const krd_handle* h, int32_t n_samples);

@@ -808,7 +808,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     krd_rank_tiles(n_tiles_all, rank, world, &t0, &t1);
     if (h->force_t0 >= 0) { t0 = h->force_t0; t1 = h->force_t1; }   // pipelined ingest: one phase of the phase-major list
     const int n_tiles = (int)(t1 - t0);
-    if (d_out_packed && n_tiles < per_rank && (!slab || slab->last))   // ragged tail: keep the all-gather payload defined
+    if (d_out_packed && n_tiles < per_rank && h->force_t0 < 0 && (!slab || slab->last))   // ragged tail: keep the all-gather payload defined
         KRD_CUDA(h, cudaMemsetAsync(d_out_packed + (size_t)n_tiles * TILE * TILE, 0, (size_t)(per_rank - n_tiles) * TILE * TILE * 8, h->stream));
     h->stats.pair_ctas = 0;
     if (n_tiles == 0) { cudaEventRecord(h->ev[2], h->stream); return KRD_OK; }
@@ -963,6 +963,15 @@ krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, dou
     (void)world;
     k_unpack<<<(unsigned)n_tiles, 256, 0, h->stream>>>(d_gathered, h->d_tiles, n_tiles, h->N, d_out);
     KRD_CUDA(h, cudaGetLastError());
+    return KRD_OK;
+}
+
+krd_status rank_tile_range(krd_handle* h, int rank, int world, const Tile** d_tiles, int64_t* t0, int64_t* t1)
+{
+    krd_status st = ensure_tiles(h);
+    if (st != KRD_OK) return st;
+    krd_rank_tiles(h->n_tiles_alloc, rank, world, t0, t1);
+    *d_tiles = h->d_tiles;
     return KRD_OK;
 }
 

@@ -28,7 +28,8 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
+    "krd_p2p_free", "krd_p2p_enable_peer", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -109,6 +110,24 @@ def lib():
     L.krd_compute_allgather.argtypes = [vp, dbl, dbl, i32, i32, vp, i32, i32, vp]
     L.krd_compute_allgather_host.restype = C.c_int
     L.krd_compute_allgather_host.argtypes = [vp, dbl, dbl, i32, i32, vp, i32, i32, vp]
+    L.krd_scatter_shard_rows.restype = C.c_int
+    L.krd_scatter_shard_rows.argtypes = [vp, i32, i32, vp, vp, vp]
+    L.krd_shard_to_host_async.restype = C.c_int
+    L.krd_shard_to_host_async.argtypes = [vp, i32, i32, vp, vp, vp, vp]
+    L.krd_compute_tile_range.restype = C.c_int
+    L.krd_compute_tile_range.argtypes = [vp, dbl, dbl, i64, i64, vp]
+    L.krd_tile_range_to_host_async.restype = C.c_int
+    L.krd_tile_range_to_host_async.argtypes = [vp, i64, i64, vp, vp, vp, vp]
+    L.krd_p2p_alloc.restype = C.c_int
+    L.krd_p2p_alloc.argtypes = [i32, i64, C.POINTER(vp), vp]
+    L.krd_p2p_open.restype = C.c_int
+    L.krd_p2p_open.argtypes = [i32, vp, C.POINTER(vp)]
+    L.krd_p2p_close.restype = None
+    L.krd_p2p_close.argtypes = [vp]
+    L.krd_p2p_free.restype = None
+    L.krd_p2p_free.argtypes = [vp]
+    L.krd_p2p_enable_peer.restype = C.c_int
+    L.krd_p2p_enable_peer.argtypes = [i32, i32]
     L.krd_nccl_init_all.restype = C.c_int
     L.krd_nccl_init_all.argtypes = [i32, vp, vp]
     L.krd_nccl_destroy.restype = None
@@ -250,6 +269,23 @@ class KrdPlan:
     def unpack_shards_rows(self, d_gathered, d_out_rows, world, row0, row1):
         self._check(self._L.krd_unpack_shards_rows(self._h, world, _ptr(d_gathered), int(row0), int(row1), _ptr(d_out_rows)))
 
+    def scatter_shard_rows(self, rank, world, d_packed, row_bounds, row_ptrs):
+        """krd_scatter_shard_rows: this rank's packed tiles -> the owners' row blocks through peer memory.
+        row_ptrs: world device addresses (ints) valid in this process."""
+        rb = np.ascontiguousarray(row_bounds, np.int32)
+        ptrs = (C.c_void_p * world)(*[C.c_void_p(int(q)) for q in row_ptrs])
+        self._check(self._L.krd_scatter_shard_rows(self._h, rank, world, _ptr(d_packed), _ptr(rb), C.cast(ptrs, C.c_void_p)))
+
+    def shard_to_host_async(self, rank, world, d_packed, d_scratch, host_matrix, copy_stream):
+        """krd_shard_to_host_async: packed tiles of (rank, world) -> pinned n x n host matrix with the copy engines."""
+        self._check(self._L.krd_shard_to_host_async(self._h, rank, world, _ptr(d_packed), _ptr(d_scratch), _ptr(host_matrix), copy_stream))
+
+    def compute_tile_range(self, d_packed, t0, t1, p=1.0, divisor=1.0):
+        self._check(self._L.krd_compute_tile_range(self._h, float(p), float(divisor), int(t0), int(t1), _ptr(d_packed)))
+
+    def tile_range_to_host_async(self, t0, t1, d_packed, d_scratch, host_matrix, copy_stream):
+        self._check(self._L.krd_tile_range_to_host_async(self._h, int(t0), int(t1), _ptr(d_packed), _ptr(d_scratch), _ptr(host_matrix), copy_stream))
+
     def compute_allgather_host(self, rank, world, comm, row0, row1, p=1.0, divisor=1.0, out_rows=None):
         """krd_compute_allgather_host: this rank's tile share, NCCL all-gather (comm = ncclComm_t as int), rows [row0, row1) on the host."""
         if out_rows is None:
@@ -360,6 +396,39 @@ def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):
         return plan.compute(p=p, divisor=divisor)
     finally:
         plan.close()
+
+
+def p2p_alloc(device, nbytes):
+    """krd_p2p_alloc: (device address, 64-byte CUDA IPC handle as bytes)."""
+    ptr = C.c_void_p()
+    hd = (C.c_ubyte * 64)()
+    st = lib().krd_p2p_alloc(device, int(nbytes), C.byref(ptr), C.cast(hd, C.c_void_p))
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
+    return int(ptr.value), bytes(hd)
+
+
+def p2p_open(device, handle):
+    ptr = C.c_void_p()
+    buf = (C.c_ubyte * 64)(*handle)
+    st = lib().krd_p2p_open(device, C.cast(buf, C.c_void_p), C.byref(ptr))
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
+    return int(ptr.value)
+
+
+def p2p_close(ptr):
+    lib().krd_p2p_close(C.c_void_p(ptr))
+
+
+def p2p_free(ptr):
+    lib().krd_p2p_free(C.c_void_p(ptr))
+
+
+def p2p_enable_peer(device, peer):
+    st = lib().krd_p2p_enable_peer(device, peer)
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
 
 
 def nccl_init_all(devices):

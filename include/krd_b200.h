@@ -171,6 +171,43 @@ krd_status krd_compute_allgather_host(krd_handle* h, double p, double divisor, i
 krd_status krd_nccl_init_all(int32_t n, const int32_t* devices, void** comms);
 void       krd_nccl_destroy(int32_t n, void** comms);
 
+/* Exchange over PEER MEMORY instead of a collective (NVLink / NVSwitch stores; csrc/krd_p2p.cu): rank `rank` scatters the
+ * packed tiles it computed (krd_compute_shard's output) straight into the row blocks of the ranks that OWN those rows —
+ * the tile into the block of its rows, its mirror into the block of its columns.  row_bounds (HOST, world + 1 entries,
+ * 0 ... n_samples) says which rows each rank owns; d_rows (HOST array of world DEVICE pointers valid in THIS process: the
+ * own block and peer mappings) are the blocks, (row_bounds[r+1] - row_bounds[r]) x n_samples doubles each.  Every cell
+ * crosses NVLink once, to the one GPU that needs it (the all-gather moves every tile to every rank).  Asynchronous on the
+ * handle's stream; a rank's block is complete once EVERY rank's call has finished — order that with any stream-ordered
+ * barrier (a one-element all-reduce) before reading it, and do not rewrite a block a peer may still be reading (bench.py
+ * alternates two sets of blocks).  world <= 16. */
+krd_status krd_scatter_shard_rows(krd_handle* h, int32_t rank, int32_t world, const double* d_packed,
+                                  const int32_t* row_bounds, double* const* d_rows);
+/* This rank's packed tiles (krd_compute_shard's output) straight into the caller's n x n HOST matrix (pinned / registered
+ * memory) with the COPY ENGINES: the tiles are transposed on the handle's stream into d_scratch (DEVICE, as large as
+ * d_packed), then one 2-D copy per tile and one per mirror are queued on copy_stream (a cudaStream_t).  Every cell of the
+ * matrix is written by exactly one rank, so no collective and no barrier is needed, and because the copies do not occupy
+ * SMs they run UNDER the next pair launch: split a rank's share into sub-shares (rank * k + q of world * k, q = 0..k-1:
+ * contiguous parts of the same tile list) and only the last sub-share's copies are exposed (bench.py --exchange host_tiles).
+ * d_packed and d_scratch must stay untouched until copy_stream has passed the copies. */
+krd_status krd_shard_to_host_async(krd_handle* h, int32_t rank, int32_t world, const double* d_packed, double* d_scratch,
+                                   double* host_matrix, void* copy_stream);
+/* The same two steps for an arbitrary range [t0, t1) of the tile list (krd_tile_list order; krd_rank_tiles gives a rank's
+ * range): d_packed receives / holds (t1 - t0) tiles.  Lets a caller cut its share UNEVENLY — a long first launch whose
+ * copies are hidden under a short last one — which equal sub-shares cannot (every extra pair launch costs ~1 ms of stream-K
+ * balance at the cfg4 shape). */
+krd_status krd_compute_tile_range(krd_handle* h, double p, double divisor, int64_t t0, int64_t t1, double* d_packed);
+krd_status krd_tile_range_to_host_async(krd_handle* h, int64_t t0, int64_t t1, const double* d_packed, double* d_scratch,
+                                        double* host_matrix, void* copy_stream);
+
+/* Row blocks that other PROCESSES can map: cudaMalloc + CUDA IPC handle (64 bytes, to be sent to the peers by any means),
+ * mapping of a peer's handle on `device`, unmapping, release.  One process driving several GPUs can use ordinary device
+ * pointers after krd_p2p_enable_peer(device, peer). */
+krd_status krd_p2p_alloc(int32_t device, int64_t bytes, void** d_ptr, unsigned char* ipc_handle_64);
+krd_status krd_p2p_open(int32_t device, const unsigned char* ipc_handle_64, void** d_ptr);
+void       krd_p2p_close(void* d_ptr);
+void       krd_p2p_free(void* d_ptr);
+krd_status krd_p2p_enable_peer(int32_t device, int32_t peer);
+
 /* The same for a caller without an NCCL communicator (e.g. one host thread per GPU in one process, as
  * `gappa-b200 --gpus G` does): the rank's packed tiles go to a HOST buffer of krd_shard_doubles() doubles
  * (D2H over that GPU's own PCIe link), and the concatenation of all ranks' buffers, in rank order, is

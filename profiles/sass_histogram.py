@@ -29,7 +29,7 @@ for line in txt.splitlines():
 dem = subprocess.run(["cu++filt"], input="\n".join(hist.keys()), capture_output=True, text=True).stdout.splitlines()
 print("instruction histogram per kernel (cuobjdump -sass %s)" % os.path.relpath(lib, ROOT))
 for (name, h), d in zip(hist.items(), dem):
-    d = re.sub(r"\(.*", "", d)
+    d = re.sub(r"\(.*", "", d.replace("(int)", "").replace("(bool)", ""))
     if not any(k in d for k in ("k_pairs", "k_tile", "k_exact", "k_subtree", "k_gram", "k_epilogue", "k_sq_one", "k_km_assign", "k_peak", "k_unpack")):
         continue
     items = sorted(((k, v) for k, v in h.items() if k != "_total"), key=lambda kv: -kv[1])

@@ -101,3 +101,65 @@ def test_row_range_unpack_equals_full_unpack(world):
     assert torch.equal(rows, full)
     assert np.array_equal(full.cpu().numpy(), plan.compute())
     plan.close()
+
+
+@pytest.mark.parametrize("world,n", [(3, 333), (8, 1000)])
+def test_peer_scatter_equals_full_unpack(world, n):
+    """krd_scatter_shard_rows with every "rank" on this one GPU (the row blocks are then ordinary local buffers): the blocks,
+    stacked, are the unpacked matrix — tile, mirror and zero diagonal, row bounds that do not fall on tile borders."""
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(77, seed=6)
+    raw, b = _binified(tree, n, 60, 2, seed=6)
+    plan = gappa_b200.KrdPlan(bins=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned(b["off"], gappa_b200.krd.binned_cells(tree, b, 2), b["mass"])
+    shard = plan.shard_doubles(world)
+    bounds = np.array([r * n // world for r in range(world + 1)], np.int32)
+    blocks = [torch.full((int(bounds[r + 1] - bounds[r]), n), -3.0, dtype=torch.float64, device="cuda") for r in range(world)]
+    packed = torch.empty(shard, dtype=torch.float64, device="cuda")
+    for r in range(world):
+        plan.compute_shard(packed, r, world)
+        plan.scatter_shard_rows(r, world, packed, bounds, [blk.data_ptr() for blk in blocks])
+    torch.cuda.synchronize()
+    got = torch.cat(blocks).cpu().numpy()
+    assert np.array_equal(got, plan.compute())
+    plan.close()
+
+
+@pytest.mark.parametrize("world,k,n", [(1, 1, 200), (3, 2, 333), (2, 4, 1000)])
+def test_copy_engine_tiles_to_host_equals_compute(world, k, n):
+    """krd_shard_to_host_async: every (virtual) rank's packed tiles go straight into one pinned n x n host matrix — tile, mirror
+    (transposed on the device), symmetric diagonal tiles, ragged edges — through 2-D copies on a second stream."""
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(77, seed=6)
+    raw, b = _binified(tree, n, 60, 2, seed=6)
+    plan = gappa_b200.KrdPlan(bins=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned(b["off"], gappa_b200.krd.binned_cells(tree, b, 2), b["mass"])
+    W = world * k
+    shard = plan.shard_doubles(W)
+    host = torch.full((n, n), -7.0, dtype=torch.float64).pin_memory()
+    side = torch.cuda.Stream()
+    bufs = [(torch.empty(shard, dtype=torch.float64, device="cuda"), torch.empty(shard, dtype=torch.float64, device="cuda")) for _ in range(W)]
+    for r in range(W):
+        plan.compute_shard(bufs[r][0], r, W)
+        plan.shard_to_host_async(r, W, bufs[r][0], bufs[r][1], host, side.cuda_stream)
+    torch.cuda.synchronize()
+    want = plan.compute()
+    assert np.array_equal(host.numpy(), want)
+    # the same through arbitrary tile ranges (an uneven cut of the list)
+    host.fill_(-7.0)
+    nt = len(gappa_b200.krd.tile_list(n)[0])
+    cuts = [0, max(1, (nt * 7) // 8), nt] if nt > 1 else [0, nt]
+    for a, c in zip(cuts[:-1], cuts[1:]):
+        pk = torch.empty((c - a) * 128 * 128, dtype=torch.float64, device="cuda"); sc = torch.empty_like(pk)
+        plan.compute_tile_range(pk, a, c)
+        plan.tile_range_to_host_async(a, c, pk, sc, host, side.cuda_stream)
+        torch.cuda.synchronize()
+    got = host.numpy()
+    assert np.max(np.abs(got - want) / np.maximum(want, 1e-300)) <= 1e-12 and np.array_equal(got, got.T)
+    plan.close()

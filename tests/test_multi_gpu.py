@@ -51,3 +51,37 @@ def test_nccl_allgather_in_one_process_equals_single_gpu(bins, p):
     # (a rank's tile share is cut between its CTAs differently than the whole list: partial sums round differently)
     assert np.max(np.abs(out - single) / np.maximum(single, 1e-300)) <= 1e-12
     assert np.array_equal(out, out.T) and np.all(np.diag(out) == 0)
+
+
+def test_peer_scatter_across_two_gpus_equals_single_gpu():
+    """krd_scatter_shard_rows over NVLink peer mappings, one process driving two GPUs (krd_p2p_enable_peer): every GPU
+    computes its tile share and stores tile + mirror straight into the row block of the GPU that owns those rows."""
+    _need_gpus(2)
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth, krd
+    G, n = 2, 700
+    tree = synth.tree_with_edges(201, seed=4)
+    mass = synth.sample_masses(tree, n, 200, seed=4)
+    krd.p2p_enable_peer(0, 1); krd.p2p_enable_peer(1, 0)
+    bounds = np.array([g * n // G for g in range(G + 1)], np.int32)
+    plans, blocks, packed = [], [], []
+    for g in range(G):
+        pl = gappa_b200.KrdPlan(device=g, bins=2)
+        pl.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+        pl.set_masses(mass["off"], mass["edge"], mass["pos"], mass["mass"])
+        plans.append(pl)
+        blocks.append(torch.full((int(bounds[g + 1] - bounds[g]), n), -3.0, dtype=torch.float64, device=f"cuda:{g}"))
+        packed.append(torch.empty(pl.shard_doubles(G), dtype=torch.float64, device=f"cuda:{g}"))
+    single = plans[0].compute(p=1.0)
+    ptrs = [b.data_ptr() for b in blocks]
+    for g in range(G):
+        plans[g].compute_shard(packed[g], g, G, p=1.0)
+        plans[g].scatter_shard_rows(g, G, packed[g], bounds, ptrs)
+    for g in range(G):
+        torch.cuda.synchronize(g)
+    got = np.concatenate([b.cpu().numpy() for b in blocks])
+    for pl in plans:
+        pl.close()
+    assert np.max(np.abs(got - single) / np.maximum(single, 1e-300)) <= 1e-12
+    assert np.array_equal(got, got.T) and np.all(np.diag(got) == 0)

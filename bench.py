@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--no-base", action="store_true", help="N = 1: skip the 1-GPU cfg4 block (strong_scaling_base)")
     ap.add_argument("--exchange", default="p2p_rows", choices=["host_tiles", "p2p_rows", "allgather_rows", "allgather_rank0", "own_tiles_host"],
                     help="N > 1: how the result tiles reach host memory (SURVEY §8e asks for an A/B)")
+    ap.add_argument("--late", type=float, default=0.0625, help="--exchange p2p_rows: fraction of the sample blocks treated as 'late' (krd_set_late_blocks): "
+                    "the rectangle outside them is copied to the host under the pair launch of the tiles that touch them (0 = no overlap)")
     ap.add_argument("--tail", type=float, default=0.125, help="--exchange host_tiles: fraction of a rank's tiles in the short LAST launch; the copies "
                     "of the long first launch run under it (0 = one launch)")
     return ap.parse_args()
@@ -566,6 +568,18 @@ def run_multi(args):
         p2p_ptrs = [[p2p_mine[k] if r == rank else gappa_b200.krd.p2p_open(local, handles[r][k]) for r in range(world)] for k in range(2)]
         p2p_own = [torch.as_tensor(_Raw(p2p_mine[k], (r1 - r0, N)), device=torch.device("cuda", local)) for k in range(2)]
         d_flag = torch.zeros(1, dtype=torch.float32, device="cuda")
+        # two-part tile order: tiles that touch the last `late` sample blocks come last (krd_set_late_blocks)
+        Tb = (N + 127) // 128
+        late = min(Tb - 1, max(1, int(round(Tb * args.late)))) if args.late > 0 else 0
+        t_split = plan.set_late_blocks(late)
+        n_tiles_all = Tb * (Tb + 1) // 2
+        a0, a1 = gappa_b200.krd.rank_tiles(t_split, rank, world)
+        b0, b1 = (t_split + q for q in gappa_b200.krd.rank_tiles(n_tiles_all - t_split, rank, world))
+        cA = min(N, (Tb - late) * 128)           # rows / columns below cA are final after the first part
+        d_pkA = torch.empty(max(1, a1 - a0) * 128 * 128, dtype=torch.float64, device="cuda")
+        d_pkB = torch.empty(max(1, b1 - b0) * 128 * 128, dtype=torch.float64, device="cuda")
+        p2p_stream = torch.cuda.Stream()
+        rect = gappa_b200.krd.copy_rect_to_host_async
     PH = 1
     if args.exchange == "host_tiles":
         # the rank's contiguous share of the tile list, cut UNEVENLY: a long first launch and a short last one (--tail); per piece
@@ -604,18 +618,7 @@ def run_multi(args):
 
     def exchange(ev=None):
         mark = (lambda k: ev[k].record(stream)) if ev else (lambda k: None)
-        if args.exchange == "p2p_rows":
-            # every rank stores its tiles (and their mirrors) straight into the owners' row blocks over NVLink; a one-element
-            # all-reduce on the same stream is the barrier after which this rank's block is complete
-            k = step_no[0] % 2
-            step_no[0] += 1
-            plan.scatter_shard_rows(rank, world, d_packed, bounds, p2p_ptrs[k])
-            mark(1)
-            dist.all_reduce(d_flag)
-            mark(2)
-            h_rows.copy_(p2p_own[k], non_blocking=True)
-            mark(3)
-        elif args.exchange == "allgather_rows":
+        if args.exchange == "allgather_rows":
             dist.all_gather_into_tensor(d_gath, d_packed)
             mark(1)
             plan.unpack_shards_rows(d_gath, d_rows, world, r0, r1)
@@ -643,10 +646,52 @@ def run_multi(args):
             plan.tile_range_to_host_async(a, b, d_pk[q], d_sc[q], h_full, out_stream.cuda_stream)
         stream.wait_stream(out_stream)             # the step ends when the last copy has landed
 
+    def step_p2p(collect=None, ev=None):
+        # Tiles (and their mirrors) are stored straight into the owners' row blocks over NVLink; a one-element all-reduce on
+        # the same stream is the barrier after which a block is complete.  Two parts: after part A (tiles that do not touch
+        # the late blocks) the rectangle [own rows] x [columns < cA] is final and goes to the host on a second stream, UNDER
+        # the pair launch of part B; only the thin late strip is copied after it.
+        k = step_no[0] % 2
+        step_no[0] += 1
+        own, hb = p2p_mine[k], h_full.data_ptr()
+        rA = min(r1, cA)                           # own rows [r0, rA) are "early", [rA, r1) late
+        stream.wait_stream(p2p_stream)
+        plan.compute_tile_range(d_pkA, a0, a1, p=p)
+        if collect is not None:
+            torch.cuda.synchronize(); collect.append(plan.stats())
+        plan.scatter_tile_range_rows(a0, a1, d_pkA, bounds, p2p_ptrs[k])
+        dist.all_reduce(d_flag)
+        if late > 0:
+            p2p_stream.wait_stream(stream)
+            if ev: ev[0].record(p2p_stream)
+            if rA > r0:
+                rect(hb + r0 * N * 8, N, own, N, cA, rA - r0, p2p_stream.cuda_stream)
+            if ev: ev[1].record(p2p_stream)
+            if b1 > b0:
+                plan.compute_tile_range(d_pkB, b0, b1, p=p)
+                if collect is not None:
+                    torch.cuda.synchronize(); collect.append(plan.stats())
+                plan.scatter_tile_range_rows(b0, b1, d_pkB, bounds, p2p_ptrs[k])
+            dist.all_reduce(d_flag)
+            if ev: ev[2].record(stream)
+            if rA > r0 and N > cA:
+                rect(hb + (r0 * N + cA) * 8, N, own + cA * 8, N, N - cA, rA - r0, stream.cuda_stream)
+            if r1 > max(r0, rA):
+                rl = max(r0, rA)
+                rect(hb + rl * N * 8, N, own + (rl - r0) * N * 8, N, N, r1 - rl, stream.cuda_stream)
+            stream.wait_stream(p2p_stream)
+            if ev: ev[3].record(stream)
+        else:
+            if ev: ev[0].record(stream); ev[1].record(stream); ev[2].record(stream)
+            rect(hb + r0 * N * 8, N, own, N, N, r1 - r0, stream.cuda_stream)
+            if ev: ev[3].record(stream)
+
     def step_device():
         plan.invalidate_F()
         if args.exchange == "host_tiles":
             return step_host_tiles()
+        if args.exchange == "p2p_rows":
+            return step_p2p()
         plan.compute_shard(d_packed, rank, world, p=p)
         exchange()
 
@@ -663,6 +708,8 @@ def run_multi(args):
         plan.set_masses_binned_device(off_np, d_all[0], d_all[1])
         if args.exchange == "host_tiles":
             step_host_tiles()
+        elif args.exchange == "p2p_rows":
+            step_p2p()
         else:
             plan.compute_shard(d_packed, rank, world, p=p)
             exchange()
@@ -672,10 +719,11 @@ def run_multi(args):
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step = timed(torch, dist, stream, step_device, args.steps, warmup)
     st = plan.stats()
-    if args.exchange == "host_tiles":          # one traced step: per-launch times of the PH sub-shares (K1 runs in the first)
+    if args.exchange in ("host_tiles", "p2p_rows"):   # one traced step: per-launch times of the parts (K1 runs in the first)
         plan.invalidate_F()
         per = []
-        step_host_tiles(per)
+        (step_host_tiles if args.exchange == "host_tiles" else step_p2p)(per)
+        PH = len(per)
         torch.cuda.synchronize()
         st = dict(per[-1])
         st["ms_pairs"] = float(sum(q["ms_pairs"] for q in per)); st["ms_epilogue"] = float(sum(q["ms_epilogue"] for q in per))
@@ -700,7 +748,15 @@ def run_multi(args):
         del Dh
     # one traced step: where the time after the pair kernel goes (CUDA events on this rank's stream)
     breakdown = None
-    if args.exchange in ("p2p_rows", "allgather_rows"):
+    if args.exchange == "p2p_rows":
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        dist.barrier(); torch.cuda.synchronize()
+        plan.invalidate_F()
+        step_p2p(None, ev)
+        torch.cuda.synchronize()
+        breakdown = {"d2h_early_rectangle_on_side_stream": ev[0].elapsed_time(ev[1]), "exposed_after_last_barrier": ev[2].elapsed_time(ev[3]),
+                     "late_blocks": late, "early_columns": cA}
+    if args.exchange == "allgather_rows":
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         dist.barrier(); torch.cuda.synchronize()
         plan.invalidate_F()
@@ -708,7 +764,7 @@ def run_multi(args):
         ev[0].record(stream)
         exchange(ev)
         torch.cuda.synchronize()
-        names = ("scatter_peer_stores", "barrier_allreduce", "d2h_row_block") if args.exchange == "p2p_rows" else ("nccl_allgather", "unpack_row_block", "d2h_row_block")
+        names = ("nccl_allgather", "unpack_row_block", "d2h_row_block")
         breakdown = {nm: ev[k].elapsed_time(ev[k + 1]) for k, nm in enumerate(names)}
     ms_e2e = timed(torch, dist, stream, step_e2e, max(2, min(args.steps, 5)), 3)
     dist.barrier()
@@ -718,6 +774,8 @@ def run_multi(args):
     one_gpu = None
     if rank == 0:
         h_one = torch.empty((N, N), dtype=torch.float64).pin_memory()
+        if args.exchange == "p2p_rows":
+            plan.set_late_blocks(0)          # the one-GPU base runs on the default tile order
 
         def step_one():
             plan.invalidate_F()

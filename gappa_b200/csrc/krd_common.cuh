@@ -128,6 +128,8 @@ struct krd_handle {
     std::unordered_map<int64_t, Sched> scheds;   // schedules by key (tile range, chunks, CTAs, diagonal cost); d_sched points into one
     int64_t force_t0 = -1, force_t1 = -1;        // pipelined ingest: explicit tile range of the next run_pairs
     bool custom_tiles = false;                   // tile list set by the pipelined ingest (phase-major), not krd_tile_list
+    int32_t late_blocks = 0;                     // krd_set_late_blocks: tiles touching the last `late_blocks` sample blocks come last
+    int64_t late_split = 0;                      // ... and start at this index of the list
 
     // ---- pipelined ingest (krd_config.pipeline, krd_pipe.cu): sample-range children whose uploads overlap the pair kernel ----
     std::vector<krd_handle*> kids;
@@ -208,6 +210,7 @@ krd_status run_pairs_slab(krd_handle* h, double p, double divisor, int rank, int
 krd_status compute_streamed(krd_handle* h, double p, double divisor, int rank, int world, double* d_out, double* d_packed);   // krd_build.cu
 krd_status unpack_shards(krd_handle* h, int world, const double* d_gathered, double* d_out);
 krd_status unpack_shard_rows(krd_handle* h, const double* d_gathered, int row0, int row1, double* d_out_rows);
+krd_status set_late_blocks(krd_handle* h, int n_late, int64_t* split);
 krd_status rank_tile_range(krd_handle* h, int rank, int world, const Tile** d_tiles, int64_t* t0, int64_t* t1);   // device tile list + the rank's share
 
 // krd_pipe.cu — pipelined ingest (krd_config.pipeline)

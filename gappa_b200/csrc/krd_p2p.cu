@@ -96,16 +96,27 @@ krd_status krd_scatter_shard_rows(krd_handle* h, int32_t rank, int32_t world, co
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
-    if (world < 1 || world > P2P_MAX_WORLD || rank < 0 || rank >= world || !d_packed || !row_bounds || !d_rows)
-        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_scatter_shard_rows: bad arguments (world <= 16)");
+    if (world < 1 || rank < 0 || rank >= world) return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_scatter_shard_rows: bad rank/world");
+    int64_t t0 = 0, t1 = 0;
+    krd_rank_tiles(krd_tile_count(h->N), rank, world, &t0, &t1);
+    return krd_scatter_tile_range_rows(h, t0, t1, d_packed, world, row_bounds, d_rows);
+}
+
+krd_status krd_scatter_tile_range_rows(krd_handle* h, int64_t t0, int64_t t1, const double* d_packed, int32_t world,
+                                       const int32_t* row_bounds, double* const* d_rows)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
+    if (world < 1 || world > P2P_MAX_WORLD || !d_packed || !row_bounds || !d_rows || t0 < 0 || t1 < t0 || t1 > krd_tile_count(h->N))
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_scatter_tile_range_rows: bad arguments (at most 16 owners)");
     if (row_bounds[0] != 0 || row_bounds[world] != h->N) return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_scatter_shard_rows: row_bounds must run from 0 to n_samples");
     for (int r = 0; r < world; ++r)
         if (row_bounds[r + 1] < row_bounds[r] || (row_bounds[r + 1] > row_bounds[r] && !d_rows[r]))
             return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_scatter_shard_rows: row_bounds must be non-decreasing and every non-empty block needs a pointer");
     KRD_CUDA(h, cudaSetDevice(h->device));
     if (h->piped) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }
-    const krd::Tile* d_tiles = nullptr; int64_t t0 = 0, t1 = 0;
-    krd_status st = rank_tile_range(h, rank, world, &d_tiles, &t0, &t1);
+    const krd::Tile* d_tiles = nullptr; int64_t u0 = 0, u1 = 0;
+    krd_status st = rank_tile_range(h, 0, 1, &d_tiles, &u0, &u1);
     if (st != KRD_OK) return st;
     if (t1 == t0) return KRD_OK;
     ScatterParams P;
@@ -168,6 +179,27 @@ krd_status krd_shard_to_host_async(krd_handle* h, int32_t rank, int32_t world, c
     int64_t t0 = 0, t1 = 0;
     krd_rank_tiles(krd_tile_count(h->N), rank, world, &t0, &t1);
     return krd_tile_range_to_host_async(h, t0, t1, d_packed, d_scratch, host_matrix, copy_stream);
+}
+
+krd_status krd_set_late_blocks(krd_handle* h, int32_t n_late_blocks, int64_t* t_split)
+{
+    if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    if (!h->have_masses) return fail(h, KRD_ERR_STATE, "no masses set");
+    if (n_late_blocks < 0) return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_late_blocks: n_late_blocks must be >= 0");
+    KRD_CUDA(h, cudaSetDevice(h->device));
+    if (h->piped) { krd_status fs = pipe_flatten(h); if (fs != KRD_OK) return fs; }
+    return set_late_blocks(h, n_late_blocks, t_split);
+}
+
+krd_status krd_copy_rect_to_host_async(double* host_dst, int64_t host_pitch_doubles, const double* d_src, int64_t src_pitch_doubles,
+                                       int64_t cols, int64_t rows, void* cuda_stream)
+{
+    if (rows <= 0 || cols <= 0) return KRD_OK;
+    if (!host_dst || !d_src || host_pitch_doubles < cols || src_pitch_doubles < cols) return fail(nullptr, KRD_ERR_INVALID_ARGUMENT, "krd_copy_rect_to_host_async: bad arguments");
+    const cudaError_t e = cudaMemcpy2DAsync(host_dst, (size_t)host_pitch_doubles * 8, d_src, (size_t)src_pitch_doubles * 8, (size_t)cols * 8, (size_t)rows,
+                                            cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(cuda_stream));
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaMemcpy2DAsync");
+    return KRD_OK;
 }
 
 krd_status krd_p2p_alloc(int32_t device, int64_t bytes, void** d_ptr, unsigned char* ipc_handle_64)

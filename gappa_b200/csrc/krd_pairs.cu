@@ -701,18 +701,35 @@ static krd_status ensure_norms(krd_handle* h)
 
 int64_t tiles_per_rank(int64_t n_tiles, int world) { return (n_tiles + world - 1) / world; }
 
+// Tile order of the handle.  Default: krd_tile_list (diagonal-major).  With late_blocks = L > 0 (krd_set_late_blocks) the list
+// has two parts: first every tile whose blocks both lie before the last L sample blocks — in the default order of that smaller
+// matrix — then the tiles that touch the last L blocks, column by column.  After the first part all cells (i, j) with i and j
+// outside the late blocks are final, so their copy to the host can run under the pair launch of the (short) second part.
+static void build_tile_order(int N, int late, std::vector<Tile>& out, int64_t* split)
+{
+    const int T = (N + TILE - 1) / TILE;
+    late = std::max(0, std::min(late, T - 1));
+    const int Ta = T - late;
+    const int64_t na = (int64_t)Ta * (Ta + 1) / 2, n = (int64_t)T * (T + 1) / 2;
+    out.resize((size_t)n);
+    std::vector<int32_t> ti((size_t)std::max<int64_t>(na, 1)), tj((size_t)std::max<int64_t>(na, 1));
+    krd_tile_list(Ta * TILE, ti.data(), tj.data());
+    for (int64_t t = 0; t < na; ++t) out[(size_t)t] = Tile{ti[(size_t)t], tj[(size_t)t]};
+    int64_t k = na;
+    for (int j = Ta; j < T; ++j) {
+        out[(size_t)k++] = Tile{j, j};
+        for (int i = 0; i < j; ++i) out[(size_t)k++] = Tile{i, j};
+    }
+    *split = na;
+}
+
 static krd_status ensure_tiles(krd_handle* h)
 {
     const int T = (h->N + TILE - 1) / TILE;   // (ld may be wider than N: squash clustering appends cluster columns)
     const int64_t n_tiles = (int64_t)T * (T + 1) / 2;
     if (h->n_tiles_alloc == n_tiles && h->d_tiles) return KRD_OK;
     if (h->custom_tiles) return fail(h, KRD_ERR_STATE, "pipelined tile list is out of date");
-    h->h_tiles.resize((size_t)n_tiles);
-    {
-        std::vector<int32_t> ti((size_t)n_tiles), tj((size_t)n_tiles);
-        krd_tile_list(h->N, ti.data(), tj.data());
-        for (int64_t t = 0; t < n_tiles; ++t) h->h_tiles[(size_t)t] = Tile{ti[(size_t)t], tj[(size_t)t]};
-    }
+    build_tile_order(h->N, h->late_blocks, h->h_tiles, &h->late_split);
     cudaFree(h->d_tiles); h->d_tiles = nullptr;
     KRD_CUDA(h, cudaMalloc(&h->d_tiles, (size_t)std::max<int64_t>(n_tiles, 1) * sizeof(Tile)));
     KRD_CUDA(h, cudaMemcpyAsync(h->d_tiles, h->h_tiles.data(), (size_t)n_tiles * sizeof(Tile), cudaMemcpyHostToDevice, h->stream));
@@ -724,6 +741,16 @@ static krd_status ensure_tiles(krd_handle* h)
     h->scheds.clear();
     h->d_sched = nullptr; h->sched_key = -1;
     return KRD_OK;
+}
+
+krd_status set_late_blocks(krd_handle* h, int n_late, int64_t* split)
+{
+    const int T = (h->N + TILE - 1) / TILE;
+    h->late_blocks = std::max(0, std::min(n_late, T - 1));
+    h->n_tiles_alloc = -1;                    // rebuild the list (and drop the cached schedules) in the new order
+    krd_status st = ensure_tiles(h);
+    if (st == KRD_OK && split) *split = h->late_split;
+    return st;
 }
 
 static void drop_schedules(krd_handle* h)

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
+    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_scatter_tile_range_rows", "krd_set_late_blocks", "krd_copy_rect_to_host_async", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
     "krd_p2p_free", "krd_p2p_enable_peer", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
@@ -112,6 +112,12 @@ def lib():
     L.krd_compute_allgather_host.argtypes = [vp, dbl, dbl, i32, i32, vp, i32, i32, vp]
     L.krd_scatter_shard_rows.restype = C.c_int
     L.krd_scatter_shard_rows.argtypes = [vp, i32, i32, vp, vp, vp]
+    L.krd_scatter_tile_range_rows.restype = C.c_int
+    L.krd_scatter_tile_range_rows.argtypes = [vp, i64, i64, vp, i32, vp, vp]
+    L.krd_set_late_blocks.restype = C.c_int
+    L.krd_set_late_blocks.argtypes = [vp, i32, C.POINTER(i64)]
+    L.krd_copy_rect_to_host_async.restype = C.c_int
+    L.krd_copy_rect_to_host_async.argtypes = [vp, i64, vp, i64, i64, i64, vp]
     L.krd_shard_to_host_async.restype = C.c_int
     L.krd_shard_to_host_async.argtypes = [vp, i32, i32, vp, vp, vp, vp]
     L.krd_compute_tile_range.restype = C.c_int
@@ -280,6 +286,18 @@ class KrdPlan:
         """krd_shard_to_host_async: packed tiles of (rank, world) -> pinned n x n host matrix with the copy engines."""
         self._check(self._L.krd_shard_to_host_async(self._h, rank, world, _ptr(d_packed), _ptr(d_scratch), _ptr(host_matrix), copy_stream))
 
+    def scatter_tile_range_rows(self, t0, t1, d_packed, row_bounds, row_ptrs):
+        rb = np.ascontiguousarray(row_bounds, np.int32)
+        n = len(rb) - 1
+        ptrs = (C.c_void_p * n)(*[C.c_void_p(int(q)) for q in row_ptrs])
+        self._check(self._L.krd_scatter_tile_range_rows(self._h, int(t0), int(t1), _ptr(d_packed), n, _ptr(rb), C.cast(ptrs, C.c_void_p)))
+
+    def set_late_blocks(self, n_late_blocks):
+        """krd_set_late_blocks: reorder the tile list (tiles touching the last blocks come last); returns the split index."""
+        sp = C.c_int64(0)
+        self._check(self._L.krd_set_late_blocks(self._h, int(n_late_blocks), C.byref(sp)))
+        return int(sp.value)
+
     def compute_tile_range(self, d_packed, t0, t1, p=1.0, divisor=1.0):
         self._check(self._L.krd_compute_tile_range(self._h, float(p), float(divisor), int(t0), int(t1), _ptr(d_packed)))
 
@@ -396,6 +414,13 @@ def earth_movers_distance(tree, masses, p=1.0, bins=0, device=0, divisor=1.0):
         return plan.compute(p=p, divisor=divisor)
     finally:
         plan.close()
+
+
+def copy_rect_to_host_async(host_dst_ptr, host_pitch, d_src_ptr, src_pitch, cols, rows, stream):
+    """krd_copy_rect_to_host_async (addresses as ints, pitches / cols in doubles)."""
+    st = lib().krd_copy_rect_to_host_async(C.c_void_p(int(host_dst_ptr)), int(host_pitch), C.c_void_p(int(d_src_ptr)), int(src_pitch), int(cols), int(rows), stream)
+    if st != KRD_OK:
+        raise KrdError(st, lib().krd_last_error(None).decode())
 
 
 def p2p_alloc(device, nbytes):

@@ -199,6 +199,23 @@ krd_status krd_compute_tile_range(krd_handle* h, double p, double divisor, int64
 krd_status krd_tile_range_to_host_async(krd_handle* h, int64_t t0, int64_t t1, const double* d_packed, double* d_scratch,
                                         double* host_matrix, void* copy_stream);
 
+/* The same scatter for an arbitrary range [t0, t1) of the handle's tile list; d_packed holds (t1 - t0) tiles; n_owners row
+ * blocks (<= 16). */
+krd_status krd_scatter_tile_range_rows(krd_handle* h, int64_t t0, int64_t t1, const double* d_packed, int32_t n_owners,
+                                       const int32_t* row_bounds, double* const* d_rows);
+/* Tile ORDER for overlapping the device-to-host copy with compute.  n_late_blocks = L > 0 reorders the handle's tile list:
+ * first every tile whose sample blocks both lie before the last L blocks (in the default order of that smaller matrix),
+ * then the tiles that touch the last L blocks; *t_split = the index where the second part starts.  Once the first part is
+ * computed (and, across GPUs, scattered and a barrier passed) all cells (i, j) with i, j < n_samples' = (T - L) * 128 are
+ * final, so that rectangle can be copied to the host (krd_copy_rect_to_host_async, copy engine) UNDER the pair launch of the
+ * short second part; afterwards only the thin strip of late columns / rows is left to copy.  The order is a property of the
+ * handle (it survives krd_set_masses* of the same size); L = 0 restores the default.  The host-only helpers krd_tile_list /
+ * krd_unpack_shards_host describe the DEFAULT order only: use the handle-based calls with a reordered handle. */
+krd_status krd_set_late_blocks(krd_handle* h, int32_t n_late_blocks, int64_t* t_split);
+/* cudaMemcpy2DAsync device -> (pinned) host of a cols x rows rectangle of doubles, pitches in doubles; no handle needed. */
+krd_status krd_copy_rect_to_host_async(double* host_dst, int64_t host_pitch_doubles, const double* d_src,
+                                       int64_t src_pitch_doubles, int64_t cols, int64_t rows, void* cuda_stream);
+
 /* Row blocks that other PROCESSES can map: cudaMalloc + CUDA IPC handle (64 bytes, to be sent to the peers by any means),
  * mapping of a peer's handle on `device`, unmapping, release.  One process driving several GPUs can use ordinary device
  * pointers after krd_p2p_enable_peer(device, peer). */

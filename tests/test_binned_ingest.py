@@ -163,3 +163,53 @@ def test_copy_engine_tiles_to_host_equals_compute(world, k, n):
     got = host.numpy()
     assert np.max(np.abs(got - want) / np.maximum(want, 1e-300)) <= 1e-12 and np.array_equal(got, got.T)
     plan.close()
+
+
+def test_late_block_tile_order_and_two_part_scatter():
+    """krd_set_late_blocks: the reordered tile list is still the whole upper triangle (same matrix from every entry point);
+    after the first part alone, the rectangle outside the late blocks is already final."""
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth, krd
+    n, world = 1000, 3
+    tree = synth.tree_with_edges(77, seed=6)
+    raw, b = _binified(tree, n, 60, 2, seed=6)
+    plan = gappa_b200.KrdPlan(bins=2)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned(b["off"], krd.binned_cells(tree, b, 2), b["mass"])
+    want = plan.compute()
+    T = (n + 127) // 128
+    split = plan.set_late_blocks(2)
+    assert split == (T - 2) * (T - 1) // 2 and plan.stats()["n_tiles"] == T * (T + 1) // 2
+    got = plan.compute()
+    assert np.max(np.abs(got - want) / np.maximum(want, 1e-300)) <= 1e-12 and np.array_equal(got, got.T)
+    cA = (T - 2) * 128
+    bounds = np.array([r * n // world for r in range(world + 1)], np.int32)
+    blocks = [torch.full((int(bounds[r + 1] - bounds[r]), n), -3.0, dtype=torch.float64, device="cuda") for r in range(world)]
+    ptrs = [blk.data_ptr() for blk in blocks]
+    nt = T * (T + 1) // 2
+    for r in range(world):                                   # part A of every "rank"
+        a0, a1 = krd.rank_tiles(split, r, world)
+        pk = torch.empty(max(1, a1 - a0) * 128 * 128, dtype=torch.float64, device="cuda")
+        plan.compute_tile_range(pk, a0, a1)
+        plan.scatter_tile_range_rows(a0, a1, pk, bounds, ptrs)
+    torch.cuda.synchronize()
+    early = torch.cat(blocks).cpu().numpy()
+    assert np.max(np.abs(early[:cA, :cA] - want[:cA, :cA]) / np.maximum(want[:cA, :cA], 1e-300)) <= 1e-12
+    assert np.all(early[cA:, :] == -3.0) and np.all(early[:, cA:] == -3.0)      # nothing of the late strip yet
+    for r in range(world):                                   # part B
+        b0, b1 = (split + q for q in krd.rank_tiles(nt - split, r, world))
+        pk = torch.empty(max(1, b1 - b0) * 128 * 128, dtype=torch.float64, device="cuda")
+        plan.compute_tile_range(pk, b0, b1)
+        plan.scatter_tile_range_rows(b0, b1, pk, bounds, ptrs)
+    torch.cuda.synchronize()
+    full = torch.cat(blocks).cpu().numpy()
+    assert np.max(np.abs(full - want) / np.maximum(want, 1e-300)) <= 1e-12 and np.array_equal(full, full.T)
+    # rectangle copy helper + back to the default order
+    host = torch.zeros((n, n), dtype=torch.float64).pin_memory()
+    krd.copy_rect_to_host_async(host.data_ptr() + 5 * 8, n, blocks[0].data_ptr() + 5 * 8, n, 100, 7, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(host.numpy()[:7, 5:105], full[:7, 5:105]) and host.numpy()[7:].sum() == 0
+    assert plan.set_late_blocks(0) == nt
+    assert np.array_equal(plan.compute(), want)
+    plan.close()

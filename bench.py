@@ -810,6 +810,10 @@ def run_multi(args):
                               "K0 + K1 replicated, sharded pair kernel, exchange, per-rank D2H",
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int((r1 - r0) * N * 8)},
             "one_gpu_same_job": one_gpu,
+            "strong_scaling": {"speedup_vs_one_gpu_same_job": (pairs / (ms_step * 1e-3)) / one_gpu["value"], "n_gpus": world,
+                               "note": "pairs/s is proportional to 1/segments, so this line (cfg4, 99,998 segments) is not comparable with the "
+                                       "--gpus 1 line (cfg2, 49,995 segments): the one-GPU base of THIS workload is one_gpu_same_job here and "
+                                       "strong_scaling_base in the --gpus 1 line"},
             "gpu_launches": (int(st["launches"]) + 1) * args.steps,
             "clocks": clocks,
             "roofline": roof, "roofline_build_F": k1,

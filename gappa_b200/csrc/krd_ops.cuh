@@ -24,16 +24,30 @@ __device__ __forceinline__ double kr_rsqrt_seed_abs(double d)   // ~ 1/sqrt(|d|)
     return __hiloint2double(xh < 0x00100000 ? 0 : __double2hiint(r), __double2loint(r));
 }
 
+// Seed for the 3-instruction form below: instead of replacing an infinite seed by 0 (compare + select), its high word is
+// clamped to 2^512 with ONE integer min.  Normal x >= 2^-1022 have r <= 2^511 and are untouched; x = 0 gives y = 0 * 2^512 = 0
+// exactly; a subnormal x (seed +inf, flushed) gives y = x 2^512 < 2^-510, t in (-1, 3], result < 2^-508: zero for every purpose.
+__device__ __forceinline__ double kr_rsqrt_seed_clamped(double d)
+{
+    const int xh = __double2hiint(d) & 0x7fffffff;
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(__hiloint2double(xh, __double2loint(d))));
+    return __hiloint2double(min(__double2hiint(r), 0x5ff00000), __double2loint(r));
+}
+
 // Shorter forms: the reference's std::pow is correctly rounded, the bar is 1e-10, so ONE second-order step is enough.
 // With r = (1 + q)/sqrt(x), |q| <= 2^-22, both forms below return sqrt(x) (1 - 3/2 q^2 - ...): relative error <= 8.6e-14.
-//   KRD_SQRT_SHORT = 2 (default)  y = x r,  e = 1 - y r,  s = y + (y e)/2        4 FP64 (DMUL, DFMA, DMUL, DFMA)
+//   KRD_SQRT_SHORT = 2            y = x r,  e = 1 - y r,  s = y + (y e)/2        4 FP64 (DMUL, DFMA, DMUL, DFMA)
 //   KRD_SQRT_SHORT = 1            y = x r,  s = y + (x - y^2) h,  h = r/2        3 FP64 + the integer work for h
 //   KRD_SQRT_SHORT = 0            the 5-instruction third-order step above (error 2^-64)
+//   KRD_SQRT_SHORT = 3 (default)  y = x r,  t = 3 - y r,  2 s = y t                3 FP64 (DMUL, DFMA, DMUL); the 1/2 is folded
+//                                 into the segment length (exact), only in kr_row_sqrt (the pair kernel's p = 1/2 body):
+//                                 2 s = sqrt(x) (1 + q)(2 - 2q - q^2) = 2 sqrt(x) (1 - 3/2 q^2 - ...): the same error as form 2
 // Measured at the cfg2 shape (pair kernel, p = 1/2): 12.9 ms / 14.1 ms / 14.8 ms.  Per operator the kernel issues
 // DADD + sqrt + DFMA on the FP64 pipe (2 issue cycles each) plus MUFU, LOP3, ISETP, SEL and a MOV for the seed: form 2 is
 // FP64-pipe-bound at 12 cycles, form 1 needs h as a second register pair (VIADD, SEL, MOV) and becomes issue-bound at ~15.
 #ifndef KRD_SQRT_SHORT
-#define KRD_SQRT_SHORT 2
+#define KRD_SQRT_SHORT 3
 #endif
 __device__ __forceinline__ void kr_rsqrt_seed_abs2(double d, double& r, double& h)   // r ~ 1/sqrt(|d|), h = r/2; both 0-ish for |d| < 2^-1022
 {
@@ -48,7 +62,7 @@ __device__ __forceinline__ void kr_rsqrt_seed_abs2(double d, double& r, double& 
 
 __device__ __forceinline__ double kr_sqrt_abs(double d)
 {
-#if KRD_SQRT_SHORT == 2
+#if KRD_SQRT_SHORT >= 2   // (form 3 exists only in kr_row_sqrt, which can fold the 1/2 into the segment length)
     const double r = kr_rsqrt_seed_abs(d);
     const double y = fabs(d) * r;
     return fma(y * fma(-y, r, 1.0), 0.5, y);
@@ -75,7 +89,17 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
     double d[NC], r[NC], e[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) d[c] = a - b[c];
-#if KRD_SQRT_SHORT == 2   // second-order step in the e form: y = x r, e = 1 - y r, s = y + (y e)/2 -> 4 FP64, no h
+#if KRD_SQRT_SHORT == 3   // y = x r, t = 3 - y r, 2 sqrt = y t; the caller's l is halved here once per row
+#pragma unroll
+    for (int c = 0; c < NC; ++c) r[c] = kr_rsqrt_seed_clamped(d[c]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = fabs(d[c]) * r[c];          // y
+#pragma unroll
+    for (int c = 0; c < NC; ++c) e[c] = fma(-d[c], r[c], 3.0);      // t
+#pragma unroll
+    for (int c = 0; c < NC; ++c) d[c] = d[c] * e[c];                // 2 sqrt
+    l *= 0.5;
+#elif KRD_SQRT_SHORT == 2   // second-order step in the e form: y = x r, e = 1 - y r, s = y + (y e)/2 -> 4 FP64, no h
 #pragma unroll
     for (int c = 0; c < NC; ++c) r[c] = kr_rsqrt_seed_abs(d[c]);
 #pragma unroll

@@ -143,7 +143,7 @@ __device__ __forceinline__ void kr_row_sqrt(double a, const double* __restrict__
 //   exp2: t = k/32 + g, |g| <= 1/64; 2^t = 2^(k>>5) * 2^((k&31)/32) * (1 + g (C1 + ... g C4))   (truncation 1.25e-12)
 // tab = [invc 64][logc 64][2^(i/32) 32] in shared memory (make_pow_tables() below), entry stride TS.
 #ifndef KRD_POW_I2F
-#define KRD_POW_I2F 0
+#define KRD_POW_I2F 1   // pair kernel (kr_pow_acc16): 1 = the exponent through I2F (41.5 ms at the cfg2 shape against 42.2 with the 2^52 trick), 2 = k as well (41.9)
 #endif
 constexpr int POW_LOGN = 64, POW_EXPN = 32;
 constexpr int POW_TAB = 2 * POW_LOGN + POW_EXPN;
@@ -196,6 +196,83 @@ __device__ __forceinline__ double kr_pow(double x, double p, const double* __res
     const double sc = __hiloint2double((__double2hiint(s0) + ((k >> 5) << 20)) & keep, __double2loint(s0) & keep);
     return fma(sc, g * w, sc);
 }
+// The pair kernel's form of  acc += l * |d|^p  (the arithmetic of kr_pow with fewer instructions around it — the general-p
+// body is ISSUE-bound: 20 FP64 instructions per operator against 31 others before this form; 19 against 17 now):
+//  * d comes in SIGNED: |d| is an operand modifier of the one FP64 instruction that reads it, and the integer side masks
+//    the sign away (fabs() on a value that is then taken apart as integers costs a DADD on the FP64 pipe);
+//  * the mantissa is not rebuilt as a double m in [1, 2): r = m / c - 1 = |d| * (2^-e / c) - 1, and 2^-e / c is the table
+//    value with its exponent field lowered IN PLACE (mask + three-input add on the loaded high word, no register-pair move).
+//    Exact (powers of two) as long as the field stays positive: e <= 1021, i.e. |d| < 2^1022 ~ 4.5e307;
+//  * tables in shared memory at an 8 KB-aligned address `tb` (32-bit shared address + 8 * (lane & 15)): [invc 64][logc 64]
+//    [exp 32], every entry 16 times (128 B per entry), so an entry address is (index bits) | tb — ONE lop3 after the shift,
+//    no add — and logc / exp are reached with immediate offsets (+8192, +16384) of ld.shared;
+//  * the exp entries carry their high word pre-compensated by -(i << 15): the scale's exponent field is then
+//    hi' + k * 32768 (one IMAD) instead of ((k >> 5) << 20) + hi (shift, mask, add);
+//  * results below 2^-1022 need no flag: k is clamped to -1023 * 32, where the scale's high word becomes
+//    0x3ff00000 - (1023 << 20) = 0 and its low word (entry 0 = 1.0) is 0: the scale is exactly +0.  (For k in between, the
+//    exponent field is 0 and the scale some subnormal: an absolute error below 2^-1022 per operator, as before.)
+//    d = 0 / subnormal selects the same clamp value (one compare, one select) -> contributes exactly 0 for every p.
+#ifndef KRD_POW_FAST16
+#define KRD_POW_FAST16 1
+#endif
+#ifndef KRD_POW_PSCALE
+#define KRD_POW_PSCALE 0
+#endif
+__device__ __forceinline__ void kr_pow_acc16(double d, double p, double l, uint32_t tb, double& acc)
+{
+    const int hi = __double2hiint(d);
+    const int eb = hi & 0x7ff00000;                                     // biased exponent, in place
+    uint32_t a1;
+    asm("lop3.b32 %0, %1, 0x1f80, %2, 0xEA;" : "=r"(a1) : "r"((uint32_t)hi >> 7), "r"(tb));   // (j * 128) | tb, j = top 6 mantissa bits
+    double invc, logc;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(invc) : "r"(a1));
+    asm("ld.shared.f64 %0, [%1+8192];" : "=d"(logc) : "r"(a1));
+    const double sinvc = __hiloint2double(__double2hiint(invc) - eb + 0x3ff00000, __double2loint(invc));   // 2^-e / c
+    const double r = fma(fabs(d), sinvc, -1.0);
+#if KRD_POW_PSCALE   // p folded into the polynomial and the logc table (filled as p * logc): t = p e + (r q' + logc') — one FP64 less
+    double q = fma(r, 0.28853900817779268 * p, -0.36067376022224085 * p);   // (loop-invariant products: hoisted)
+    q = fma(r, q, 0.48089834696298783 * p);
+    q = fma(r, q, -0.72134752044448170 * p);
+    q = fma(r, q, 1.4426950408889634 * p);
+#else
+    double q = fma(r, 0.28853900817779268, -0.36067376022224085);
+    q = fma(r, q, 0.48089834696298783);
+    q = fma(r, q, -0.72134752044448170);
+    q = fma(r, q, 1.4426950408889634);
+#endif
+#if KRD_POW_I2F
+    const double ed = (double)((eb >> 20) - 1023);
+#else
+    const double ed = __hiloint2double(0x43300000, (eb >> 20) + 0x7ffffc01) - 4503601774854144.0;   // (e ^ 0x80000000 = e + 2^31)
+#endif
+#if KRD_POW_PSCALE
+    const double t = fma(p, ed, fma(r, q, logc));
+#else
+    const double L = fma(r, q, logc) + ed;
+    const double t = p * L;
+#endif
+    const double MAGIC = 6755399441055744.0;
+    double kd = fma(t, 32.0, MAGIC);
+    const int k = __double2loint(kd);
+#if KRD_POW_I2F >= 2
+    kd = (double)k;                                                    // = kd - MAGIC (|32 t| < 2^31), on the conversion unit
+#else
+    kd -= MAGIC;
+#endif
+    const double g = fma(kd, -0.03125, t);
+    double w = fma(g, 9.6181291076284772e-3, 5.5504108664821580e-2);
+    w = fma(g, w, 2.4022650695910071e-1);
+    w = fma(g, w, 6.9314718055994531e-1);
+    int kc = min(max(k, -1023 * 32), 1023 * 32);
+    asm("{\n\t.reg .pred z;\n\tsetp.eq.s32 z, %1, 0;\n\tselp.s32 %0, -32736, %0, z;\n\t}" : "+r"(kc) : "r"(eb));   // d = 0 or subnormal
+    uint32_t a2;
+    asm("lop3.b32 %0, %1, 0xf80, %2, 0xEA;" : "=r"(a2) : "r"((uint32_t)kc << 7), "r"(tb));    // ((k & 31) * 128) | tb
+    double s0;
+    asm("ld.shared.f64 %0, [%1+16384];" : "=d"(s0) : "r"(a2));
+    const double sc = __hiloint2double((int)((uint32_t)__double2hiint(s0) + (uint32_t)kc * 32768u), __double2loint(s0));
+    acc = fma(l, fma(sc, g * w, sc), acc);
+}
+
 __device__ __forceinline__ double kr_powi(double x, int n)   // n >= 1, warp-uniform
 {
     double r = (n & 1) ? x : 1.0, base = x;

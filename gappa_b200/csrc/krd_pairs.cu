@@ -115,6 +115,14 @@ __device__ unsigned long long g_item_time[2 * 4096];
 #endif
 // unroll factor of the segment loop: the short operators (p = 1, 2) are unrolled 4x; the long ones keep ONE segment
 // (64 independent operators, fixed accumulator registers) as the loop body so that it stays inside the instruction cache
+#ifndef KRD_PHALF_UNROLL
+#define KRD_PHALF_UNROLL 1
+#endif
+#ifndef KRD_GENERIC_UNROLL
+#define KRD_GENERIC_UNROLL 1
+#endif
+// segment-loop unrolling of the halved modes' four-row body (chunk_math_rows4)
+constexpr int rows4_unroll(int mode) { return mode == MODE_PHALF ? KRD_PHALF_UNROLL : mode == MODE_GENERIC ? KRD_GENERIC_UNROLL : 1; }
 constexpr int mode_unroll(int mode) { return (mode == MODE_PHALF || mode == MODE_INT || mode == MODE_GENERIC || mode == MODE_LIBPOW) ? 1 : (mode == MODE_P3 || mode == MODE_P4) ? KRD_P34_UNROLL : KRD_P12_UNROLL; }
 
 // Integer exponents 5..16 with the exponent as a template parameter: one segment = 64 independent, fully static operator
@@ -265,7 +273,7 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
                                                  int half, double (&acc)[4][8])
 {
     constexpr int NC = 8 - 2 * QMIN;
-#pragma unroll 1
+#pragma unroll (rows4_unroll(MODE))
     for (int kk = 0; kk < KC; ++kk) {
         double a[4], b[8];
         const double l = sL[kk];
@@ -282,6 +290,12 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
         if (MODE == MODE_PHALF) {
 #pragma unroll
             for (int r = 0; r < 4; ++r) kr_row_sqrt<NC>(a[r], b + 2 * QMIN, l, &acc[r][2 * QMIN]);
+        } else if (MODE == MODE_GENERIC && KRD_POW_FAST16) {
+            const uint32_t tb = (uint32_t)__cvta_generic_to_shared(tab);
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int cc = 2 * QMIN; cc < 8; ++cc) kr_pow_acc16(a[r] - b[cc], p, l, tb, acc[r][cc]);
         } else {
 #pragma unroll
             for (int r = 0; r < 4; ++r)
@@ -339,8 +353,19 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
     double* spill = reinterpret_cast<double*>(smem_raw + (size_t)STM * STAGE_DOUBLES * sizeof(double) + 2 * STM * sizeof(uint64_t)) + threadIdx.x;
 
     // general p: the pow tables, every entry POW_TS_PAIR times (lane L reads copy L & 15: conflict-free for any index)
-    __shared__ double s_tab_all[MODE == MODE_GENERIC ? POW_TAB * POW_TS_PAIR : 1];
-    if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB * POW_TS_PAIR; k += NT) s_tab_all[k] = g_pow_tab[k / POW_TS_PAIR];   // visible after the barrier below
+    // kr_pow_acc16 forms entry addresses with OR: the tables must start at a multiple of 8 KB of the shared window.  An
+    // alignment attribute does not give that (the first 1 KB of the window is reserved and the section starts behind it),
+    // so the array is 8 KB longer and the start is rounded up at run time.  The exp entries carry hi - (i << 15).
+    constexpr int TAB_PAD = (MODE == MODE_GENERIC && KRD_POW_FAST16) ? 8192 / 8 : 0;
+    __shared__ __align__(16) double s_tab_raw[MODE == MODE_GENERIC ? POW_TAB * POW_TS_PAIR + TAB_PAD : 1];
+    double* const s_tab_all = s_tab_raw + (TAB_PAD ? ((8192u - ((uint32_t)__cvta_generic_to_shared(s_tab_raw) & 8191u)) & 8191u) / 8 : 0);
+    if (MODE == MODE_GENERIC) for (int k = threadIdx.x; k < POW_TAB * POW_TS_PAIR; k += NT) {   // visible after the barrier below
+        const int ent = k / POW_TS_PAIR;
+        double v = g_pow_tab[ent];
+        if (KRD_POW_FAST16 && KRD_POW_PSCALE && ent >= POW_LOGN && ent < 2 * POW_LOGN) v *= P.p;
+        if (KRD_POW_FAST16 && ent >= 2 * POW_LOGN) v = __hiloint2double(__double2hiint(v) - ((ent - 2 * POW_LOGN) << 15), __double2loint(v));
+        s_tab_all[k] = v;
+    }
     const double* const s_tab = s_tab_all + (MODE == MODE_GENERIC ? (threadIdx.x & (POW_TS_PAIR - 1)) : 0);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -36,7 +36,10 @@ constexpr size_t SMEM_BYTES = (size_t)ST * STAGE_DOUBLES * sizeof(double) + 2 * 
 // accumulators resident the compiler has ~45 doubles left for the operators' temporaries, interleaves 4-5 dependency
 // chains and the FP64 latency shows (computing only four rows ran 1.41x faster per operator, profiles/r1o_long_ops.txt).
 // These modes need a fraction of the operand bandwidth, so the ring shrinks to 4 stages and leaves room for the spill.
-constexpr bool mode_is_halved(int mode) { return mode == MODE_PHALF || mode == MODE_GENERIC || mode == MODE_LIBPOW; }
+#ifndef KRD_PHALF_HALVED
+#define KRD_PHALF_HALVED 1
+#endif
+constexpr bool mode_is_halved(int mode) { return (mode == MODE_PHALF && KRD_PHALF_HALVED) || mode == MODE_GENERIC || mode == MODE_LIBPOW; }
 constexpr int stages_for(int mode) { return mode_is_halved(mode) ? 4 : ST; }
 constexpr size_t SPILL_BYTES = (size_t)32 * NT * sizeof(double);
 constexpr size_t smem_bytes_for(int mode)

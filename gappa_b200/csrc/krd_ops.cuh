@@ -216,9 +216,14 @@ __device__ __forceinline__ double kr_pow(double x, double p, const double* __res
 #define KRD_POW_FAST16 1
 #endif
 #ifndef KRD_POW_PSCALE
-#define KRD_POW_PSCALE 0
+#define KRD_POW_PSCALE 1   // p folded into the log2 polynomial (coefficients = kernel parameters) and the logc table: one FP64 instruction less
 #endif
-__device__ __forceinline__ void kr_pow_acc16(double d, double p, double l, uint32_t tb, double& acc)
+struct PowCoef { double c5, c4, c3, c2, c1; };   // p / (5 ln2), -p / (4 ln2), p / (3 ln2), -p / (2 ln2), p / ln2
+static inline PowCoef pow_coef(double p)
+{
+    return PowCoef{0.28853900817779268 * p, -0.36067376022224085 * p, 0.48089834696298783 * p, -0.72134752044448170 * p, 1.4426950408889634 * p};
+}
+__device__ __forceinline__ void kr_pow_acc16(double d, double p, double l, uint32_t tb, double& acc, const PowCoef& pc)
 {
     const int hi = __double2hiint(d);
     const int eb = hi & 0x7ff00000;                                     // biased exponent, in place
@@ -230,10 +235,10 @@ __device__ __forceinline__ void kr_pow_acc16(double d, double p, double l, uint3
     const double sinvc = __hiloint2double(__double2hiint(invc) - eb + 0x3ff00000, __double2loint(invc));   // 2^-e / c
     const double r = fma(fabs(d), sinvc, -1.0);
 #if KRD_POW_PSCALE   // p folded into the polynomial and the logc table (filled as p * logc): t = p e + (r q' + logc') — one FP64 less
-    double q = fma(r, 0.28853900817779268 * p, -0.36067376022224085 * p);   // (loop-invariant products: hoisted)
-    q = fma(r, q, 0.48089834696298783 * p);
-    q = fma(r, q, -0.72134752044448170 * p);
-    q = fma(r, q, 1.4426950408889634 * p);
+    double q = fma(r, pc.c5, pc.c4);      // coefficients from the kernel parameters: constant-bank operands (as registers they
+    q = fma(r, q, pc.c3);                 // made every DFMA of the chain a three-register-source instruction: slower)
+    q = fma(r, q, pc.c2);
+    q = fma(r, q, pc.c1);
 #else
     double q = fma(r, 0.28853900817779268, -0.36067376022224085);
     q = fma(r, q, 0.48089834696298783);

@@ -61,6 +61,7 @@ struct PairParams {
     int64_t ld;
     double p;
     int N;                 // samples (columns >= N are zero padding: ragged last block)
+    PowCoef pc;            // general p: p times the log2 polynomial's coefficients (constant-bank operands of the DFMAs)
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
@@ -273,7 +274,7 @@ __device__ __forceinline__ void chunk_math(const double* __restrict__ pa, const 
 template <int MODE, int QMIN>
 __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, const double* __restrict__ pb,
                                                  const double* __restrict__ sL, double p, const double* __restrict__ tab,
-                                                 int half, double (&acc)[4][8])
+                                                 int half, double (&acc)[4][8], const PowCoef& pc)
 {
     constexpr int NC = 8 - 2 * QMIN;
 #pragma unroll (rows4_unroll(MODE))
@@ -298,7 +299,7 @@ __device__ __forceinline__ void chunk_math_rows4(const double* __restrict__ pa, 
 #pragma unroll
             for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int cc = 2 * QMIN; cc < 8; ++cc) kr_pow_acc16(a[r] - b[cc], p, l, tb, acc[r][cc]);
+                for (int cc = 2 * QMIN; cc < 8; ++cc) kr_pow_acc16(a[r] - b[cc], p, l, tb, acc[r][cc], pc);
         } else {
 #pragma unroll
             for (int r = 0; r < 4; ++r)
@@ -473,12 +474,12 @@ __global__ void __launch_bounds__(NT, 1) k_pairs(const PairParams P)
                             for (int cc = 0; cc < 8; ++cc) { const double t = spill[(r * 8 + cc) * NT]; spill[(r * 8 + cc) * NT] = h4[r][cc]; h4[r][cc] = t; }
                         act ^= 1;
                     }
-                    if (MODE == MODE_GENERIC || MODE == MODE_LIBPOW) { chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); continue; }   // one code variant
+                    if (MODE == MODE_GENERIC || MODE == MODE_LIBPOW) { chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4, P.pc); continue; }   // one code variant
                     switch (qmin) {
-                        case 0: chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4); break;
-                        case 1: chunk_math_rows4<MODE, 1>(pa, pb, sL, P.p, s_tab, act, h4); break;
-                        case 2: chunk_math_rows4<MODE, 2>(pa, pb, sL, P.p, s_tab, act, h4); break;
-                        default: chunk_math_rows4<MODE, 3>(pa, pb, sL, P.p, s_tab, act, h4); break;
+                        case 0: chunk_math_rows4<MODE, 0>(pa, pb, sL, P.p, s_tab, act, h4, P.pc); break;
+                        case 1: chunk_math_rows4<MODE, 1>(pa, pb, sL, P.p, s_tab, act, h4, P.pc); break;
+                        case 2: chunk_math_rows4<MODE, 2>(pa, pb, sL, P.p, s_tab, act, h4, P.pc); break;
+                        default: chunk_math_rows4<MODE, 3>(pa, pb, sL, P.p, s_tab, act, h4, P.pc); break;
                     }
                 }
             } else if (MODE == MODE_P2G) {
@@ -935,7 +936,7 @@ static krd_status run_pairs_once(krd_handle* h, double p, double divisor, int ra
     PairParams P;
     P.F = slab ? slab->F : (mode == MODE_P2G) ? h->d_Fg : h->d_F;
     P.len = ((mode == MODE_P2) ? h->d_sqrt_len : h->d_len) + (slab ? slab->row0 : 0);
-    P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p; P.N = h->N;
+    P.tiles = h->d_tiles + t0; P.items = d_items; P.cta_item_off = d_cta_off; P.ws = h->d_ws; P.ld = h->ld; P.p = p; P.N = h->N; P.pc = pow_coef(p);
     cudaError_t e;
     switch (mode) {
         case MODE_P1: e = launch_pairs<MODE_P1>(P, G, h->stream); break;

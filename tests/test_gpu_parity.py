@@ -375,6 +375,30 @@ def test_underflowing_terms_are_flushed_to_zero(gb, oracle_mod):
         assert rel_err(got[~within], want[~within]) <= 1e-10, p
 
 
+@pytest.mark.parametrize("scale", [1.0, 1e-150, 1e120])
+@pytest.mark.parametrize("p", [0.3, 1.7])
+def test_general_exponent_identical_samples_and_extreme_magnitudes(gb, oracle_mod, p, scale):
+    """The pair kernel's general-p operator (kr_pow_acc16) takes |d| apart as integers: identical samples (d = 0 on every
+    segment) must give exactly 0 for p below and above 1, and unnormalised masses far from 1 (exponent fields near both
+    ends of the table arithmetic) must stay within the bar."""
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(47, seed=5)
+    base = synth.sample_masses(tree, 70, 50, seed=5)
+    n0 = 70
+    off = np.concatenate([base["off"], base["off"][-1] + base["off"][1:11]])            # samples 70..79 = copies of 0..9
+    m10 = int(base["off"][10])
+    masses = dict(off=off, edge=np.concatenate([base["edge"], base["edge"][:m10]]),
+                  pos=np.concatenate([base["pos"], base["pos"][:m10]]),
+                  mass=np.concatenate([base["mass"], base["mass"][:m10]]) * scale)
+    got = gb.earth_movers_distance(tree, masses, p=p, bins=2)
+    want = oracle_mod.port_matrix(tree, masses, p=p, bins=2)
+    for k in range(10):
+        assert got[k, n0 + k] == 0.0 and got[n0 + k, k] == 0.0 and want[k, n0 + k] == 0.0
+    off_diag = ~np.eye(80, dtype=bool)
+    assert np.all(np.isfinite(got))
+    assert rel_err(got[off_diag], want[off_diag]) <= TOL, (p, scale)
+
+
 @pytest.mark.parametrize("p2_mode", [1, 2])
 def test_positions_outside_the_branch_keep_signed_lengths(gb, oracle_mod, p2_mode):
     """Exact mode: a jplace distal/proximal length outside the branch gives pos < 0 or pos > bl and the reference keeps the

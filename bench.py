@@ -289,8 +289,18 @@ def timed(torch, dist, stream, fn, steps, warmup):
 
 
 def pinned(torch, a):
-    t = torch.from_numpy(a.view(np.int32) if a.dtype == np.uint32 else a)
+    t = torch.from_numpy(a.view(np.int32) if a.dtype == np.uint32 else a.view(np.int16) if a.dtype == np.uint16 else a)
     return t.pin_memory()
+
+
+def transport_cells(cell, spec):
+    """The cell ids in the narrowest form the C ABI takes: uint16 (krd_set_masses_binned16, 10 B per entry with the mass)
+    when edges * bins <= 65536 — every BASELINE config — else uint32 (12 B per entry)."""
+    return cell.astype(np.uint16) if spec["edges"] * spec["bins"] <= 65536 else cell
+
+
+def cell_form(spec):
+    return ("krd_set_masses_binned16", 10) if spec["edges"] * spec["bins"] <= 65536 else ("krd_set_masses_binned", 12)
 
 
 def measure_single(local, spec, tree, comp, steps, warmup, sample_clocks, e2e_steps):
@@ -301,7 +311,7 @@ def measure_single(local, spec, tree, comp, steps, warmup, sample_clocks, e2e_st
     N, p, bins = spec["samples"], spec["p"], spec["bins"]
     pairs = N * (N - 1) / 2
     stream = torch.cuda.current_stream()
-    h_off, h_cell, h_mass = pinned(torch, comp["off"]), pinned(torch, comp["cell"]), pinned(torch, comp["mass"])
+    h_off, h_cell, h_mass = pinned(torch, comp["off"]), pinned(torch, transport_cells(comp["cell"], spec)), pinned(torch, comp["mass"])
     h_out = torch.empty((N, N), dtype=torch.float64).pin_memory()
     h2d_bytes = sum(t.numel() * t.element_size() for t in (h_off, h_cell, h_mass))
 
@@ -378,8 +388,8 @@ def run_single(args):
         "value_includes": "F build (K1) + pair kernel + epilogue + D2H of the n x n matrix into pinned host memory (%.3f ms of the step)" % r["ms_d2h"],
         "masses": int(st["n_masses"]),
         "e2e": {"value": pairs / (r["ms_e2e"] * 1e-3), "unit": UNIT, "ms_per_step": r["ms_e2e"],
-                "ingest": "krd_set_masses_binned (12 B per entry: cell = edge*bins+bin, mass) on a pipeline=1 handle: up to 8 sample blocks, "
-                          "upload overlapped with K0/K1/pair phases",
+                "ingest": "%s (%d B per entry: cell = edge*bins+bin, mass) on a pipeline=1 handle: up to 8 sample blocks, "
+                          "upload overlapped with K0/K1/pair phases" % cell_form(spec),
                 "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"]},
         "gpu_launches": r["launches"] * args.steps,
         "clocks": r["clocks"],
@@ -609,12 +619,13 @@ def run_multi(args):
     # rest over NVLink (the one exchange step on the input side; F itself is built replicated)
     per = (M + world - 1) // world
     lo, hi = min(rank * per, M), min((rank + 1) * per, M)
-    h_cell = pinned(torch, np.ascontiguousarray(comp["cell"][lo:hi]))
+    h_cell = pinned(torch, transport_cells(np.ascontiguousarray(comp["cell"][lo:hi]), spec))
+    cell_dt = h_cell.dtype                                      # int16 (10 B per entry with the mass) or int32
     h_mass = pinned(torch, np.ascontiguousarray(comp["mass"][lo:hi]))
     off_np = np.ascontiguousarray(comp["off"], np.int64)
-    d_part = [torch.zeros(per, dtype=torch.int32, device="cuda"), torch.zeros(per, dtype=torch.float64, device="cuda")]
-    d_all = [torch.empty(per * world, dtype=torch.int32, device="cuda"), torch.empty(per * world, dtype=torch.float64, device="cuda")]
-    h2d_bytes = (hi - lo) * 12 + off_np.nbytes
+    d_part = [torch.zeros(per, dtype=cell_dt, device="cuda"), torch.zeros(per, dtype=torch.float64, device="cuda")]
+    d_all = [torch.empty(per * world, dtype=cell_dt, device="cuda"), torch.empty(per * world, dtype=torch.float64, device="cuda")]
+    h2d_bytes = (hi - lo) * (8 + h_cell.element_size()) + off_np.nbytes
     copy_stream = torch.cuda.Stream()
     up_events = [torch.cuda.Event() for _ in range(2)]
     head_blk = workloads.head(comp, min(N, 64))
@@ -708,7 +719,7 @@ def run_multi(args):
                 up_events[k].record(copy_stream)
         for k in (1, 0):
             stream.wait_event(up_events[k])
-            dist.all_gather_into_tensor(d_all[k], d_part[k])
+            dist.all_gather_into_tensor(d_all[k].view(torch.uint8), d_part[k].view(torch.uint8))   # (bytes: NCCL has no 16-bit integer type)
         plan.set_masses_binned_device(off_np, d_all[0], d_all[1])
         if args.exchange == "host_tiles":
             step_host_tiles()
@@ -810,8 +821,8 @@ def run_multi(args):
             "ms_pairs_per_launch": st.get("ms_pairs_per_launch"), "exchange_breakdown_ms_rank0": breakdown, "ms_host_unpack_untimed": ms_host_unpack,
             "shard_check": {"samples": ns, "max_rel_diff_sharded_vs_single_gpu": shard_diff, "bound": 1e-12},
             "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "ingest": "every rank uploads 1/N of the compact entries (12 B each) on a copy stream, NVLink all-gather of the two arrays, "
-                              "K0 + K1 replicated, sharded pair kernel, exchange, per-rank D2H",
+                    "ingest": "every rank uploads 1/N of the compact entries (%s, %d B each) on a copy stream, NVLink all-gather of the two arrays, "
+                              "K0 + K1 replicated, sharded pair kernel, exchange, per-rank D2H" % cell_form(spec),
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int((r1 - r0) * N * 8)},
             "one_gpu_same_job": one_gpu,
             "strong_scaling": {"speedup_vs_one_gpu_same_job": (pairs / (ms_step * 1e-3)) / one_gpu["value"], "n_gpus": world,

@@ -62,7 +62,7 @@ static void pipe_quiesce(krd_handle* h)
 
 static void free_masses(krd_handle* h)   // buffers are kept for reuse; only the state is dropped
 {
-    h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr; h->d_cell32 = nullptr; h->binned_input = false;
+    h->d_edge = nullptr; h->d_pos = nullptr; h->d_mass = nullptr; h->d_cell32 = nullptr; h->binned_input = false; h->cell_bytes = 4;
     h->have_masses = false; h->F_valid = false;
 }
 
@@ -158,21 +158,35 @@ krd_status krd_set_tree(krd_handle* h, int32_t n_edges, const int32_t* parent_no
     return st;
 }
 
-// Host arrays -> HBM + K0.  cell32 != nullptr: the compact binned form (cell = edge * bins + bin, 12 B per entry).
+// The compact form needs bins >= 1 and every cell id edge * bins + bin representable in the cell type.
+static krd_status check_cell_range(krd_handle* h, int cell_bytes)
+{
+    if (cell_bytes == 0) return KRD_OK;
+    const int64_t cells = (int64_t)h->E * h->cfg.bins;
+    if (h->cfg.bins < 1 || cells > 0xFFFFFFF0ll)
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned needs krd_config.bins >= 1 and n_edges * bins < 2^32");
+    if (cell_bytes == 2 && cells > 65536)
+        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned16 needs n_edges * bins <= 65536 (" + std::to_string(cells) +
+                                                  " here): use krd_set_masses_binned");
+    return KRD_OK;
+}
+
+// Host arrays -> HBM + K0.  cell_bytes 4 / 2: the compact binned form (cell = edge * bins + bin as uint32_t / uint16_t,
+// 12 / 10 B per entry); 0: (edge, pos, mass), 20 B per entry.
 static krd_status set_masses_host(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
-                                  const double* pos, const double* mass, const uint32_t* cell32, bool binned)
+                                  const double* pos, const double* mass, const void* cell32, int cell_bytes)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
+    const bool binned = cell_bytes != 0;
     krd_status st = set_masses_common(h, n_samples, sample_off);
     if (st != KRD_OK) return st;
     const int64_t M = sample_off[n_samples];
     if (M > 0 && (!mass || (binned ? !cell32 : (!edge || !pos)))) return fail(h, KRD_ERR_INVALID_ARGUMENT, "null mass arrays");
-    if (binned && (h->cfg.bins < 1 || (int64_t)h->E * h->cfg.bins > 0xFFFFFFF0ll))
-        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned needs krd_config.bins >= 1 and n_edges * bins < 2^32");
+    if ((st = check_cell_range(h, cell_bytes)) != KRD_OK) return st;
     KRD_CUDA(h, cudaSetDevice(h->device));
     pipe_quiesce(h);
     free_masses(h);
-    if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass, cell32, binned);
+    if (pipe_wanted(h, n_samples)) return pipe_set_masses(h, n_samples, sample_off, edge, pos, mass, cell32, cell_bytes);
     if (h->piped || h->custom_tiles) { h->piped = false; h->custom_tiles = false; h->n_tiles_alloc = -1; }
     h->N = n_samples; h->M = M;
     const size_t Mx = (size_t)std::max<int64_t>(M, 1);
@@ -183,8 +197,8 @@ static krd_status set_masses_host(krd_handle* h, int32_t n_samples, const int64_
     h->d_mass = (double*)h->d_owned[2];
     KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     if (binned) {
-        h->binned_input = true; h->d_cell32 = (const uint32_t*)h->d_owned[0];
-        KRD_CUDA(h, cudaMemcpyAsync(h->d_owned[0], cell32, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
+        h->binned_input = true; h->d_cell32 = h->d_owned[0]; h->cell_bytes = cell_bytes;
+        KRD_CUDA(h, cudaMemcpyAsync(h->d_owned[0], cell32, (size_t)M * cell_bytes, cudaMemcpyHostToDevice, h->stream));
     } else {
         h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1];
         KRD_CUDA(h, cudaMemcpyAsync(h->d_edge, edge, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
@@ -201,26 +215,32 @@ static krd_status set_masses_host(krd_handle* h, int32_t n_samples, const int64_
 krd_status krd_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge,
                           const double* pos, const double* mass)
 {
-    return set_masses_host(h, n_samples, sample_off, edge, pos, mass, nullptr, false);
+    return set_masses_host(h, n_samples, sample_off, edge, pos, mass, nullptr, 0);
 }
 
 krd_status krd_set_masses_binned(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* cell,
                                  const double* mass)
 {
-    return set_masses_host(h, n_samples, sample_off, nullptr, nullptr, mass, cell, true);
+    return set_masses_host(h, n_samples, sample_off, nullptr, nullptr, mass, cell, 4);
+}
+
+krd_status krd_set_masses_binned16(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint16_t* cell,
+                                   const double* mass)
+{
+    return set_masses_host(h, n_samples, sample_off, nullptr, nullptr, mass, cell, 2);
 }
 
 }  // extern "C"
 
 namespace krd {
 krd_status set_masses_device_impl(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
-                                  const double* d_pos, const double* d_mass, const uint32_t* d_cell32, bool binned)
+                                  const double* d_pos, const double* d_mass, const void* d_cell32, int cell_bytes)
 {
     if (!h) return KRD_ERR_INVALID_ARGUMENT;
     krd_status st = set_masses_common(h, n_samples, sample_off);
     if (st != KRD_OK) return st;
-    if (binned && (h->cfg.bins < 1 || (int64_t)h->E * h->cfg.bins > 0xFFFFFFF0ll))
-        return fail(h, KRD_ERR_INVALID_ARGUMENT, "krd_set_masses_binned needs krd_config.bins >= 1 and n_edges * bins < 2^32");
+    const bool binned = cell_bytes != 0;
+    if ((st = check_cell_range(h, cell_bytes)) != KRD_OK) return st;
     KRD_CUDA(h, cudaSetDevice(h->device));
     pipe_quiesce(h);
     free_masses(h);
@@ -230,7 +250,7 @@ krd_status set_masses_device_impl(krd_handle* h, int32_t n_samples, const int64_
     if (h->d_off_from) launch_rebase_off(h->d_off_from, n_samples + 1, h->d_off, h->stream);
     else KRD_CUDA(h, cudaMemcpyAsync(h->d_off, sample_off, (size_t)(n_samples + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     h->d_edge = const_cast<int32_t*>(d_edge); h->d_pos = const_cast<double*>(d_pos); h->d_mass = const_cast<double*>(d_mass);
-    h->binned_input = binned; h->d_cell32 = d_cell32;
+    h->binned_input = binned; h->d_cell32 = d_cell32; h->cell_bytes = binned ? cell_bytes : 4;
     st = prepare_masses(h);
     if (st != KRD_OK) return st;
     h->have_masses = true;
@@ -244,13 +264,19 @@ extern "C" {
 krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge,
                                  const double* d_pos, const double* d_mass)
 {
-    return set_masses_device_impl(h, n_samples, sample_off, d_edge, d_pos, d_mass, nullptr, false);
+    return set_masses_device_impl(h, n_samples, sample_off, d_edge, d_pos, d_mass, nullptr, 0);
 }
 
 krd_status krd_set_masses_binned_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* d_cell,
                                         const double* d_mass)
 {
-    return set_masses_device_impl(h, n_samples, sample_off, nullptr, nullptr, d_mass, d_cell, true);
+    return set_masses_device_impl(h, n_samples, sample_off, nullptr, nullptr, d_mass, d_cell, 4);
+}
+
+krd_status krd_set_masses_binned16_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint16_t* d_cell,
+                                          const double* d_mass)
+{
+    return set_masses_device_impl(h, n_samples, sample_off, nullptr, nullptr, d_mass, d_cell, 2);
 }
 
 static krd_status check_compute(krd_handle* h, double p, double divisor)

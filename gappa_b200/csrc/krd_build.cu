@@ -205,7 +205,8 @@ __global__ void k_slots_binned(const int32_t* __restrict__ edge, const double* _
 // Compact binned input (krd_set_masses_binned): cell = edge * B + bin.  One pass decodes edge / slot / sample id and checks
 // the range and the order (ascending cell within a sample = MassTree order of the binified tree); flags as in
 // k_check_canonical.  `clamp`: deferred check of a pipelined child — a bad edge is recorded and replaced by edge 0.
-__global__ void k_decode_binned(const int64_t* __restrict__ off, int n, const uint32_t* __restrict__ cell, int64_t M, uint32_t B, int E,
+template <typename CT>
+__global__ void k_decode_binned(const int64_t* __restrict__ off, int n, const CT* __restrict__ cell, int64_t M, uint32_t B, int E,
                                 int clamp, uint32_t* __restrict__ sid, int32_t* __restrict__ edge, int32_t* __restrict__ slot,
                                 int* __restrict__ flags)
 {
@@ -216,7 +217,7 @@ __global__ void k_decode_binned(const int64_t* __restrict__ off, int n, const ui
     uint32_t e = c / B;
     const uint32_t q = c - e * B;
     if (e >= (uint32_t)E) { atomicOr(flags, 2); if (!clamp) return; e = 0; }
-    if (m > off[i] && cell[m - 1] > c) atomicOr(flags, 1);
+    if (m > off[i] && (uint32_t)cell[m - 1] > c) atomicOr(flags, 1);
     sid[m] = (uint32_t)i; edge[m] = (int32_t)e; slot[m] = (int32_t)q;
 }
 
@@ -402,8 +403,12 @@ krd_status prepare_masses(krd_handle* h)
         if ((rs = reserve(h, (void**)&h->d_slot, (size_t)std::max<int64_t>(M, 1) * 4)) != KRD_OK) return rs;
         if ((rs = reserve(h, (void**)&h->d_edge_dec, (size_t)std::max<int64_t>(M, 1) * 4)) != KRD_OK) return rs;
         h->d_edge = h->d_edge_dec;
-        if (M > 0) k_decode_binned<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, h->d_cell32, M, (uint32_t)h->cfg.bins, E, h->defer_check ? 1 : 0,
-                                                                   h->d_sid, h->d_edge, h->d_slot, d_flags);
+        if (M > 0 && h->cell_bytes == 2)
+            k_decode_binned<uint16_t><<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, static_cast<const uint16_t*>(h->d_cell32), M, (uint32_t)h->cfg.bins, E,
+                                                                      h->defer_check ? 1 : 0, h->d_sid, h->d_edge, h->d_slot, d_flags);
+        else if (M > 0)
+            k_decode_binned<uint32_t><<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, static_cast<const uint32_t*>(h->d_cell32), M, (uint32_t)h->cfg.bins, E,
+                                                                      h->defer_check ? 1 : 0, h->d_sid, h->d_edge, h->d_slot, d_flags);
     } else if (M > 0) {
         k_sample_ids<<<nblk(M), 256, 0, h->stream>>>(h->d_off, N, M, h->d_sid);
         if (h->defer_check) k_clamp_edges<<<nblk(M), 256, 0, h->stream>>>(h->d_edge, M, E, d_flags);

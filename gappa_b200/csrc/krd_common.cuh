@@ -71,7 +71,8 @@ struct krd_handle {
     // compact binned input (krd_set_masses_binned): entries arrive as (cell = edge * bins + bin, mass); d_edge / d_slot are
     // decoded from it by K0 and d_pos stays null (the bin centre is implied)
     bool     binned_input = false;
-    const uint32_t* d_cell32 = nullptr;   // M
+    const void* d_cell32 = nullptr;       // M cells of cell_bytes each (uint32_t, or uint16_t from krd_set_masses_binned16)
+    int      cell_bytes = 4;
     int32_t* d_edge_dec = nullptr;        // M: decoded edge ids (owned, grow-only)
 
     // ---- segments + dense matrix ----
@@ -216,10 +217,10 @@ krd_status rank_tile_range(krd_handle* h, int rank, int world, const Tile** d_ti
 // krd_pipe.cu — pipelined ingest (krd_config.pipeline)
 bool pipe_wanted(const krd_handle* h, int32_t n_samples);
 krd_status pipe_set_masses(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* edge, const double* pos, const double* mass,
-                           const uint32_t* cell32, bool binned);   // binned: compact input (cell32, mass); edge / pos unused
+                           const void* cell32, int cell_bytes);   // cell_bytes 4 / 2: compact input (cells, mass), edge / pos unused; 0: (edge, pos, mass)
 // krd_api.cu: masses already on the device; `binned` selects the compact form (d_cell32, d_mass)
 krd_status set_masses_device_impl(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const int32_t* d_edge, const double* d_pos,
-                                  const double* d_mass, const uint32_t* d_cell32, bool binned);
+                                  const double* d_mass, const void* d_cell32, int cell_bytes);
 krd_status pipe_compute(krd_handle* h, double p, double divisor, double* d_out);   // all phases, or everything at once when the children are resident
 krd_status pipe_flatten(krd_handle* h);     // finish the uploads and turn the handle into an ordinary one (squash, k-means, sharding, introspection)
 void pipe_destroy(krd_handle* h);

@@ -65,8 +65,9 @@ static krd_status kid_error(krd_handle* h, krd_handle* kid, krd_status st)
 static krd_status kid_prepare(krd_handle* h, int q, bool wait = true);
 
 krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const int32_t* edge, const double* pos, const double* mass,
-                           const uint32_t* cell32, bool binned)
+                           const void* cell32, int cell_bytes)
 {
+    const bool binned = cell_bytes != 0;
     const int64_t M = off[N];
     const int T = (N + TILE - 1) / TILE;
     int K = std::min(T, PIPE_KIDS);
@@ -124,8 +125,8 @@ krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const i
     if ((st = reserve(h, &h->d_owned[2], Mx * 8)) != KRD_OK) return st;
     h->d_mass = (double*)h->d_owned[2];
     h->binned_input = binned;
-    if (binned) { h->d_cell32 = (const uint32_t*)h->d_owned[0]; h->d_edge = nullptr; h->d_pos = nullptr; }
-    else { h->d_cell32 = nullptr; h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; }
+    if (binned) { h->d_cell32 = h->d_owned[0]; h->cell_bytes = cell_bytes; h->d_edge = nullptr; h->d_pos = nullptr; }
+    else { h->d_cell32 = nullptr; h->cell_bytes = 4; h->d_edge = (int32_t*)h->d_owned[0]; h->d_pos = (double*)h->d_owned[1]; }
 
     // ---- uploads, child by child, on the copy stream (after whatever the compute stream still does with the buffers) ----
     KRD_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
@@ -142,7 +143,7 @@ krd_status pipe_set_masses(krd_handle* h, int32_t N, const int64_t* off, const i
         ko.resize((size_t)(s1 - s0) + 1);
         for (int i = s0; i <= s1; ++i) ko[(size_t)(i - s0)] = off[i] - m0;
         if (m1 > m0) {
-            if (binned) KRD_CUDA(h, cudaMemcpyAsync((uint32_t*)h->d_owned[0] + m0, cell32 + m0, (size_t)(m1 - m0) * 4, cudaMemcpyHostToDevice, h->copy_stream));
+            if (binned) KRD_CUDA(h, cudaMemcpyAsync((char*)h->d_owned[0] + m0 * cell_bytes, (const char*)cell32 + m0 * cell_bytes, (size_t)(m1 - m0) * cell_bytes, cudaMemcpyHostToDevice, h->copy_stream));
             else {
                 KRD_CUDA(h, cudaMemcpyAsync(h->d_edge + m0, edge + m0, (size_t)(m1 - m0) * 4, cudaMemcpyHostToDevice, h->copy_stream));
                 KRD_CUDA(h, cudaMemcpyAsync(h->d_pos + m0, pos + m0, (size_t)(m1 - m0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
@@ -200,8 +201,8 @@ static krd_status kid_prepare(krd_handle* h, int q, bool wait)
     for (int k = 0; k < q; ++k) base += h->kid_off[(size_t)k].back();
     if (g_dbg) std::fprintf(stderr, "[pipe] child %d: samples %d..%d, entries %lld..%lld of %lld\n", q, s0, s0 + (int)ko.size() - 1, (long long)base, (long long)(base + ko.back()), (long long)h->M);
     krd_status st = h->binned_input
-        ? set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), nullptr, nullptr, h->d_mass + base, h->d_cell32 + base, true)
-        : set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), h->d_edge + base, h->d_pos + base, h->d_mass + base, nullptr, false);
+        ? set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), nullptr, nullptr, h->d_mass + base, (const char*)h->d_cell32 + base * h->cell_bytes, h->cell_bytes)
+        : set_masses_device_impl(kid, (int32_t)ko.size() - 1, ko.data(), h->d_edge + base, h->d_pos + base, h->d_mass + base, nullptr, 0);
     if (st != KRD_OK) return kid_error(h, kid, st);
     if (!kid->tiled) return fail(h, KRD_ERR_STATE, "pipelined ingest: child without a tiled builder");
     return KRD_OK;

@@ -28,7 +28,7 @@ EXPORTS = [
     "krd_create", "krd_destroy", "krd_last_error", "krd_set_stream", "krd_set_tree",
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
-    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_scatter_tile_range_rows", "krd_set_late_blocks", "krd_copy_rect_to_host_async", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
+    "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_set_masses_binned16", "krd_set_masses_binned16_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_scatter_tile_range_rows", "krd_set_late_blocks", "krd_copy_rect_to_host_async", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
     "krd_p2p_free", "krd_p2p_enable_peer", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
@@ -104,6 +104,10 @@ def lib():
     L.krd_set_masses_binned.argtypes = [vp, i32, vp, vp, vp]
     L.krd_set_masses_binned_device.restype = C.c_int
     L.krd_set_masses_binned_device.argtypes = [vp, i32, vp, vp, vp]
+    L.krd_set_masses_binned16.restype = C.c_int
+    L.krd_set_masses_binned16.argtypes = [vp, i32, vp, vp, vp]
+    L.krd_set_masses_binned16_device.restype = C.c_int
+    L.krd_set_masses_binned16_device.argtypes = [vp, i32, vp, vp, vp]
     L.krd_unpack_shards_rows.restype = C.c_int
     L.krd_unpack_shards_rows.argtypes = [vp, i32, vp, i32, i32, vp]
     L.krd_compute_allgather.restype = C.c_int
@@ -193,6 +197,11 @@ def _ptr(a):
     return a.data_ptr()  # torch tensor
 
 
+def _itemsize(a):
+    """Bytes per element of a numpy array / torch tensor."""
+    return a.dtype.itemsize if isinstance(a, np.ndarray) else a.element_size()
+
+
 class KrdPlan:
     """One handle of the C ABI: tree + masses resident in HBM, distance matrices on demand."""
 
@@ -254,22 +263,27 @@ class KrdPlan:
         self.n_samples = n
 
     def set_masses_binned(self, off, cell, mass):
-        """Compact binned form (krd_set_masses_binned): cell = edge * bins + bin (uint32), sorted within a sample. HOST arrays."""
+        """Compact binned form: cell = edge * bins + bin, sorted within a sample; HOST arrays.  16-bit cells (numpy uint16 or a
+        2-byte torch tensor) go through krd_set_masses_binned16 (10 B per entry), anything else through krd_set_masses_binned
+        (uint32, 12 B per entry)."""
         if isinstance(off, (np.ndarray, list, tuple)):
             off = np.ascontiguousarray(off, np.int64)
         if isinstance(cell, np.ndarray):
-            cell = np.ascontiguousarray(cell, np.uint32)
+            cell = np.ascontiguousarray(cell, np.uint16 if cell.dtype == np.uint16 else np.uint32)
             mass = np.ascontiguousarray(mass, np.float64)
         n = len(off) - 1
         self._keep_host = [off, cell, mass]
-        self._check(self._L.krd_set_masses_binned(self._h, n, _ptr(off), _ptr(cell), _ptr(mass)))
+        fn = self._L.krd_set_masses_binned16 if _itemsize(cell) == 2 else self._L.krd_set_masses_binned
+        self._check(fn(self._h, n, _ptr(off), _ptr(cell), _ptr(mass)))
         self.n_samples = n
 
     def set_masses_binned_device(self, off, d_cell, d_mass):
+        """DEVICE arrays; a 2-byte cell tensor selects krd_set_masses_binned16_device."""
         off = np.ascontiguousarray(off, np.int64)
         n = len(off) - 1
         self._keep = [d_cell, d_mass]
-        self._check(self._L.krd_set_masses_binned_device(self._h, n, _ptr(off), _ptr(d_cell), _ptr(d_mass)))
+        fn = self._L.krd_set_masses_binned16_device if _itemsize(d_cell) == 2 else self._L.krd_set_masses_binned_device
+        self._check(fn(self._h, n, _ptr(off), _ptr(d_cell), _ptr(d_mass)))
         self.n_samples = n
 
     def unpack_shards_rows(self, d_gathered, d_out_rows, world, row0, row1):

@@ -129,6 +129,14 @@ krd_status krd_set_masses_binned(krd_handle* h, int32_t n_samples, const int64_t
 /* Same with DEVICE arrays (no copy is made: they must stay valid until the next krd_set_masses*). sample_off is host. */
 krd_status krd_set_masses_binned_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* d_cell,
                                         const double* d_mass);
+/* The compact form with 16-bit cells, for trees with n_edges * B <= 65536 (every BASELINE config: 9,999 x 4, 49,999 x 1,
+ * 19,999 x 1): 10 bytes per entry across PCIe — half of what the MassTree form (edge, pos, mass) ships.  Same rules, same
+ * results (the cells are widened on the device by the pass that decodes them).  Replaces nothing in the reference: it is the
+ * transport form of the MassTrees that earth_movers_distance (emd.hpp:124) receives after mass_tree_binify_masses. */
+krd_status krd_set_masses_binned16(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint16_t* cell,
+                                   const double* mass);
+krd_status krd_set_masses_binned16_device(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint16_t* d_cell,
+                                          const double* d_mass);
 
 /* earth_movers_distance(trees, p) [/ divisor].  Builds F (level-synchronous subtree scan), runs
  * the all-pairs kernel, writes the n x n matrix.  `out` is a HOST pointer; returns after the

@@ -50,6 +50,53 @@ def test_compact_form_equals_full_form(n, E, P, bins, pipeline):
     full.close(); comp.close()
 
 
+@pytest.mark.parametrize("n,E,P,bins,pipeline", [(150, 61, 80, 3, 0), (700, 301, 200, 4, 1), (1300, 97, 60, 1, 1)])
+def test_16_bit_cells_equal_32_bit_cells(n, E, P, bins, pipeline):
+    """krd_set_masses_binned16 (10 B per entry) is the same input in a narrower transport form: identical bits out, host and
+    device variants, ordinary and pipelined handles; a tree with more than 65,536 cells is refused with a sized message."""
+    import torch
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(E, seed=n)
+    raw, b = _binified(tree, n, P, bins, seed=n)
+    cell = gappa_b200.krd.binned_cells(tree, b, bins)
+    assert cell.max() < 65536
+    res = {}
+    for name, c in (("u32", cell), ("u16", cell.astype(np.uint16))):
+        plan = gappa_b200.KrdPlan(bins=bins, pipeline=pipeline)
+        plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+        plan.set_masses_binned(b["off"], c, b["mass"])
+        res[name] = [plan.compute(p=p) for p in (1.0, 0.5, 2.0)] + [plan.debug_F()[0]]
+        plan.close()
+    for a, c in zip(res["u32"], res["u16"]):
+        assert np.array_equal(a, c)
+    # device arrays (2-byte tensor -> krd_set_masses_binned16_device)
+    d_cell = torch.from_numpy(cell.astype(np.uint16).view(np.int16)).cuda()
+    d_mass = torch.from_numpy(b["mass"]).cuda()
+    plan = gappa_b200.KrdPlan(bins=bins)
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    plan.set_masses_binned_device(b["off"], d_cell, d_mass)
+    got = plan.compute(p=1.0)
+    if pipeline:       # (this handle is not pipelined: default tile order, different partial-sum splits than res[...])
+        assert rel_err(got, res["u32"][0]) <= 1e-12
+    else:
+        assert np.array_equal(got, res["u32"][0])
+    plan.close()
+
+
+def test_16_bit_cells_are_refused_for_large_trees():
+    import gappa_b200
+    from gappa_b200 import synth
+    tree = synth.tree_with_edges(20001, seed=1)
+    plan = gappa_b200.KrdPlan(bins=4)                       # 80,004 cells > 65,536
+    plan.set_tree(tree["parent"], tree["child"], tree["bl"], tree["root"])
+    with pytest.raises(gappa_b200.KrdError, match="krd_set_masses_binned16 needs n_edges \\* bins <= 65536"):
+        plan.set_masses_binned(np.array([0, 1], np.int64), np.array([5], np.uint16), np.array([1.0]))
+    plan.set_masses_binned(np.array([0, 1, 2], np.int64), np.array([5, 70000], np.uint32), np.array([1.0, 1.0]))   # 32-bit cells still work
+    assert plan.compute(p=1.0).shape == (2, 2)
+    plan.close()
+
+
 def test_compact_form_duplicates_are_summed_and_errors_are_reported():
     import gappa_b200
     from gappa_b200 import synth

@@ -183,6 +183,50 @@ void check_krd(krd_handle* h, krd_status st)
     throw std::runtime_error(m);
 }
 
+// Masses -> device.  With --bins B the entries are binned HERE (the reference's expression, mass_tree/functions.cpp:231-237,
+// evaluated exactly as the library's device pass evaluates it) and cross PCIe in the compact form of krd_set_masses_binned*:
+// cell = edge * B + bin as uint16 (trees with n_edges * B <= 65536) or uint32, plus the mass — 10 / 12 bytes per entry
+// instead of 20.  Equal cells of a sample stay separate entries; the library sums them in input order, as it does for the
+// full form, so both routes give the same bits.
+template <typename CT>
+void binned_cells(const MassSet& ms, int bins, int threads, std::vector<CT>& cell)
+{
+    const size_t M = ms.edge.size();
+    cell.resize(M);
+    const double nb = (double)bins, below = std::nextafter(nb, 0.0);
+    auto work = [&](size_t m0, size_t m1) {
+        for (size_t m = m0; m < m1; ++m) {
+            const double v = ms.pos[m] / ms.tree.bl[(size_t)ms.edge[m]] * nb;
+            double pn = (0.0 < v) ? v : 0.0;          // (NaN -> 0, like std::max(0.0, v))
+            pn = (below < pn) ? below : pn;
+            cell[m] = (CT)((uint32_t)ms.edge[m] * (uint32_t)bins + (uint32_t)std::floor(pn));
+        }
+    };
+    const int T = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(threads, 1), M / 65536 + 1));
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; ++t) pool.emplace_back(work, M * (size_t)t / (size_t)T, M * (size_t)(t + 1) / (size_t)T);
+    work(0, M / (size_t)T);
+    for (auto& w : pool) w.join();
+}
+
+krd_status set_masses(krd_handle* h, const MassSet& ms, int bins, int threads)
+{
+    const int32_t n = ms.n_samples();
+    const int64_t cells = (int64_t)ms.tree.n_edges * bins;
+    if (bins < 1 || cells > 0xFFFFFFF0ll)
+        return krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data());
+    for (int32_t e : ms.edge)                          // (the ingest has checked edge numbers; a foreign MassSet may not have)
+        if (e < 0 || e >= ms.tree.n_edges) return krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data());
+    if (cells <= 65536) {
+        std::vector<uint16_t> cell;
+        binned_cells(ms, bins, threads, cell);
+        return krd_set_masses_binned16(h, n, ms.off.data(), cell.data(), ms.mass.data());
+    }
+    std::vector<uint32_t> cell;
+    binned_cells(ms, bins, threads, cell);
+    return krd_set_masses_binned(h, n, ms.off.data(), cell.data(), ms.mass.data());
+}
+
 int run_krd(const KrdOptions& o, Log& log)
 {
     using clk = std::chrono::steady_clock;
@@ -219,7 +263,7 @@ int run_krd(const KrdOptions& o, Log& log)
         if (krd_create(&cfg, &h) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
         try {
             check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
-            check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+            check_krd(h, set_masses(h, ms, o.bins, o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency()));
             check_krd(h, krd_compute(h, o.exponent, divisor, matrix.data()));
             krd_get_stats(h, &st);
         } catch (...) { krd_destroy(h); throw; }
@@ -244,7 +288,7 @@ int run_krd(const KrdOptions& o, Log& log)
                 if (krd_create(&cfg, &hs[(size_t)g]) != KRD_OK) throw std::runtime_error(krd_last_error(nullptr));
                 krd_handle* h = hs[(size_t)g];
                 check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
-                check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+                check_krd(h, set_masses(h, ms, o.bins, o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency()));
             } catch (std::exception const& ex) { errors[(size_t)g] = ex.what(); }
         });
         for (auto& w : workers) w.join();
@@ -359,7 +403,7 @@ int run_squash(const KrdOptions& o, Log& log)
     std::vector<krd_merger> mergers((size_t)std::max(n - 1, 0));
     try {
         check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
-        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+        check_krd(h, set_masses(h, ms, o.bins, o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency()));
         check_krd(h, krd_squash(h, o.exponent, mergers.data()));
     } catch (...) { krd_destroy(h); throw; }
     krd_destroy(h);
@@ -447,7 +491,7 @@ int run_kmeans(const KrdOptions& o, Log& log)
     mkdirs(dir);
     try {
         check_krd(h, krd_set_tree(h, ms.tree.n_edges, ms.tree.parent.data(), ms.tree.child.data(), ms.tree.bl.data(), ms.tree.root));
-        check_krd(h, krd_set_masses(h, n, ms.off.data(), ms.edge.data(), ms.pos.data(), ms.mass.data()));
+        check_krd(h, set_masses(h, ms, o.bins, o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency()));
         std::vector<double> D;   // pairwise KR matrix: the data-to-data-point distances k-means++ draws from
         std::vector<int32_t> assign((size_t)n), prev_assign;
         std::vector<double> dist((size_t)n);

@@ -121,8 +121,8 @@ krd_status krd_set_masses_device(krd_handle* h, int32_t n_samples, const int64_t
 /* The same N mass trees in COMPACT BINNED form (krd_config.bins = B >= 1 only): what mass_tree_binify_masses
  * (tree/mass_tree/functions.cpp:222-265) leaves is one mass per occupied (edge, bin), sitting at the bin centre, so an
  * entry is fully described by  cell = edge * B + bin  (bin = floor(min(max(0, pos / bl * B), nextafter(B, 0))),
- * functions.cpp:231-237) and its mass: 12 bytes instead of 20 across PCIe.  libkrd_host's ingest emits this form when
- * it bins (include/krd_host.h).  Within a sample the entries must be sorted by cell (= MassTree order); equal cells are
+ * functions.cpp:231-237) and its mass: 12 bytes instead of 20 across PCIe.  The command `gappa-b200 analyze krd | phylogenetic-kmeans
+ * --bins B` bins on the host and ships this form (host/krd_command.cpp, set_masses).  Within a sample the entries must be sorted by cell (= MassTree order); equal cells are
  * summed.  n_edges * B must be < 2^32.  HOST pointers; honours krd_config.pipeline like krd_set_masses. */
 krd_status krd_set_masses_binned(krd_handle* h, int32_t n_samples, const int64_t* sample_off, const uint32_t* cell,
                                  const double* mass);

@@ -294,6 +294,21 @@ def test_cli_phylogenetic_kmeans_end_to_end(tmp_path):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("bins", [1, 4, 37])
+def test_cli_bins_ships_compact_form_and_matches_full_form(tmp_path, bins):
+    """`analyze krd --bins B`: the command bins on the host and uploads (cell, mass) — krd_set_masses_binned16 here; the
+    matrix must equal, bit for bit, what the library computes from the full (edge, pos, mass) form with bins = B."""
+    import gappa_b200
+    r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path / "o"), "--bins", str(bins),
+                        "--write-binary", str(tmp_path / "m.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    tree, masses, _ = host.load_jplace([JP])
+    want = gappa_b200.earth_movers_distance(tree, masses, p=1.0, bins=bins)
+    got = np.fromfile(tmp_path / "m.bin").reshape(want.shape)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
 def test_cli_exponent_error_message(tmp_path):
     r = subprocess.run([host.CLI_PATH, "analyze", "krd", "--jplace-path", JP, "--out-dir", str(tmp_path), "--exponent", "-1"],
                        capture_output=True, text=True)

@@ -21,8 +21,19 @@ namespace krd {
 //  Tree preprocessing (host): validate, levels, child-edge lists
 // ------------------------------------------------------------------------------------------------
 
-constexpr int TOP_MAX = 256;    // edges finished by k_subtree_top (2 x 256 x 32 doubles = 128 KB of shared memory)
-constexpr int TOP_COLS = 32;    // samples per CTA of k_subtree_top
+// Top-of-tree kernel shape, measured at cfg2 (K1 per build, `bench.py`): 32 columns x 256 threads (round 1) 0.404 ms;
+// 32 x 1,024 threads 0.372; 16 x 1,024 (512 edges) 0.358; 8 x 1,024 (1,024 edges: two more levels leave the per-level
+// launches) 0.354.  The kernel's time is (edges per thread group) x (latency of three dependent loads), not bandwidth.
+#ifndef KRD_TOP_COLS
+#define KRD_TOP_COLS 8
+#endif
+constexpr int TOP_COLS = KRD_TOP_COLS;       // samples per CTA of k_subtree_top
+constexpr int TOP_MAX = 256 * 32 / TOP_COLS; // edges finished by k_subtree_top (2 x TOP_MAX x TOP_COLS doubles = 128 KB of shared memory)
+#ifndef KRD_TOP_THREADS
+#define KRD_TOP_THREADS 1024
+#endif
+constexpr int TOP_THREADS = KRD_TOP_THREADS;   // the kernel is a chain of dependent loads per (edge, column): its time is (edges per thread group) x latency —
+                                              // 1,024 threads = 32 groups of 32 columns: 8 edges per group instead of 32 (46 -> ~15 us at cfg2)
 
 krd_status build_tree(krd_handle* h)
 {
@@ -738,7 +749,7 @@ k_subtree_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_co
 // The last `n_lvl` levels of the tree (Kt <= TOP_MAX edges) in one launch: a CTA owns 32 sample
 // columns and keeps M and D of those edges in shared memory, so the level-by-level dependency costs a
 // CTA barrier instead of a kernel launch plus a chain of DRAM round trips.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(TOP_THREADS)
 k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_t ld, double* __restrict__ Msub,
               double* __restrict__ Dsub)
 {
@@ -747,7 +758,7 @@ k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_
     double* Dsm = sm + (size_t)Kt * TOP_COLS;      // [Kt][TOP_COLS]
     int32_t* meta = reinterpret_cast<int32_t*>(Dsm + (size_t)Kt * TOP_COLS);
     const int n_meta = Kt + (Kt + 1) + nk + (n_lvl + 1);
-    for (int k = threadIdx.x; k < n_meta; k += 256) meta[k] = top[k];
+    for (int k = threadIdx.x; k < n_meta; k += TOP_THREADS) meta[k] = top[k];
     __syncthreads();
     const int32_t* edge_id = meta;
     const int32_t* koff = meta + Kt;
@@ -756,7 +767,7 @@ k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_
     const int col = threadIdx.x & (TOP_COLS - 1), grp = threadIdx.x / TOP_COLS;
     const int64_t gcol = (int64_t)blockIdx.x * TOP_COLS + col;
 
-    for (int j = grp; j < Kt; j += 256 / TOP_COLS) {      // everything that comes from below the top: independent loads
+    for (int j = grp; j < Kt; j += TOP_THREADS / TOP_COLS) {      // everything that comes from below the top: independent loads
         double d = 0.0;
         for (int k = koff[j]; k < koff[j + 1]; ++k) if (kid[k] >= 0) d += Msub[(int64_t)kid[k] * ld + gcol];
         Dsm[j * TOP_COLS + col] = d;
@@ -764,7 +775,7 @@ k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_
     }
     __syncthreads();
     for (int l = 0; l < n_lvl; ++l) {
-        for (int j = loff[l] + grp; j < loff[l + 1]; j += 256 / TOP_COLS) {
+        for (int j = loff[l] + grp; j < loff[l + 1]; j += TOP_THREADS / TOP_COLS) {
             double d = Dsm[j * TOP_COLS + col];
             for (int k = koff[j]; k < koff[j + 1]; ++k) if (kid[k] < 0) d += Msm[(~kid[k]) * TOP_COLS + col];
             Dsm[j * TOP_COLS + col] = d;
@@ -772,7 +783,7 @@ k_subtree_top(const int32_t* __restrict__ top, int Kt, int nk, int n_lvl, int64_
         }
         __syncthreads();
     }
-    for (int j = grp; j < Kt; j += 256 / TOP_COLS) {
+    for (int j = grp; j < Kt; j += TOP_THREADS / TOP_COLS) {
         Msub[(int64_t)edge_id[j] * ld + gcol] = Msm[j * TOP_COLS + col];
         Dsub[(int64_t)edge_id[j] * ld + gcol] = Dsm[j * TOP_COLS + col];
     }
@@ -833,7 +844,7 @@ static krd_status subtree_passes(krd_handle* h, int64_t ldm, int* n_launch, doub
     if (use_top) {
         static std::atomic<unsigned long long> top_configured{0};
         KRD_CUDA(h, allow_dynamic_smem(k_subtree_top, 200 * 1024, top_configured));
-        k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), 256, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
+        k_subtree_top<<<(unsigned)(h->ncols / TOP_COLS), TOP_THREADS, smem_top, h->stream>>>(h->d_top, h->top_edges, h->top_kids, h->top_levels,
                                                                                  ldm, Msub, Dsub);
         ++*n_launch;
     }

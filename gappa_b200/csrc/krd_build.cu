@@ -602,7 +602,13 @@ k_scan_level(const int32_t* __restrict__ lvl_edges, int lvl_begin, int lvl_count
 //                    below the edge (emd.cpp:141-166), tile rows streamed to F.
 // Algorithmic bytes: 8*S*ld (F, written once) + 2 * 12*M (CSR read twice) + ~5 * 8*E*ld (T/M).
 constexpr int FT = 64;           // samples per tile
-constexpr int FT_MAX_ROWS = 96;  // tile rows (segments) -> 48 KB of shared memory, 4 CTAs per SM
+#ifndef KRD_FT_ROWS_BINNED
+#define KRD_FT_ROWS_BINNED 48
+#endif
+#ifndef KRD_FT_MAX_ROWS
+#define KRD_FT_MAX_ROWS 96
+#endif
+constexpr int FT_MAX_ROWS = KRD_FT_MAX_ROWS;  // tile rows (segments) -> 48 KB of shared memory, 4 CTAs per SM
 
 // blk_ptr[b][i] = first entry of sample i whose edge is >= b*EB (b = n_eblocks: end of the sample)
 __global__ void k_block_ptr(const int64_t* __restrict__ off, const int32_t* __restrict__ edge, int N, int n_eblocks, int EB,
@@ -795,7 +801,11 @@ static krd_status prepare_tiled(krd_handle* h)
     h->tiled = false;
     const int B1 = h->cfg.bins + 1;
     if (h->cfg.bins <= 0 || B1 > 32 || h->E == 0 || h->N == 0) return KRD_OK;   // 5 slot bits in the entry code
-    h->EB = std::max(1, std::min(32, FT_MAX_ROWS / B1));                        // 5 edge bits
+    // Tile height: FT_MAX_ROWS rows (32 edges) for bins = 1, whose builder is a pure stream; about half of that for bins > 1,
+    // where a CTA goes through its phases (zero, scatter, running sums, store) in sequence and more, smaller CTAs hide them
+    // better: cfg2 K1 0.352 -> 0.333 ms with 48 rows (9 edges); 24 rows: 0.376 (profiles/r3g_k1_top_kernel_shapes.txt).
+    const int rows_max = (B1 == 2) ? FT_MAX_ROWS : std::min(FT_MAX_ROWS, KRD_FT_ROWS_BINNED);
+    h->EB = std::max(1, std::min(32, rows_max / B1));                           // 5 edge bits
     h->n_eblocks = (h->E + h->EB - 1) / h->EB;
     const int64_t n_slices = (int64_t)h->n_eblocks * h->N;
     krd_status st;

@@ -11,6 +11,8 @@
 
 #include <algorithm>
 #include <cctype>
+#include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -31,11 +33,73 @@ inline MatrixFormat parse_matrix_format(std::string v)
     throw std::invalid_argument("--matrix-format: Invalid format '" + v + "'.");
 }
 
+// "%g" (6 significant digits) without printf for the values a distance matrix holds.  The six digits come from ONE
+// correctly rounded scaling of v by an exact power of ten (10^k is a double for |k| <= 22): scaled = v * 10^(5 - X) lies in
+// [1e5, 1e6) with an absolute error below 1.2e-10, so its integer part and its distance to the rounding boundary .5 decide
+// the digits with certainty unless the fraction lies within 1e-9 of .5 — those values (and anything outside
+// [1e-17, 1e22), infinities, NaN) take the printf path.  Returns the length, 0 = not handled.
+inline int format_g6_fast(char* out, double v)
+{
+    static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16,
+                                   1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    char* p = out;
+    if (std::signbit(v)) { *p++ = '-'; v = -v; }
+    if (v == 0.0) { *p++ = '0'; return (int)(p - out); }
+    if (!(v >= 1e-17 && v < 1e22)) return 0;                     // (also NaN)
+    uint64_t bits;
+    std::memcpy(&bits, &v, 8);
+    const int e2 = (int)(bits >> 52) - 1022;                     // v = f * 2^e2, f in [0.5, 1)  (v is normal here)
+    int X = ((e2 - 1) * 78913) >> 18;                            // floor((e2 - 1) * log10 2): floor(log10 v) or one less
+    auto scale = [&](int k) { return k >= 0 ? v * P10[k] : v / P10[-k]; };
+    if (X < -17) X = -17;
+    double sc = scale(5 - X);
+    if (sc >= 1e6) { ++X; sc = scale(5 - X); }
+    else if (sc < 1e5) { --X; if (X < -17) return 0; sc = scale(5 - X); }
+    if (!(sc >= 1e5 && sc < 1e6)) return 0;
+    uint32_t n = (uint32_t)sc;                                    // (sc > 0: truncation = floor)
+    const double frac = sc - (double)n;
+    if (frac > 0.5 - 1e-9 && frac < 0.5 + 1e-9) return 0;         // too close to a tie to decide here
+    n += frac > 0.5 ? 1u : 0u;
+    if (n >= 1000000u) { n = 100000u; ++X; }
+    char d[6];
+    { const uint32_t hi = n / 1000u, lo = n - hi * 1000u;         // two three-digit halves
+      d[0] = (char)('0' + hi / 100u); d[1] = (char)('0' + hi / 10u % 10u); d[2] = (char)('0' + hi % 10u);
+      d[3] = (char)('0' + lo / 100u); d[4] = (char)('0' + lo / 10u % 10u); d[5] = (char)('0' + lo % 10u); }
+    int nd = 6;
+    while (nd > 1 && d[nd - 1] == '0') --nd;                     // %g drops trailing zeros
+    if (X < -4 || X >= 6) {                                       // d.ddddde[+-]XX
+        *p++ = d[0];
+        if (nd > 1) { *p++ = '.'; for (int i = 1; i < nd; ++i) *p++ = d[i]; }
+        *p++ = 'e';
+        int ax = X;
+        if (ax < 0) { *p++ = '-'; ax = -ax; } else *p++ = '+';
+        if (ax >= 100) { *p++ = (char)('0' + ax / 100); ax %= 100; }
+        *p++ = (char)('0' + ax / 10); *p++ = (char)('0' + ax % 10);
+    } else if (X >= 0) {
+        for (int i = 0; i <= X; ++i) *p++ = d[i];
+        if (nd > X + 1) { *p++ = '.'; for (int i = X + 1; i < nd; ++i) *p++ = d[i]; }
+    } else {
+        *p++ = '0'; *p++ = '.';
+        for (int i = 0; i < -X - 1; ++i) *p++ = '0';
+        for (int i = 0; i < nd; ++i) *p++ = d[i];
+    }
+    return (int)(p - out);
+}
+
+constexpr size_t VALUE_MAX = 32;   // longest "%g" text of a double, with room to spare
+
+// Writes "%g" of v at p (at least VALUE_MAX bytes free) and returns the end.
+inline char* put_value(char* p, double v)
+{
+    int n = format_g6_fast(p, v);
+    if (n == 0) n = std::snprintf(p, VALUE_MAX, "%g", v);
+    return p + n;
+}
+
 inline void append_value(std::string& s, double v)
 {
-    char buf[40];
-    int n = std::snprintf(buf, sizeof buf, "%g", v);
-    s.append(buf, (size_t)n);
+    char buf[VALUE_MAX + 8];
+    s.append(buf, (size_t)(put_value(buf, v) - buf));
 }
 
 // One output row (or, for "list", the n lines of matrix row r).
@@ -52,12 +116,20 @@ inline void format_row(std::string& out, const double* m, size_t n, size_t r, Ma
         return;
     }
     if (names) { out += (*names)[r]; out += '\t'; }
+    // the values of the row are written through a pointer into a scratch row sized for the longest case (kept per thread:
+    // growing the std::string itself would zero-fill four times the bytes the row ends up with), then appended once
+    const size_t cells = (fmt == MatrixFormat::Matrix) ? n : n - r;
+    thread_local std::vector<char> scratch;
+    if (scratch.size() < cells * (VALUE_MAX + 1) + 1) scratch.resize(cells * (VALUE_MAX + 1) + 1);
+    char* const p0 = scratch.data();
+    char* p = p0;
     if (fmt == MatrixFormat::Matrix) {
-        for (size_t c = 0; c < n; ++c) { if (c) out += '\t'; append_value(out, row[c]); }
+        for (size_t c = 0; c < n; ++c) { if (c) *p++ = '\t'; p = put_value(p, row[c]); }
     } else {  // columns backwards, starting at the last one, down to col == row
-        for (size_t cb = 0; cb < n - r; ++cb) { if (cb) out += '\t'; append_value(out, row[n - cb - 1]); }
+        for (size_t cb = 0; cb < n - r; ++cb) { if (cb) *p++ = '\t'; p = put_value(p, row[n - cb - 1]); }
     }
-    out += '\n';
+    *p++ = '\n';
+    out.append(p0, (size_t)(p - p0));
 }
 
 inline std::string format_header(size_t n, MatrixFormat fmt, const std::vector<std::string>& names, const std::string& corner)

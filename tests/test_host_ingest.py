@@ -136,6 +136,28 @@ def test_matrix_writer_bytes(gold, tmp_path, fmt, labels):
     assert gzip.open(gz, "rb").read() == want
 
 
+def test_matrix_writer_value_text_equals_printf_g(tmp_path):
+    """The writer formats values without printf where it can decide the six digits with certainty and falls back to printf
+    otherwise: every cell must read exactly like "%g" (= the reference's default ostream formatting, writer.hpp:72,237) —
+    checked on random magnitudes, values on and next to six-digit rounding ties, powers of ten, zeros, infinities, NaN."""
+    rng = np.random.default_rng(11)
+    vals = [0.0, -0.0, 1.0, 10.0, 100000.0, 999999.0, 999999.5, 1e6, 1e-4, 1e-5, 9.9999949999e-5, 1e-17, 1e22, 5e-324, 1e308,
+            123456.5, 0.1, 0.5, 2.5, 1234565.0, float("inf"), float("-inf"), float("nan"), 0.30000000000000004, 4.35, 0.000123456789]
+    vals += list(rng.random(20000) * 5.0) + list(np.exp(rng.uniform(-60, 60, 20000)) * rng.choice([-1.0, 1.0], 20000))
+    for X in range(-19, 24):
+        for n in rng.integers(100000, 1000000, 40):
+            base = (int(n) + 0.5) * 10.0 ** (X - 5)
+            vals += [base, np.nextafter(base, 0.0), np.nextafter(base, np.inf), int(n) * 10.0 ** (X - 5)]
+    k = int(np.ceil(np.sqrt(len(vals))))
+    m = np.zeros(k * k)
+    m[: len(vals)] = vals
+    out = tmp_path / "v.csv"
+    host.write_matrix(str(out), m.reshape(k, k), "matrix", None, threads=3)
+    got = out.read_text().replace("\n", "\t").split("\t")
+    want = ["%g" % v for v in m]
+    assert got[: len(want)] == want
+
+
 def test_cfg1_csv_is_7847_bytes(tmp_path):
     # gappa test/scripts/analyze-krd-1.sh:7 expects krd_matrix.csv of exactly 7847 bytes
     g = np.load(os.path.join(GOLD, "cfg1.npz"))

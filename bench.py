@@ -223,7 +223,12 @@ def rooflines(gappa_b200, local, spec, st, pairs, share, ms_step, world):
     """Roofline of the dominant kernel (k_pairs: FP64 pipe) and of the F builder (K1: HBM)."""
     S = st["n_segments"]
     p = spec["p"]
-    flops = 3.0 * S * pairs * share                      # SURVEY §8d: 3 flop per (pair, segment)
+    # SURVEY §8d: 3 flop per (pair, segment) for the direct operator (subtract, multiply / abs, accumulate).  p = 2 on the
+    # Gram path contracts len * (a - c)(b - c) on the FP64 tensor cores: ONE fused multiply-add = 2 flop per (pair, segment)
+    # (operands centred and scaled once by k_gram_prescale); counting 3 would put the kernel above the DMMA peak.
+    gram = (p == 2.0 and int(st.get("gram_fixups", -1)) >= 0 and spec["bins"] > 0)
+    per = 2.0 if gram else 3.0
+    flops = per * S * pairs * share
     t_pairs = st["ms_pairs"] * 1e-3
     peak_dfma = gappa_b200.measure_fp64_peak(local, 0, 200.0)
     peak_mix = gappa_b200.measure_fp64_peak(local, 1, 200.0)
@@ -238,11 +243,15 @@ def rooflines(gappa_b200, local, spec, st, pairs, share, ms_step, world):
     off_tiles = st["n_tiles"] - T
     rag_tiles = (T - 1) if qmax < 8 else 0
     executed = 3.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * ((off_tiles - rag_tiles) + rag_tiles * qmax / 8.0 + 0.625 * T) * share
-    roof = {"bound": "fp64", "kernel": "k_pairs<p=%g>" % p, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+    if gram:      # every tile in full, both triangles of the diagonal ones
+        executed = 2.0 * ((S + 15) // 16 * 16) * 128.0 * 128.0 * st["n_tiles"] * share
+        peak = peak_dmma
+    roof = {"bound": "fp64", "kernel": ("k_pairs<p=2, Gram form on DMMA>" if gram else "k_pairs<p=%g>" % p), "flop_per_pair_segment": per,
+            "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak, "traffic": traffic_from_profile(spec, world),
             "peak_source": "measured live: max(DFMA loop %.1f, DMMA m8n8k4 loop %.1f) TFLOP/s; MEASURED_PEAKS.json has no FP64 entry"
                            % (peak_dfma, peak_dmma),
-            "mix_ceiling": peak_mix, "frac_of_mix_ceiling": achieved / peak_mix,
+            "mix_ceiling": None if gram else peak_mix, "frac_of_mix_ceiling": None if gram else achieved / peak_mix,   # (DADD+DFMA mix: direct operators only)
             "executed_tflops": executed / t_pairs / 1e12,
             "ms_kernel": st["ms_pairs"], "ms_build_F": st["ms_build"], "ms_epilogue": st["ms_epilogue"],
             "ctas": st["pair_ctas"], "split": st["split"]}

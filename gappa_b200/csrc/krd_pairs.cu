@@ -1052,6 +1052,18 @@ int64_t krd_tile_count(int32_t n_samples)
     return T * (T + 1) / 2;
 }
 
+// The two-part order of krd_set_late_blocks, host-only (what a handle with n_late_blocks late blocks uses).
+krd_status krd_tile_list_late(int32_t n_samples, int32_t n_late_blocks, int32_t* tile_i, int32_t* tile_j, int64_t* t_split)
+{
+    if (n_samples < 0 || n_late_blocks < 0 || !tile_i || !tile_j) return KRD_ERR_INVALID_ARGUMENT;
+    std::vector<krd::Tile> tiles;
+    int64_t split = 0;
+    krd::build_tile_order(n_samples, n_late_blocks, tiles, &split);
+    for (size_t t = 0; t < tiles.size(); ++t) { tile_i[t] = tiles[t].i; tile_j[t] = tiles[t].j; }
+    if (t_split) *t_split = split;
+    return KRD_OK;
+}
+
 // Off-diagonal tiles in diagonal-major order ((i,i+1) for all i, then (i,i+2), ...: every contiguous
 // range mixes tile rows and columns evenly), with the T cheaper diagonal tiles spread evenly through
 // the list — so that equal-COUNT contiguous shares (one per rank) are also equal-COST shares.

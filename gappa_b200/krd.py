@@ -29,7 +29,7 @@ EXPORTS = [
     "krd_set_masses", "krd_set_masses_device", "krd_compute", "krd_compute_device",
     "krd_shard_doubles", "krd_compute_shard", "krd_unpack_shards", "krd_get_stats",
     "krd_squash", "krd_kmeans", "krd_kmeans_ex", "krd_matrix_from_F_noalloc", "krd_set_masses_binned", "krd_set_masses_binned_device", "krd_set_masses_binned16", "krd_set_masses_binned16_device", "krd_unpack_shards_rows", "krd_compute_allgather", "krd_compute_allgather_host", "krd_scatter_shard_rows", "krd_scatter_tile_range_rows", "krd_set_late_blocks", "krd_copy_rect_to_host_async", "krd_shard_to_host_async", "krd_compute_tile_range", "krd_tile_range_to_host_async", "krd_p2p_alloc", "krd_p2p_open", "krd_p2p_close",
-    "krd_p2p_free", "krd_p2p_enable_peer", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
+    "krd_p2p_free", "krd_p2p_enable_peer", "krd_nccl_init_all", "krd_nccl_destroy", "krd_compute_shard_host", "krd_unpack_shards_host", "krd_tile_count", "krd_tile_list", "krd_tile_list_late", "krd_rank_tiles", "krd_invalidate_F", "krd_debug_copy_F", "krd_host_alloc", "krd_host_free", "krd_measure_fp64_peak",
 ]
 
 
@@ -170,6 +170,8 @@ def lib():
     L.krd_tile_count.argtypes = [i32]
     L.krd_tile_list.restype = C.c_int
     L.krd_tile_list.argtypes = [i32, vp, vp]
+    L.krd_tile_list_late.restype = C.c_int
+    L.krd_tile_list_late.argtypes = [i32, i32, vp, vp, vp]
     L.krd_rank_tiles.restype = None
     L.krd_rank_tiles.argtypes = [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)]
     L.krd_invalidate_F.restype = C.c_int
@@ -507,6 +509,17 @@ def tile_list(n_samples):
     ti = np.zeros(n, np.int32); tj = np.zeros(n, np.int32)
     lib().krd_tile_list(n_samples, _ptr(ti), _ptr(tj))
     return ti, tj
+
+
+def tile_list_late(n_samples, n_late_blocks):
+    """The two-part order of krd_set_late_blocks (host-only): (tile_i, tile_j, t_split)."""
+    n = int(lib().krd_tile_count(n_samples))
+    ti = np.zeros(max(n, 1), np.int32); tj = np.zeros(max(n, 1), np.int32)
+    split = C.c_int64()
+    st = lib().krd_tile_list_late(n_samples, n_late_blocks, _ptr(ti), _ptr(tj), C.byref(split))
+    if st != 0:
+        raise KrdError(st, "krd_tile_list_late failed")
+    return ti[:n], tj[:n], split.value
 
 
 def rank_tiles(n_tiles, rank, world):

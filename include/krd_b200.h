@@ -248,6 +248,9 @@ krd_status krd_unpack_shards_host(int32_t n_samples, int32_t world, const double
 int64_t    krd_tile_count(int32_t n_samples);
 krd_status krd_tile_list(int32_t n_samples, int32_t* tile_i, int32_t* tile_j);
 void       krd_rank_tiles(int64_t n_tiles, int32_t rank, int32_t world, int64_t* t0, int64_t* t1);
+/* The tile list a handle uses after krd_set_late_blocks(h, n_late_blocks, &t_split) (n_late_blocks is clamped to the number
+ * of sample blocks - 1; 0 gives krd_tile_list's order and t_split = the tile count). */
+krd_status krd_tile_list_late(int32_t n_samples, int32_t n_late_blocks, int32_t* tile_i, int32_t* tile_j, int64_t* t_split);
 
 /* Squash clustering on the resident dense matrix:
  *     genesis::tree::SquashClustering::run()   libs/genesis/lib/genesis/tree/mass_tree/squash_clustering.cpp:57-249

@@ -103,6 +103,38 @@ def test_rank_shares_cover_every_tile_once():
             assert all(b - a <= per for a, b in spans)
 
 
+@pytest.mark.parametrize("n,late", [(1000, 1), (10000, 5), (20000, 10), (130, 3), (129, 1), (128, 4), (5, 0)])
+def test_two_part_tile_order_host_logic(n, late):
+    """krd_set_late_blocks' order (host-only mirror krd_tile_list_late): a permutation of the default list; part A = exactly the
+    tiles inside the leading T - L sample blocks, in the default order of that smaller matrix; part B = the tiles touching a
+    late block, column block by column block.  With every rank taking its share of A and then of B (bench.py --exchange
+    p2p_rows), each tile is computed once, and after part A every cell of the leading square has an owner that wrote it."""
+    import gappa_b200.krd as k
+    T = (n + 127) // 128
+    L = max(0, min(late, T - 1))
+    ti, tj, split = k.tile_list_late(n, late)
+    di, dj = k.tile_list(n)
+    assert sorted(zip(ti.tolist(), tj.tolist())) == sorted(zip(di.tolist(), dj.tolist()))
+    Ta = T - L
+    assert split == Ta * (Ta + 1) // 2
+    ai, aj = k.tile_list(Ta * 128)
+    assert np.array_equal(ti[:split], ai) and np.array_equal(tj[:split], aj)
+    assert np.all(tj[:split] < Ta) and np.all(tj[split:] >= Ta)
+    assert np.all(np.diff(tj[split:]) >= 0)                       # column block by column block
+    for world in (1, 2, 8):
+        done = np.zeros((T, T), np.int32)
+        lead = np.zeros((T, T), bool)
+        for r in range(world):
+            a0, a1 = k.rank_tiles(split, r, world)
+            b0, b1 = k.rank_tiles(len(ti) - split, r, world)
+            for t in list(range(a0, a1)) + list(range(split + b0, split + b1)):
+                done[ti[t], tj[t]] += 1
+            for t in range(a0, a1):
+                lead[ti[t], tj[t]] = lead[tj[t], ti[t]] = True
+        assert np.array_equal(done, np.triu(np.ones((T, T), np.int32)))
+        assert lead[:Ta, :Ta].all()
+
+
 @pytest.mark.parametrize("world,n", [(1, 5), (2, 300), (3, 513), (8, 1000)])
 def test_unpack_shards_host_matches_device_contract(world, n):
     # krd_unpack_shards_host is the host twin of k_unpack (used by `gappa-b200 --gpus G`): no GPU needed

@@ -143,9 +143,14 @@ public:
         double dx = (double)ix;
         if (p_ < e_ && *p_ == '.') {
             ++p_;
+            // the reference forms the place value by repeated division (pos /= 10.0 per digit, reader.cpp:290-296); that
+            // sequence does not depend on the input, so it is tabulated ONCE with the same divisions — same bits, without a
+            // serial chain of ~17 divides per number (64 -> 40 ns per number on 17-digit fractions)
+            const double* const pw = frac_place_values();
+            int k = 0;
             double pos = 1.0;
             while (p_ < e_ && *p_ >= '0' && *p_ <= '9') {
-                pos /= 10.0;
+                if (k < FRAC_TABLE) pos = pw[k++]; else pos /= 10.0;
                 dx += (double)(*p_ - '0') * pos;
                 ++p_; mant = true;
             }
@@ -209,6 +214,16 @@ public:
     }
 
     const std::string& source() const { return src_; }
+
+    static constexpr int FRAC_TABLE = 40;
+    static const double* frac_place_values()       // [k] = 1.0 divided k + 1 times by 10.0, one division after the other
+    {
+        static const struct Table {
+            double v[FRAC_TABLE];
+            Table() { double pos = 1.0; for (int k = 0; k < FRAC_TABLE; ++k) { pos /= 10.0; v[k] = pos; } }
+        } t;
+        return t.v;
+    }
 
 private:
     const char* p_;
